@@ -1,0 +1,402 @@
+// The whole parameter-server training step of the reference's MNIST MLP as ONE
+// persistent cooperative kernel: pull -> forward -> loss/accuracy -> backward ->
+// push+apply -> global_step, for `nsteps` consecutive steps without returning to
+// the host.
+//
+// Reference step (worker.py:129-141): sess.run(sync_op) [4 Assign pulls over gRPC],
+// sess.run([train_op, loss, summary, global_step]) [fwd/bwd on GPU, 4 gradient
+// tensors over gRPC, ApplyGradientDescent on the ps CPU], sess.run(counter_op).
+// Three RPC round trips and ~25 TF kernels.  Here:
+//
+//   phase A  each CTA owns a KS-row slice of W1 ([D,H], reference layout [in,out]).
+//            It reads that slice *directly from the ps shard* (possibly a peer GPU's
+//            HBM: this is the pull) and the matching KS columns of the batch, and
+//            writes a split-K partial of X.W1 to scratch.
+//   barrier
+//   phase B  two batch rows per CTA: reduce the partials, +b1, sigmoid, logits with
+//            W2/b2 read from the shard, softmax cross-entropy fwd+bwd, accuracy,
+//            dA = (dZ.W2^T) * h(1-h).
+//   barrier
+//   phase C  each CTA computes dW1 for the SAME KS rows it pulled (X slice is still in
+//            shared memory) and pushes -lr*dW1 into the shard with red.add.sys: the
+//            push is the apply, there is no ps-side kernel.  dW2/db1/db2 rows are
+//            spread over CTAs the same way.  The last CTA to finish bumps global_step
+//            with a system-scope atomic and records the pre-increment value
+//            (the `step` the reference fetches).
+//
+// Scratch (global memory beyond inputs/outputs): the split-K partials, H, dA, dZ,
+// per-row loss/correct flags and three sync words.
+#include "common.cuh"
+#include <math.h>
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kMaxB = 128, kMaxH = 128, kMaxC = 16;
+
+struct Mlp2Args {
+  int B, D, H, C;
+  float *W1, *b1, *W2, *b2;
+  int* global_step;
+  const float* X; long ldx;
+  const int* labels;
+  const int* batch_idx;     // [nsteps*B] dataset rows, or null
+  long rows_per_step;       // used when batch_idx is null: row = s*rows_per_step + r
+  float* part;              // [G][B][H]
+  float* Hbuf;              // [B][H]
+  float* dA;                // [B][H]
+  float* dZ;                // [B][C]
+  float* rowloss;           // [B]
+  int* rowcorrect;          // [B]
+  unsigned* sync;           // [4]: grid barrier, exit count, done count, -
+  float* loss_out;          // [nsteps]
+  float* acc_out;           // [nsteps]
+  int* step_out;            // [nsteps]
+  float lr;
+  int nsteps;
+  int atomic;
+  int train;                // 0: forward/metrics only (no phase C)
+};
+
+__device__ __forceinline__ void grid_barrier(unsigned* ctr, unsigned& target, unsigned G) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    target += G;
+    __threadfence();
+    atomicAdd(ctr, 1u);
+    while (dtfe::ld_acquire_gpu(ctr) < target) { }
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ void push1(float* p, float v, int atomic) {
+  if (atomic) dtfe::red_add_sys(p, v);
+  else *p = dtfe::ld_relaxed_sys(p) + v;
+}
+
+template <int KS>
+__global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
+  extern __shared__ __align__(16) float smem[];
+  const int B = a.B, D = a.D, H = a.H, C = a.C;
+  const int HP = H;  // row pitch of H-wide smem tiles
+  float* Xs = smem;                       // [B][KS]
+  float* Ws = Xs + kMaxB * KS;            // [KS][H]
+  float* W2s = Ws + KS * kMaxH;           // [H][C]
+  float* b1s = W2s + kMaxH * kMaxC;       // [H]
+  float* b2s = b1s + kMaxH;               // [C]
+  float* hs = b2s + kMaxC;                // [2][H]
+  float* zs = hs + 2 * kMaxH;             // [2][C]
+  float* dzs = zs + 2 * kMaxC;            // [2][C]
+  float* red = dzs + 2 * kMaxC;           // [256]
+  float* dZs = red + kThreads;            // [B][C]
+  float* dAs = dZs + kMaxB * kMaxC;       // [B][H]  (phase C)
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const unsigned G = gridDim.x;
+  const int g = blockIdx.x;
+  const int k0 = g * KS;
+  unsigned bar_target = 0;
+  const float invB = 1.f / (float)B;
+
+  for (int s = 0; s < a.nsteps; ++s) {
+    // ------------------------------ phase A ------------------------------------
+    for (int e = tid; e < B * KS; e += kThreads) {
+      int r = e / KS, kk = e % KS;
+      long row = a.batch_idx ? (long)a.batch_idx[(long)s * B + r] : (long)s * a.rows_per_step + r;
+      int k = k0 + kk;
+      Xs[e] = (k < D) ? __ldg(a.X + row * a.ldx + k) : 0.f;
+    }
+    for (int e = tid; e < KS * H; e += kThreads) {
+      int kk = e / H, j = e % H;
+      int k = k0 + kk;
+      Ws[kk * HP + j] = (k < D) ? dtfe::ld_relaxed_sys(a.W1 + (long)k * H + j) : 0.f;
+    }
+    __syncthreads();
+    {
+      float acc[16][4];
+#pragma unroll
+      for (int i = 0; i < 16; ++i)
+#pragma unroll
+        for (int jj = 0; jj < 4; ++jj) acc[i][jj] = 0.f;
+#pragma unroll
+      for (int kk = 0; kk < KS; ++kk) {
+        float wv[4];
+#pragma unroll
+        for (int jj = 0; jj < 4; ++jj) {
+          int j = lane + 32 * jj;
+          wv[jj] = (j < H) ? Ws[kk * HP + j] : 0.f;
+        }
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          int r = warp + 8 * i;
+          float xv = (r < B) ? Xs[r * KS + kk] : 0.f;
+#pragma unroll
+          for (int jj = 0; jj < 4; ++jj) acc[i][jj] = fmaf(xv, wv[jj], acc[i][jj]);
+        }
+      }
+      float* P = a.part + (long)g * B * H;
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        int r = warp + 8 * i;
+        if (r < B) {
+#pragma unroll
+          for (int jj = 0; jj < 4; ++jj) {
+            int j = lane + 32 * jj;
+            if (j < H) __stcg(P + (long)r * H + j, acc[i][jj]);
+          }
+        }
+      }
+    }
+    grid_barrier(a.sync, bar_target, G);
+
+    // ------------------------------ phase B ------------------------------------
+    // Small parameters are read after the barrier so that every CTA sees the pushes
+    // all CTAs made in the previous step's phase C.
+    for (int e = tid; e < H * C; e += kThreads) W2s[e] = dtfe::ld_relaxed_sys(a.W2 + e);
+    if (tid < H) b1s[tid] = dtfe::ld_relaxed_sys(a.b1 + tid);
+    if (tid < C) b2s[tid] = dtfe::ld_relaxed_sys(a.b2 + tid);
+    __syncthreads();
+    {
+      const int slot = tid >> 7, t = tid & 127, wq = warp & 3;
+      for (int r0 = 2 * g; r0 < B; r0 += 2 * (int)G) {
+        const int r = r0 + slot;
+        const bool rv = r < B;
+        float h = 0.f;
+        if (rv && t < H) {
+          float z = b1s[t];
+          const float* P = a.part + (long)r * H + t;
+          const long gs = (long)B * H;
+          unsigned q = 0;
+          for (; q + 8 <= G; q += 8) {
+            float v[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) v[u] = __ldcg(P + (long)(q + u) * gs);
+#pragma unroll
+            for (int u = 0; u < 8; ++u) z += v[u];
+          }
+          for (; q < G; ++q) z += __ldcg(P + (long)q * gs);
+          h = dtfe::sigmoidf_fast(z);
+          hs[slot * kMaxH + t] = h;
+          __stcg(a.Hbuf + (long)r * H + t, h);
+        }
+        __syncthreads();
+        for (int c = wq; c < C; c += 4) {
+          float p = 0.f;
+          for (int u = lane; u < H; u += 32) p = fmaf(hs[slot * kMaxH + u], W2s[u * C + c], p);
+          p = dtfe::warp_sum(p);
+          if (lane == 0) zs[slot * kMaxC + c] = p + b2s[c];
+        }
+        __syncthreads();
+        if (wq == 0 && rv) {
+          float z = (lane < C) ? zs[slot * kMaxC + lane] : -INFINITY;
+          float mx = z; int am = (lane < C) ? lane : 0x7fffffff;
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) {
+            float om = __shfl_xor_sync(0xffffffffu, mx, o);
+            int oa = __shfl_xor_sync(0xffffffffu, am, o);
+            if (om > mx || (om == mx && oa < am)) { mx = om; am = oa; }
+          }
+          float ex = (lane < C) ? __expf(z - mx) : 0.f;
+          float se = dtfe::warp_sum(ex);
+          long row = a.batch_idx ? (long)a.batch_idx[(long)s * B + r] : (long)s * a.rows_per_step + r;
+          int y = a.labels[row];
+          float zy = __shfl_sync(0xffffffffu, z, y);
+          if (lane < C) {
+            float dz = (ex / se - (lane == y ? 1.f : 0.f)) * invB;
+            dzs[slot * kMaxC + lane] = dz;
+            __stcg(a.dZ + (long)r * C + lane, dz);
+          }
+          if (lane == 0) {
+            __stcg(a.rowloss + r, mx + __logf(se) - zy);
+            __stcg(a.rowcorrect + r, (am == y) ? 1 : 0);
+          }
+        }
+        __syncthreads();
+        if (rv && t < H) {
+          float dh = 0.f;
+          for (int c = 0; c < C; ++c) dh = fmaf(dzs[slot * kMaxC + c], W2s[t * C + c], dh);
+          __stcg(a.dA + (long)r * H + t, dh * h * (1.f - h));
+        }
+        __syncthreads();
+      }
+    }
+    grid_barrier(a.sync, bar_target, G);
+
+    // ------------------------------ phase C ------------------------------------
+    if (g == 0 && warp == 7) {
+      // metrics of this step, fixed summation order -> bitwise reproducible
+      float l = 0.f; int cnt = 0;
+      for (int r = lane; r < B; r += 32) { l += __ldcg(a.rowloss + r); cnt += __ldcg(a.rowcorrect + r); }
+      l = dtfe::warp_sum(l);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+      if (lane == 0) {
+        a.loss_out[s] = l * invB;
+        a.acc_out[s] = (float)cnt * invB;
+      }
+    }
+    if (a.train) {
+      const float nlr = -a.lr;
+      for (int e = tid; e < (B * H) / 4; e += kThreads)
+        reinterpret_cast<float4*>(dAs)[e] = __ldcg(reinterpret_cast<const float4*>(a.dA) + e);
+      for (int e = (B * H) / 4 * 4 + tid; e < B * H; e += kThreads) dAs[e] = __ldcg(a.dA + e);
+      for (int e = tid; e < B * C; e += kThreads) dZs[e] = __ldcg(a.dZ + e);
+      __syncthreads();
+      // dW1 rows [k0, k0+KS): warp <-> row (KS=8) or two rows (KS=16); lanes <-> columns
+      for (int kk = warp; kk < KS; kk += 8) {
+        int k = k0 + kk;
+        if (k >= D) break;
+        float acc[4] = {0.f, 0.f, 0.f, 0.f};
+        for (int b = 0; b < B; ++b) {
+          float xv = Xs[b * KS + kk];
+#pragma unroll
+          for (int jj = 0; jj < 4; ++jj) {
+            int j = lane + 32 * jj;
+            float d = (j < H) ? dAs[b * HP + j] : 0.f;
+            acc[jj] = fmaf(xv, d, acc[jj]);
+          }
+        }
+#pragma unroll
+        for (int jj = 0; jj < 4; ++jj) {
+          int j = lane + 32 * jj;
+          if (j < H) push1(a.W1 + (long)k * H + j, nlr * acc[jj], a.atomic);
+        }
+      }
+      // small gradients: hidden unit t handled by CTA t % G
+      for (int t = g; t < H; t += (int)G) {
+        if (warp == 0) {  // dW2[t][:] = sum_b H[b][t] * dZ[b][:]
+          float accc[kMaxC];
+#pragma unroll
+          for (int c = 0; c < kMaxC; ++c) accc[c] = 0.f;
+          for (int b = lane; b < B; b += 32) {
+            float hv = __ldcg(a.Hbuf + (long)b * H + t);
+#pragma unroll
+            for (int c = 0; c < kMaxC; ++c)
+              if (c < C) accc[c] = fmaf(hv, dZs[b * C + c], accc[c]);
+          }
+#pragma unroll
+          for (int c = 0; c < kMaxC; ++c) {
+            if (c < C) {
+              float v = dtfe::warp_sum(accc[c]);
+              if (lane == 0) push1(a.W2 + (long)t * C + c, nlr * v, a.atomic);
+            }
+          }
+        } else if (warp == 1) {  // db1[t] = sum_b dA[b][t]
+          float v = 0.f;
+          for (int b = lane; b < B; b += 32) v += dAs[b * HP + t];
+          v = dtfe::warp_sum(v);
+          if (lane == 0) push1(a.b1 + t, nlr * v, a.atomic);
+        }
+      }
+      if (g == (int)G - 1 && warp == 2) {  // db2[c] = sum_b dZ[b][c]
+        for (int c = 0; c < C; ++c) {
+          float v = 0.f;
+          for (int b = lane; b < B; b += 32) v += dZs[b * C + c];
+          v = dtfe::warp_sum(v);
+          if (lane == 0) push1(a.b2 + c, nlr * v, a.atomic);
+        }
+      }
+      // all of this CTA's pushes are performed before it reports completion
+      __threadfence_system();
+      __syncthreads();
+      if (tid == 0) {
+        unsigned prev = atomicAdd(a.sync + 2, 1u);
+        if (prev == G - 1) {
+          a.sync[2] = 0;
+          int old = dtfe::atom_add_sys_s32(a.global_step, 1);
+          a.step_out[s] = old;
+        }
+      }
+    } else if (g == 0 && tid == 0) {
+      a.step_out[s] = *reinterpret_cast<volatile int*>(a.global_step);
+    }
+  }
+
+  // leave the sync words zeroed for the next launch
+  __syncthreads();
+  if (tid == 0) {
+    unsigned prev = atomicAdd(a.sync + 1, 1u);
+    if (prev == G - 1) { a.sync[0] = 0; a.sync[1] = 0; __threadfence(); }
+  }
+}
+
+template <int KS>
+constexpr size_t smem_floats() {
+  return (size_t)kMaxB * KS + (size_t)KS * kMaxH + kMaxH * kMaxC + kMaxH + kMaxC + 2 * kMaxH + 2 * kMaxC +
+         2 * kMaxC + kThreads + kMaxB * kMaxC + (size_t)kMaxB * kMaxH;
+}
+
+}  // namespace
+
+// Scratch sizing for callers: floats needed for `part` given the grid, plus the fixed rest.
+DTFE_API int dtfe_mlp2_step_grid(int D, int ks) { return (D + ks - 1) / ks; }
+
+// Element counts (4-byte words) of the scratch regions, in the order the workspace is carved:
+// part[G*B*H] | Hbuf[B*H] | dA[B*H] | dZ[B*C] | rowloss[B] | rowcorrect[B] | sync[4]
+DTFE_API size_t dtfe_mlp2_step_workspace_words(int B, int D, int H, int C, int ks) {
+  size_t G = (size_t)((D + ks - 1) / ks);
+  size_t w = G * B * H + 2 * (size_t)B * H + (size_t)B * C + 2 * (size_t)B + 4;
+  return (w + 3) / 4 * 4 + 16;
+}
+
+struct Mlp2Launch {
+  int B, D, H, C, ks;
+  float *W1, *b1, *W2, *b2;
+  int* global_step;
+  const float* X; long ldx;
+  const int* labels;
+  const int* batch_idx;
+  long rows_per_step;
+  float* workspace;   // dtfe_mlp2_step_workspace_words() words, zero-initialised once
+  float* loss_out; float* acc_out; int* step_out;
+  float lr; int nsteps; int atomic; int train;
+};
+
+static int mlp2_fill(const Mlp2Launch& L, Mlp2Args& a) {
+  DTFE_REQUIRE(L.B >= 1 && L.B <= kMaxB, "mlp2_step: batch %d outside [1,%d]", L.B, kMaxB);
+  DTFE_REQUIRE(L.H >= 1 && L.H <= kMaxH, "mlp2_step: hidden %d outside [1,%d]", L.H, kMaxH);
+  DTFE_REQUIRE(L.C >= 1 && L.C <= kMaxC, "mlp2_step: classes %d outside [1,%d]", L.C, kMaxC);
+  DTFE_REQUIRE(L.ks == 8 || L.ks == 16, "mlp2_step: ks must be 8 or 16");
+  DTFE_REQUIRE(((uintptr_t)L.workspace % 16) == 0, "mlp2_step: workspace must be 16-byte aligned");
+  size_t G = (size_t)((L.D + L.ks - 1) / L.ks);
+  DTFE_REQUIRE(G <= 148, "mlp2_step: D/ks = %zu CTAs exceeds one wave (148); use ks=16 or the layer path", G);
+  a.B = L.B; a.D = L.D; a.H = L.H; a.C = L.C;
+  a.W1 = L.W1; a.b1 = L.b1; a.W2 = L.W2; a.b2 = L.b2; a.global_step = L.global_step;
+  a.X = L.X; a.ldx = L.ldx; a.labels = L.labels; a.batch_idx = L.batch_idx; a.rows_per_step = L.rows_per_step;
+  float* w = L.workspace;
+  a.part = w;               w += G * L.B * L.H;
+  w = (float*)(((uintptr_t)w + 15) & ~(uintptr_t)15);
+  a.dA = w;                 w += (size_t)L.B * L.H;
+  w = (float*)(((uintptr_t)w + 15) & ~(uintptr_t)15);
+  a.Hbuf = w;               w += (size_t)L.B * L.H;
+  a.dZ = w;                 w += (size_t)L.B * L.C;
+  a.rowloss = w;            w += L.B;
+  a.rowcorrect = (int*)w;   w += L.B;
+  a.sync = (unsigned*)w;
+  a.loss_out = L.loss_out; a.acc_out = L.acc_out; a.step_out = L.step_out;
+  a.lr = L.lr; a.nsteps = L.nsteps; a.atomic = L.atomic; a.train = L.train;
+  return 0;
+}
+
+template <int KS>
+static int mlp2_launch(Mlp2Args& a, cudaStream_t stream) {
+  static bool configured[64] = {};
+  int dev;
+  DTFE_CUDA_CHECK(cudaGetDevice(&dev));
+  size_t smem = smem_floats<KS>() * sizeof(float);
+  if (dev < 64 && !configured[dev]) {
+    DTFE_CUDA_CHECK(cudaFuncSetAttribute(k_mlp2_step<KS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured[dev] = true;
+  }
+  int G = (a.D + KS - 1) / KS;
+  void* args[] = {&a};
+  DTFE_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)k_mlp2_step<KS>, dim3(G), dim3(kThreads), args, smem, stream));
+  return 0;
+}
+
+// Run `nsteps` full training (train=1) or metric-only (train=0) steps of the 2-layer MLP.
+DTFE_API int dtfe_mlp2_step(const Mlp2Launch* L, void* stream) {
+  Mlp2Args a{};
+  if (int rc = mlp2_fill(*L, a)) return rc;
+  return L->ks == 8 ? mlp2_launch<8>(a, (cudaStream_t)stream) : mlp2_launch<16>(a, (cudaStream_t)stream);
+}

@@ -1,0 +1,226 @@
+// Parameter-server data movement over peer memory, as standalone kernels:
+//   * async push + SGD apply  : shard[i] += alpha*grad[i] with fire-and-forget red.add.sys
+//   * Adam                    : push accumulates into an owner-side slot; owner applies
+//   * pull                    : shard -> local copy with L1-bypassing vector loads
+//   * sync reduce-scatter+apply: every owner reduces its slice of all workers' gradient
+//                                buffers straight out of peer HBM and applies it, with
+//                                flag barriers in peer memory (no NCCL, no staging)
+//
+// Reference mechanism replaced: gRPC _Send/_Recv of 4 gradient tensors to the ps and a
+// CPU ApplyGradientDescent there (worker.py:75-79), and the 4 Assign ops of the pull
+// (worker.py:81-85).  The fused-epilogue forms live in dense_simt.cu / gemm_tc.cu /
+// mlp2_step.cu; these flat kernels are the bandwidth-sweep subjects and the sync path.
+#include "common.cuh"
+
+namespace {
+
+__global__ void __launch_bounds__(256) k_push_sgd_f32(float* __restrict__ shard,
+                                                      const float* __restrict__ grad, size_t n,
+                                                      float alpha, int atomic) {
+  size_t nv = n / 4;
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  size_t stride = (size_t)gridDim.x * blockDim.x;
+  const float4* g4 = reinterpret_cast<const float4*>(grad);
+  for (size_t v = i; v < nv; v += stride) {
+    float4 g = __ldg(g4 + v);
+    g.x *= alpha; g.y *= alpha; g.z *= alpha; g.w *= alpha;
+    if (atomic) {
+      dtfe::red_add_sys_v4(shard + v * 4, g);
+    } else {
+      float4 w = dtfe::ld_relaxed_sys_v4(shard + v * 4);
+      w.x += g.x; w.y += g.y; w.z += g.z; w.w += g.w;
+      *reinterpret_cast<float4*>(shard + v * 4) = w;
+    }
+  }
+  for (size_t e = nv * 4 + i; e < n; e += stride) {
+    float g = alpha * grad[e];
+    if (atomic) dtfe::red_add_sys(shard + e, g);
+    else shard[e] = dtfe::ld_relaxed_sys(shard + e) + g;
+  }
+}
+
+__global__ void __launch_bounds__(256) k_push_sgd_bf16(__nv_bfloat16* __restrict__ shard,
+                                                       const float* __restrict__ grad, size_t n,
+                                                       float alpha) {
+  size_t nv = n / 8;
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  size_t stride = (size_t)gridDim.x * blockDim.x;
+  const float4* g4 = reinterpret_cast<const float4*>(grad);
+  for (size_t v = i; v < nv; v += stride) {
+    float4 a = __ldg(g4 + 2 * v), b = __ldg(g4 + 2 * v + 1);
+    uint4 p;
+    p.x = dtfe::pack_bf16x2(alpha * a.x, alpha * a.y);
+    p.y = dtfe::pack_bf16x2(alpha * a.z, alpha * a.w);
+    p.z = dtfe::pack_bf16x2(alpha * b.x, alpha * b.y);
+    p.w = dtfe::pack_bf16x2(alpha * b.z, alpha * b.w);
+    dtfe::red_add_sys_v4_bf16x2(shard + v * 8, p);
+  }
+  for (size_t e = nv * 8 + i * 2; e + 1 < n; e += stride * 2)
+    dtfe::red_add_sys_bf16x2(shard + e, dtfe::pack_bf16x2(alpha * grad[e], alpha * grad[e + 1]));
+}
+
+__global__ void __launch_bounds__(256) k_pull_f32(float* __restrict__ dst, const float* __restrict__ shard,
+                                                  size_t n) {
+  size_t nv = n / 4;
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t v = i; v < nv; v += stride)
+    *reinterpret_cast<float4*>(dst + v * 4) = dtfe::ld_relaxed_sys_v4(shard + v * 4);
+  for (size_t e = nv * 4 + i; e < n; e += stride) dst[e] = dtfe::ld_relaxed_sys(shard + e);
+}
+
+// Adam: workers red.add raw gradients into `slot` (owner HBM); the owner applies and clears.
+__global__ void __launch_bounds__(256) k_adam_apply(float* __restrict__ p, float* __restrict__ m,
+                                                    float* __restrict__ v, float* __restrict__ slot,
+                                                    size_t n, float lr_t, float b1, float b2, float eps,
+                                                    float gscale) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) {
+    float g = dtfe::ld_relaxed_sys(slot + i) * gscale;
+    slot[i] = 0.f;
+    float mi = b1 * m[i] + (1.f - b1) * g;
+    float vi = b2 * v[i] + (1.f - b2) * g * g;
+    m[i] = mi; v[i] = vi;
+    p[i] -= lr_t * mi / (sqrtf(vi) + eps);
+  }
+}
+
+// ---- synchronous mode: reduce-scatter fused with the update --------------------------
+constexpr int kMaxRanks = 16;
+struct SyncArgs {
+  const float* grads[kMaxRanks];  // every rank's gradient buffer (peer-mapped), full model length
+  unsigned* flags[kMaxRanks];     // every rank's flag array (peer-mapped): [2][kMaxRanks] u32
+  float* param;                   // this rank's owned shard memory (local HBM), indexed like grads
+  size_t begin, end;              // owned element range inside the flat gradient vector
+  size_t param_off;               // param element i lives at param[i - param_off]
+  float alpha;                    // -lr / W
+  int rank, world;
+  unsigned epoch;                 // strictly increasing per call, starts at 1
+  unsigned* local_sync;           // [4] u32 in local HBM: {go, done_count, _, _}
+  int* global_step;               // non-null on the owner of shard 0
+};
+
+__global__ void __launch_bounds__(256) k_sync_rs_apply(SyncArgs a) {
+  // (a) arrive: tell every peer "my gradients for this epoch are complete", then wait for all.
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    __threadfence_system();
+    for (int p = 0; p < a.world; ++p) dtfe::st_release_sys(a.flags[p] + a.rank, a.epoch);
+    for (int q = 0; q < a.world; ++q)
+      while (dtfe::ld_acquire_sys(a.flags[a.rank] + q) < a.epoch) { __nanosleep(20); }
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" :: "l"(a.local_sync), "r"(a.epoch) : "memory");
+  }
+  if (threadIdx.x == 0) {
+    while (dtfe::ld_acquire_gpu(a.local_sync) < a.epoch) { __nanosleep(20); }
+  }
+  __syncthreads();
+
+  // (b) reduce my slice over all ranks' buffers (peer loads) and apply in place.
+  size_t n = a.end - a.begin;
+  size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  size_t stride = (size_t)gridDim.x * blockDim.x;
+  bool vec_ok = ((a.begin | a.param_off) % 4 == 0);
+  size_t nv = vec_ok ? n / 4 : 0;
+  for (size_t v = tid; v < nv; v += stride) {
+    size_t i = a.begin + v * 4;
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int q = 0; q < a.world; ++q) {
+      float4 g = dtfe::ld_relaxed_sys_v4(a.grads[q] + i);
+      s.x += g.x; s.y += g.y; s.z += g.z; s.w += g.w;
+    }
+    float4* w = reinterpret_cast<float4*>(a.param + (i - a.param_off));
+    float4 o = *w;
+    o.x += a.alpha * s.x; o.y += a.alpha * s.y; o.z += a.alpha * s.z; o.w += a.alpha * s.w;
+    *w = o;
+  }
+  for (size_t e = nv * 4 + tid; e < n; e += stride) {
+    size_t i = a.begin + e;
+    float s = 0.f;
+    for (int q = 0; q < a.world; ++q) s += dtfe::ld_relaxed_sys(a.grads[q] + i);
+    a.param[i - a.param_off] += a.alpha * s;
+  }
+
+  // (c) depart: once the whole grid has applied, publish and wait until every owner has too,
+  // so that on kernel exit all shards hold the new parameters and no gradient buffer is still
+  // being read by a peer.
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned prev = atomicAdd(a.local_sync + 1, 1u);
+    if (prev == gridDim.x - 1) {
+      a.local_sync[1] = 0;
+      if (a.global_step) dtfe::atom_add_sys_s32(a.global_step, 1);
+      __threadfence_system();
+      for (int p = 0; p < a.world; ++p)
+        dtfe::st_release_sys(a.flags[p] + kMaxRanks + a.rank, a.epoch);
+      for (int q = 0; q < a.world; ++q)
+        while (dtfe::ld_acquire_sys(a.flags[a.rank] + kMaxRanks + q) < a.epoch) { __nanosleep(20); }
+    }
+  }
+}
+
+inline int grid_for(size_t n, int per_thread) {
+  size_t blocks = (n / per_thread + 255) / 256;
+  if (blocks < 1) blocks = 1;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  return (int)blocks;
+}
+
+}  // namespace
+
+DTFE_API int dtfe_push_sgd_f32(float* shard, const float* grad, size_t n, float alpha, int atomic,
+                               void* stream) {
+  DTFE_REQUIRE(((uintptr_t)shard % 16 == 0) && ((uintptr_t)grad % 16 == 0),
+               "dtfe_push_sgd_f32: shard and grad must be 16-byte aligned");
+  k_push_sgd_f32<<<grid_for(n, 4), 256, 0, (cudaStream_t)stream>>>(shard, grad, n, alpha, atomic);
+  DTFE_LAUNCH_CHECK();
+  return 0;
+}
+
+DTFE_API int dtfe_push_sgd_bf16(void* shard_bf16, const float* grad, size_t n, float alpha, void* stream) {
+  DTFE_REQUIRE(((uintptr_t)shard_bf16 % 16 == 0) && ((uintptr_t)grad % 16 == 0) && (n % 2 == 0),
+               "dtfe_push_sgd_bf16: 16-byte alignment and even n required");
+  k_push_sgd_bf16<<<grid_for(n, 8), 256, 0, (cudaStream_t)stream>>>((__nv_bfloat16*)shard_bf16, grad, n, alpha);
+  DTFE_LAUNCH_CHECK();
+  return 0;
+}
+
+DTFE_API int dtfe_pull_f32(float* dst, const float* shard, size_t n, void* stream) {
+  DTFE_REQUIRE(((uintptr_t)shard % 16 == 0) && ((uintptr_t)dst % 16 == 0),
+               "dtfe_pull_f32: 16-byte alignment required");
+  k_pull_f32<<<grid_for(n, 4), 256, 0, (cudaStream_t)stream>>>(dst, shard, n);
+  DTFE_LAUNCH_CHECK();
+  return 0;
+}
+
+// lr_t is the bias-corrected step size lr*sqrt(1-b2^t)/(1-b1^t) computed by the caller.
+DTFE_API int dtfe_adam_apply_f32(float* param, float* m, float* v, float* slot, size_t n, float lr_t,
+                                 float beta1, float beta2, float eps, float grad_scale, void* stream) {
+  k_adam_apply<<<grid_for(n, 1), 256, 0, (cudaStream_t)stream>>>(param, m, v, slot, n, lr_t, beta1, beta2,
+                                                                 eps, grad_scale);
+  DTFE_LAUNCH_CHECK();
+  return 0;
+}
+
+// One call per rank per step, all ranks, ONE RANK PER GPU (the kernel spins on peer flags).
+DTFE_API int dtfe_sync_rs_apply_f32(const float* const* grads, unsigned* const* flags, int rank, int world,
+                                    float* param, size_t begin, size_t end, size_t param_off, float alpha,
+                                    unsigned epoch, unsigned* local_sync, int* global_step_or_null,
+                                    void* stream) {
+  DTFE_REQUIRE(world >= 1 && world <= kMaxRanks, "dtfe_sync_rs_apply_f32: world must be in [1,%d]", kMaxRanks);
+  DTFE_REQUIRE(end >= begin, "dtfe_sync_rs_apply_f32: bad range");
+  SyncArgs a{};
+  for (int i = 0; i < world; ++i) { a.grads[i] = grads[i]; a.flags[i] = flags[i]; }
+  a.param = param; a.begin = begin; a.end = end; a.param_off = param_off; a.alpha = alpha;
+  a.rank = rank; a.world = world; a.epoch = epoch; a.local_sync = local_sync;
+  a.global_step = global_step_or_null;
+  // All CTAs must be co-resident (they wait on block 0): cap at one wave and launch cooperatively.
+  int grid = grid_for(end - begin, 8);
+  if (grid > 148) grid = 148;
+  void* args[] = {&a};
+  DTFE_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)k_sync_rs_apply, dim3(grid), dim3(256), args, 0,
+                                              (cudaStream_t)stream));
+  return 0;
+}
+
+DTFE_API int dtfe_sync_max_ranks() { return kMaxRanks; }

@@ -1,0 +1,129 @@
+"""Benchmark bodies behind ``bench.py`` (kept in the package so tests can import them)."""
+from __future__ import annotations
+
+import json
+import os
+import time
+from typing import Optional
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+METRIC = "MNIST MLP examples/sec (device-timed, max over ranks)"
+
+
+def _barrier(world):
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+
+
+def _max_over_ranks(value: float, world: int, dev) -> float:
+    if world == 1:
+        return value
+    t = torch.tensor([value], device=dev, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def run_mnist(args, rank: int, world: int, dev, ClockSampler) -> int:
+    from .data import synthetic_arrays
+    from .models.mlp import reference_mlp_spec
+    from .parallel.spmd import build_spmd_store
+    from .train.gpu_step import DeviceDataset
+    from .train.trainer import GpuTrainer
+
+    spec = reference_mlp_spec()
+    B = args.batch or 100
+    lr = 0.001
+    K, W = args.steps, max(args.warmup, 3)
+    spl = args.steps_per_launch or min(K, 500)
+
+    model, store = build_spmd_store(spec, rank, world, dev, seed=0)
+    names = [v.name for v in model.global_trainable]
+    params = [store.tensor(n) for n in names]
+    gs = store.tensor("global/global_step")
+
+    # synthetic 784-dim data of MNIST's training-set shape (55000 x 784 fp32 = 172 MB > 126 MB L2);
+    # every step gathers 100 random rows of it, so inputs never sit in L2 from the previous step.
+    x, y = synthetic_arrays(55000, seed=1234 + rank)
+    ds = DeviceDataset(x, y.astype(np.int32), dev, seed=rank)
+    engine = args.engine if args.engine != "tc" else "layerwise"
+    tr = GpuTrainer(spec, B, lr, params, gs, dev, steps_per_launch=spl, engine=engine)
+
+    # ------------------------------ device-timed ------------------------------------------
+    if tr.fused is not None:
+        idx_w = ds.next_indices(B, W)
+        idx = ds.next_indices(B, K)
+        tr.run_indices(ds, idx_w, W)
+    else:
+        tr.train_device_steps(ds, W)
+    _barrier(world)
+    clocks = ClockSampler(dev.index or 0)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    launches0 = tr.launch_count
+    clocks.start()
+    e0.record()
+    if tr.fused is not None:
+        tr.run_indices(ds, idx, K)
+    else:
+        tr.train_device_steps(ds, K)
+    e1.record()
+    torch.cuda.synchronize()
+    clk = clocks.stop()
+    launches = tr.launch_count - launches0
+    ms = _max_over_ranks(e0.elapsed_time(e1), world, dev)
+    _barrier(world)
+    value = world * B * K / (ms * 1e-3)
+
+    # ------------------------------ end to end (host-fed) -----------------------------------
+    e2e = None
+    if not args.no_e2e:
+        Ke = args.e2e_steps or K
+        ring = 64
+        xs = [torch.from_numpy(x[i * B:(i + 1) * B].copy()).pin_memory() for i in range(ring)]
+        ys = [torch.from_numpy(y[i * B:(i + 1) * B].astype(np.int32)).pin_memory() for i in range(ring)]
+        for s in range(W):
+            tr.train_host_batch(xs[s % ring], ys[s % ring], out_index=s)
+        _barrier(world)
+        t0 = time.perf_counter()
+        last = None
+        for s in range(Ke):
+            last = tr.train_host_batch(xs[s % ring], ys[s % ring], out_index=s)
+        torch.cuda.synchronize()
+        t1 = time.perf_counter()
+        sec = _max_over_ranks(t1 - t0, world, dev)
+        assert np.isfinite(float(last[0]))
+        e2e = {"value": world * B * Ke / sec, "unit": "examples/sec", "steps": Ke,
+               "h2d_bytes_per_step": tr.h2d_bytes_per_step(), "d2h_bytes_per_step": tr.d2h_bytes_per_step(),
+               "timing": "host wall clock around the public API loop, max over ranks"}
+        _barrier(world)
+
+    final_step = int(gs.item()) if store.shard_of("global/global_step") % world == rank or True else -1
+    out = {
+        "metric": METRIC, "value": value, "unit": "examples/sec", "n_gpus": world, "steps": K, "warmup": W,
+        "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "fp32", "data": "synthetic (55000x784 fp32 + int labels per worker, MNIST train shape)",
+        "impl": "ours",
+        "config": {"model": "MNIST MLP 784-100-10 sigmoid/softmax (reference worker.py:46-57)",
+                   "global_batch": B * world, "batch_per_worker": B, "seq_len": None,
+                   "parallelism": f"async-ps dp{world} (worker+ps shard per GPU, peer HBM)",
+                   "optimizer": "sgd lr=0.001", "engine": tr.engine, "steps_per_launch": spl,
+                   "l2": "inputs larger than L2: 172 MB resident dataset, random rows every step"},
+        "gpu_launches": launches, "clocks": clk, "global_step_after": final_step,
+    }
+    if e2e is not None:
+        out["e2e"] = e2e
+    if rank == 0:
+        print(json.dumps(out), flush=True)
+    store.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def run_wide(args, rank: int, world: int, dev, ClockSampler) -> int:
+    from .bench_wide import run as _run
+    return _run(args, rank, world, dev, ClockSampler)

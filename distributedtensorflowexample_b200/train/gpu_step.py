@@ -1,0 +1,170 @@
+"""GPU training-step engines: everything between "a batch is on the device" and "global_step
+was incremented" (reference worker.py:131-141), with pull and push fused into the
+compute kernels.
+
+* ``FusedMlp2Stepper``  - the reference's 784-100-10 model: ONE persistent cooperative kernel per
+  launch, any number of steps per launch (``csrc/cuda/mlp2_step.cu``).
+* ``LayerwiseStepper``  - any depth/width: one fused kernel per layer and direction; fp32 SIMT
+  or (bf16/tf32) tcgen05 GEMMs with bias+sigmoid / sigmoid-grad / push epilogues.
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence
+
+import torch
+
+from ..models.mlp import MLPSpec
+from ..ops import cuda_ops as ops
+
+
+class DeviceDataset:
+    """Training set resident in HBM + on-device epoch sampler: ``next_indices`` yields the
+    dataset rows of the next ``nsteps`` batches with TF1 ``DataSet.next_batch`` semantics (reshuffle at
+    every epoch boundary, straddling batches take the rest of the old epoch first)."""
+
+    def __init__(self, images, label_ids, device, seed: Optional[int] = None):
+        self.device = torch.device(device)
+        self.images = torch.as_tensor(images, dtype=torch.float32).to(self.device).contiguous()
+        self.labels = torch.as_tensor(label_ids, dtype=torch.int32).to(self.device).contiguous()
+        self.n = self.images.shape[0]
+        self._gen = torch.Generator(device=self.device)
+        if seed is None:
+            self._gen.seed()
+        else:
+            self._gen.manual_seed(seed)
+        self._perm = torch.randperm(self.n, device=self.device, generator=self._gen, dtype=torch.int32)
+        self._pos = 0
+        self.epochs_completed = 0
+
+    def next_indices(self, batch: int, nsteps: int = 1) -> torch.Tensor:
+        need = batch * nsteps
+        chunks = []
+        while need > 0:
+            avail = self.n - self._pos
+            if avail == 0:
+                self._perm = torch.randperm(self.n, device=self.device, generator=self._gen, dtype=torch.int32)
+                self._pos = 0
+                self.epochs_completed += 1
+                avail = self.n
+            take = min(avail, need)
+            chunks.append(self._perm[self._pos:self._pos + take])
+            self._pos += take
+            need -= take
+        return chunks[0] if len(chunks) == 1 else torch.cat(chunks)
+
+
+class FusedMlp2Stepper:
+    def __init__(self, spec: MLPSpec, batch: int, params: Sequence[torch.Tensor], global_step: torch.Tensor,
+                 lr: float, device, max_steps_per_launch: int = 1, atomic: bool = True, ks: int = 8):
+        if spec.num_layers != 2 or spec.param_dtype != "float32":
+            raise ValueError("FusedMlp2Stepper handles 2-layer float32 models")
+        D, H, C = spec.dims
+        self.spec, self.batch, self.lr, self.atomic = spec, batch, lr, atomic
+        self.W1, self.b1, self.W2, self.b2 = params
+        self.global_step = global_step
+        self.k = ops.Mlp2Step(batch, D, H, C, device, max_steps=max_steps_per_launch, ks=ks)
+        self.launches_per_call = 1
+
+    @staticmethod
+    def supports(spec: MLPSpec, batch: int) -> bool:
+        return (spec.num_layers == 2 and spec.param_dtype == "float32" and batch <= 128 and spec.dims[1] <= 128
+                and spec.dims[2] <= 16 and (spec.dims[0] + 7) // 8 <= 148)
+
+    def run(self, X: torch.Tensor, labels: torch.Tensor, nsteps: int = 1, batch_idx: Optional[torch.Tensor] = None,
+            rows_per_step: int = 0, train: bool = True, out_offset: int = 0) -> None:
+        """Results land in ``self.k.loss/acc/step[out_offset : out_offset+nsteps]`` (device)."""
+        self.k.run(self.W1, self.b1, self.W2, self.b2, self.global_step, X, labels, self.lr, nsteps=nsteps,
+                   batch_idx=batch_idx, rows_per_step=rows_per_step, atomic=self.atomic, train=train,
+                   out_offset=out_offset)
+
+    @property
+    def loss(self): return self.k.loss
+    @property
+    def acc(self): return self.k.acc
+    @property
+    def step(self): return self.k.step
+
+
+class LayerwiseStepper:
+    """fp32 SIMT layer-by-layer engine (any MLPSpec).  Order of operations per step:
+    forward (weights read from the shards = pull) -> xent fwd/bwd -> for each layer, last to
+    first: dX against the *pre-update* weights, then dW/db with the push fused -> global_step."""
+
+    def __init__(self, spec: MLPSpec, batch: int, params: Sequence[torch.Tensor], global_step: torch.Tensor,
+                 lr: float, device, atomic: bool = True, grad_buffers: Optional[Sequence[torch.Tensor]] = None):
+        self.spec, self.batch, self.lr, self.atomic = spec, batch, lr, atomic
+        self.params = list(params)
+        self.global_step = global_step
+        dev = torch.device(device)
+        dims = spec.dims
+        f32 = dict(device=dev, dtype=torch.float32)
+        self.acts = [torch.empty(batch, d, **f32) for d in dims[1:-1]]
+        self.logits = torch.empty(batch, dims[-1], **f32)
+        self.dz = torch.empty(batch, dims[-1], **f32)
+        self.dacts = [torch.empty(batch, d, **f32) for d in dims[1:-1]]
+        self.rowloss = torch.empty(batch, **f32)
+        self.rowcorrect = torch.empty(batch, device=dev, dtype=torch.int32)
+        self.loss = torch.zeros(1, **f32)
+        self.acc = torch.zeros(1, **f32)
+        self.step = torch.zeros(1, device=dev, dtype=torch.int32)
+        # sync mode: gradients go to local buffers instead of being pushed
+        self.grad_buffers = list(grad_buffers) if grad_buffers is not None else None
+        self.launches_per_call = 2 * spec.num_layers + 2 + (spec.num_layers - 1) + spec.num_layers + 1
+
+    def forward(self, X: torch.Tensor, acts=None, logits=None) -> torch.Tensor:
+        acts = self.acts if acts is None else acts
+        logits = self.logits if logits is None else logits
+        h = X
+        L = self.spec.num_layers
+        for l in range(L):
+            W, b = self.params[2 * l], self.params[2 * l + 1]
+            last = l == L - 1
+            out = logits if last else acts[l]
+            ops.dense_fwd(h, W, b, ops.ACT_NONE if last else ops.ACT_SIGMOID, out=out, shard_reads=True)
+            h = out
+        return logits
+
+    def run(self, X: torch.Tensor, labels: torch.Tensor, train: bool = True) -> None:
+        B = X.shape[0]
+        self.forward(X)
+        ops.softmax_xent(self.logits, labels, 1.0 / B, self.dz if train else None, self.rowloss, self.rowcorrect)
+        ops.mean_loss_acc(self.rowloss, self.rowcorrect, B, self.loss, self.acc)
+        if not train:
+            return
+        alpha = -self.lr
+        d = self.dz
+        L = self.spec.num_layers
+        for l in reversed(range(L)):
+            W, b = self.params[2 * l], self.params[2 * l + 1]
+            h_in = X if l == 0 else self.acts[l - 1]
+            d_prev = None
+            if l > 0:
+                d_prev = ops.dense_bwd_dx(d, W, h_in, ops.ACT_SIGMOID, out=self.dacts[l - 1], shard_reads=True)
+            if self.grad_buffers is None:
+                ops.dense_bwd_dw_push(h_in, d, W, alpha, atomic=self.atomic)
+                ops.bias_grad_push(d, b, alpha, atomic=self.atomic)
+            else:
+                ops.dense_bwd_dw_push(h_in, d, None, 0.0, grad_out=self.grad_buffers[2 * l])
+                ops.bias_grad_push(d, None, 0.0, grad_out=self.grad_buffers[2 * l + 1])
+            d = d_prev
+        if self.grad_buffers is None:
+            ops.global_step_add(self.global_step, 1, self.step)
+
+    def eval_counts(self, X: torch.Tensor, labels: torch.Tensor, chunk: int = 16384):
+        """Test-set accuracy with the current shard weights (reference worker.py:150-154)."""
+        dev = X.device
+        correct = torch.zeros(1, device=dev, dtype=torch.int32)
+        total = 0
+        cnt = torch.zeros(1, device=dev, dtype=torch.int32)
+        for s in range(0, X.shape[0], chunk):
+            xb, yb = X[s:s + chunk], labels[s:s + chunk]
+            m = xb.shape[0]
+            acts = [torch.empty(m, d, device=dev, dtype=torch.float32) for d in self.spec.dims[1:-1]]
+            logits = torch.empty(m, self.spec.dims[-1], device=dev, dtype=torch.float32)
+            self.forward(xb, acts, logits)
+            rc = torch.empty(m, device=dev, dtype=torch.int32)
+            ops.softmax_xent(logits, yb, 1.0, None, None, rc)
+            ops.mean_loss_acc(None, rc, m, None, None, cnt)
+            correct += cnt
+            total += m
+        return correct, total
