@@ -1,0 +1,29 @@
+"""Tiny driver for ncu: a few launches of the fused MNIST step kernel (see profiles/README.md)."""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+import torch
+from distributedtensorflowexample_b200.models.mlp import reference_mlp_spec
+from distributedtensorflowexample_b200.parallel.spmd import build_spmd_store
+from distributedtensorflowexample_b200.train.gpu_step import DeviceDataset
+from distributedtensorflowexample_b200.train.trainer import GpuTrainer
+from distributedtensorflowexample_b200.data import synthetic_arrays
+
+nsteps = int(sys.argv[1]) if len(sys.argv) > 1 else 20
+launches = int(sys.argv[2]) if len(sys.argv) > 2 else 4
+dev = torch.device("cuda:0")
+spec = reference_mlp_spec()
+model, store = build_spmd_store(spec, 0, 1, dev)
+names = [v.name for v in model.global_trainable]
+x, y = synthetic_arrays(55000, seed=0)
+ds = DeviceDataset(x, y.astype(np.int32), dev, seed=0)
+tr = GpuTrainer(spec, 100, 0.001, [store.tensor(n) for n in names], store.tensor("global/global_step"), dev,
+                steps_per_launch=nsteps)
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+for i in range(launches):
+    idx = ds.next_indices(100, nsteps)
+    e0.record()
+    tr.run_indices(ds, idx, nsteps)
+    e1.record()
+    torch.cuda.synchronize()
+    print(f"launch {i}: {e0.elapsed_time(e1) * 1e3 / nsteps:.2f} us/step")
