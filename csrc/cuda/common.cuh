@@ -7,6 +7,11 @@
 
 #define DTFE_API extern "C" __attribute__((visibility("default")))
 
+// The public C ABI; every entry point defined in csrc/cuda is declared there.
+#pragma GCC visibility push(default)
+#include "dtfe_b200.h"
+#pragma GCC visibility pop
+
 // Error plumbing: every entry point returns 0 on success; on failure the text is
 // kept per thread and can be read back with dtfe_last_error().
 void dtfe_set_error(const char* fmt, ...);

@@ -56,6 +56,8 @@ struct Mlp2Args {
   int nsteps;
   int atomic;
   int train;                // 0: forward/metrics only (no phase C)
+  int remote;               // some shard lives on a peer GPU: completion fence must be .sys
+  long long* dbg;           // optional [nsteps][G][8] globaltimer stamps (profiling)
 };
 
 __device__ __forceinline__ void grid_barrier(unsigned* ctr, unsigned& target, unsigned G) {
@@ -64,10 +66,21 @@ __device__ __forceinline__ void grid_barrier(unsigned* ctr, unsigned& target, un
     target += G;
     __threadfence();
     atomicAdd(ctr, 1u);
-    while (dtfe::ld_acquire_gpu(ctr) < target) { }
+    unsigned v;
+    do {
+      asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
+    } while (v < target);
+    __threadfence();
   }
   __syncthreads();
 }
+
+__device__ __forceinline__ long long gtime() {
+  long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+#define DBG_STAMP(i) do { if (a.dbg && tid == 0) a.dbg[((long)s * G + g) * 8 + (i)] = gtime(); } while (0)
 
 __device__ __forceinline__ void push1(float* p, float v, int atomic) {
   if (atomic) dtfe::red_add_sys(p, v);
@@ -100,6 +113,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
 
   for (int s = 0; s < a.nsteps; ++s) {
     // ------------------------------ phase A ------------------------------------
+    DBG_STAMP(0);
     for (int e = tid; e < B * KS; e += kThreads) {
       int r = e / KS, kk = e % KS;
       long row = a.batch_idx ? (long)a.batch_idx[(long)s * B + r] : (long)s * a.rows_per_step + r;
@@ -147,7 +161,9 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
         }
       }
     }
+    DBG_STAMP(1);
     grid_barrier(a.sync, bar_target, G);
+    DBG_STAMP(2);
 
     // ------------------------------ phase B ------------------------------------
     // Small parameters are read after the barrier so that every CTA sees the pushes
@@ -220,7 +236,9 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
         __syncthreads();
       }
     }
+    DBG_STAMP(3);
     grid_barrier(a.sync, bar_target, G);
+    DBG_STAMP(4);
 
     // ------------------------------ phase C ------------------------------------
     if (g == 0 && warp == 7) {
@@ -296,10 +314,13 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
           if (lane == 0) push1(a.b2 + c, nlr * v, a.atomic);
         }
       }
-      // all of this CTA's pushes are performed before it reports completion
-      __threadfence_system();
+      // All of this CTA's pushes are performed before it reports completion: the CTA barrier orders
+      // every thread's reds before thread 0's fence, and fences are cumulative.
+      DBG_STAMP(5);
       __syncthreads();
       if (tid == 0) {
+        if (a.remote) __threadfence_system(); else __threadfence();
+        DBG_STAMP(6);
         unsigned prev = atomicAdd(a.sync + 2, 1u);
         if (prev == G - 1) {
           a.sync[2] = 0;
@@ -307,6 +328,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
           a.step_out[s] = old;
         }
       }
+      DBG_STAMP(7);
     } else if (g == 0 && tid == 0) {
       a.step_out[s] = *reinterpret_cast<volatile int*>(a.global_step);
     }
@@ -339,18 +361,7 @@ DTFE_API size_t dtfe_mlp2_step_workspace_words(int B, int D, int H, int C, int k
   return (w + 3) / 4 * 4 + 16;
 }
 
-struct Mlp2Launch {
-  int B, D, H, C, ks;
-  float *W1, *b1, *W2, *b2;
-  int* global_step;
-  const float* X; long ldx;
-  const int* labels;
-  const int* batch_idx;
-  long rows_per_step;
-  float* workspace;   // dtfe_mlp2_step_workspace_words() words, zero-initialised once
-  float* loss_out; float* acc_out; int* step_out;
-  float lr; int nsteps; int atomic; int train;
-};
+using Mlp2Launch = dtfe_mlp2_launch;
 
 static int mlp2_fill(const Mlp2Launch& L, Mlp2Args& a) {
   DTFE_REQUIRE(L.B >= 1 && L.B <= kMaxB, "mlp2_step: batch %d outside [1,%d]", L.B, kMaxB);
@@ -374,7 +385,7 @@ static int mlp2_fill(const Mlp2Launch& L, Mlp2Args& a) {
   a.rowcorrect = (int*)w;   w += L.B;
   a.sync = (unsigned*)w;
   a.loss_out = L.loss_out; a.acc_out = L.acc_out; a.step_out = L.step_out;
-  a.lr = L.lr; a.nsteps = L.nsteps; a.atomic = L.atomic; a.train = L.train;
+  a.lr = L.lr; a.nsteps = L.nsteps; a.atomic = L.atomic; a.train = L.train; a.remote = L.remote; a.dbg = L.dbg;
   return 0;
 }
 

@@ -50,7 +50,8 @@ def run_mnist(args, rank: int, world: int, dev, ClockSampler) -> int:
     x, y = synthetic_arrays(55000, seed=1234 + rank)
     ds = DeviceDataset(x, y.astype(np.int32), dev, seed=rank)
     engine = args.engine if args.engine != "tc" else "layerwise"
-    tr = GpuTrainer(spec, B, lr, params, gs, dev, steps_per_launch=spl, engine=engine)
+    tr = GpuTrainer(spec, B, lr, params, gs, dev, steps_per_launch=spl, engine=engine,
+                    remote=not store.all_local())
 
     # ------------------------------ device-timed ------------------------------------------
     if tr.fused is not None:

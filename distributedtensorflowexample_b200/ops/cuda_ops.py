@@ -271,7 +271,8 @@ class _Mlp2Launch(ctypes.Structure):
         ("rows_per_step", c_long),
         ("workspace", _P),
         ("loss_out", _P), ("acc_out", _P), ("step_out", _P),
-        ("lr", c_float), ("nsteps", c_int), ("atomic", c_int), ("train", c_int),
+        ("lr", c_float), ("nsteps", c_int), ("atomic", c_int), ("train", c_int), ("remote", c_int),
+        ("dbg", _P),
     ]
 
 
@@ -290,7 +291,8 @@ class Mlp2Step:
         self.grid = lib().dtfe_mlp2_step_grid(D, ks)
 
     def run(self, W1, b1, W2, b2, global_step, X, labels, lr: float, nsteps: int = 1, batch_idx=None,
-            rows_per_step: int = 0, atomic: bool = True, train: bool = True, out_offset: int = 0):
+            rows_per_step: int = 0, atomic: bool = True, train: bool = True, out_offset: int = 0,
+            remote: bool = True, dbg=None):
         assert nsteps + out_offset <= self.max_steps
         L = _Mlp2Launch()
         L.B, L.D, L.H, L.C, L.ks = self.B, self.D, self.H, self.C, self.ks
@@ -305,4 +307,6 @@ class Mlp2Step:
         L.acc_out = self.acc.data_ptr() + 4 * out_offset
         L.step_out = self.step.data_ptr() + 4 * out_offset
         L.lr, L.nsteps, L.atomic, L.train = lr, nsteps, int(atomic), int(train)
+        L.remote = int(remote)
+        L.dbg = _ptr(dbg)
         check(lib().dtfe_mlp2_step(ctypes.byref(L), _stream()), "dtfe_mlp2_step")

@@ -74,6 +74,10 @@ class PeerParamStore:
             raise RuntimeError(f"shard {k} is not mapped")
         return self._base[k]
 
+    def all_local(self) -> bool:
+        """True when every shard is memory this process allocated on its own GPU."""
+        return all(self._owned)
+
     def is_complete(self) -> bool:
         return all(b is not None for b in self._base)
 

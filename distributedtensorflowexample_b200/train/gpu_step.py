@@ -55,13 +55,16 @@ class DeviceDataset:
 
 class FusedMlp2Stepper:
     def __init__(self, spec: MLPSpec, batch: int, params: Sequence[torch.Tensor], global_step: torch.Tensor,
-                 lr: float, device, max_steps_per_launch: int = 1, atomic: bool = True, ks: int = 8):
+                 lr: float, device, max_steps_per_launch: int = 1, atomic: bool = True, ks: int = 8,
+                 remote: bool = True):
         if spec.num_layers != 2 or spec.param_dtype != "float32":
             raise ValueError("FusedMlp2Stepper handles 2-layer float32 models")
         D, H, C = spec.dims
         self.spec, self.batch, self.lr, self.atomic = spec, batch, lr, atomic
         self.W1, self.b1, self.W2, self.b2 = params
         self.global_step = global_step
+        self.remote = remote      # False only when every shard is in this GPU's own HBM
+        self.dbg = None
         self.k = ops.Mlp2Step(batch, D, H, C, device, max_steps=max_steps_per_launch, ks=ks)
         self.launches_per_call = 1
 
@@ -75,7 +78,7 @@ class FusedMlp2Stepper:
         """Results land in ``self.k.loss/acc/step[out_offset : out_offset+nsteps]`` (device)."""
         self.k.run(self.W1, self.b1, self.W2, self.b2, self.global_step, X, labels, self.lr, nsteps=nsteps,
                    batch_idx=batch_idx, rows_per_step=rows_per_step, atomic=self.atomic, train=train,
-                   out_offset=out_offset)
+                   out_offset=out_offset, remote=self.remote, dbg=self.dbg)
 
     @property
     def loss(self): return self.k.loss

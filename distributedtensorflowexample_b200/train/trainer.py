@@ -22,7 +22,7 @@ from .gpu_step import DeviceDataset, FusedMlp2Stepper, LayerwiseStepper
 class GpuTrainer:
     def __init__(self, spec: MLPSpec, batch: int, lr: float, params: Sequence[torch.Tensor],
                  global_step: torch.Tensor, device, steps_per_launch: int = 1, atomic: bool = True,
-                 engine: str = "auto"):
+                 engine: str = "auto", remote: bool = True):
         self.spec, self.batch, self.lr = spec, batch, lr
         self.device = torch.device(device)
         self.params = list(params)
@@ -34,7 +34,7 @@ class GpuTrainer:
         self.launch_count = 0
         if engine == "fused":
             self.fused = FusedMlp2Stepper(spec, batch, self.params, global_step, lr, self.device,
-                                          max_steps_per_launch=self.steps_per_launch, atomic=atomic)
+                                          max_steps_per_launch=self.steps_per_launch, atomic=atomic, remote=remote)
             self.layer = LayerwiseStepper(spec, batch, self.params, global_step, lr, self.device, atomic=atomic)
         elif engine == "layerwise":
             self.fused = None

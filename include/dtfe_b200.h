@@ -1,0 +1,118 @@
+/* C ABI of libdtfe_cuda.so - the sm_100a kernels of the B200 parameter-server framework.
+ *
+ * Conventions
+ *   - every function returns 0 on success; otherwise dtfe_last_error() (thread-local) explains;
+ *   - `stream` is a cudaStream_t passed as void*; all work is enqueued on it, nothing synchronises;
+ *   - weight matrices use the reference's tf.layers.dense layout [in, out], row-major;
+ *   - "shard" pointers may be peer-mapped HBM of another GPU (see dtfe_ipc_*): kernels read them
+ *     with L1-bypassing loads and update them with red.add at .sys scope;
+ *   - file:line citations refer to /root/reference (rubythonode/DistributedTensorFlowExample).
+ */
+#ifndef DTFE_B200_H_
+#define DTFE_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- runtime ------------------------------------------------------------------------------ */
+const char* dtfe_last_error(void);
+int dtfe_abi_version(void);
+int dtfe_device_count(int* n);
+/* out[6] = {cc major, cc minor, SM count, max opt-in smem/CTA, L2 bytes, cooperative launch} */
+int dtfe_device_info(int dev, int* out);
+
+/* Parameter shard = what a ps task owns (reference main.py:67-68: tf.train.Server for job 'ps';
+ * TF1 keeps the variables in that process's host RAM).  Here: zeroed cudaMalloc memory on the
+ * current device, exportable to other processes on the box as a 64-byte CUDA IPC handle. */
+int dtfe_shard_alloc(size_t bytes, void** out);
+int dtfe_shard_free(void* p);
+int dtfe_ipc_export(void* p, void* handle64);
+int dtfe_ipc_open(const void* handle64, void** out);
+int dtfe_ipc_close(void* p);
+int dtfe_enable_peer(int dev, int peer);
+
+/* Benchmark hygiene: overwrite `bytes` (> L2 size) so the next kernel starts with a cold L2. */
+int dtfe_l2_flush(void* buf, size_t bytes, void* stream);
+
+/* global_step += inc with a system-scope atomic; *observed = pre-increment value
+ * (reference worker.py:29-32 counter_op, :136 fetch of global_step, :141 sess.run(counter_op)). */
+int dtfe_global_step_add(int* global_step, int inc, int* observed_or_null, void* stream);
+
+/* ---- dense layers, fp32 SIMT path ---------------------------------------------------------- */
+/* C[M,N] = act(A[M,K] . W[K,N] + bias[N]); act 0 = identity, 1 = sigmoid
+ * (reference worker.py:50-53 tf.layers.dense; shard_reads=1 when W/bias are shard memory = fused pull,
+ *  worker.py:81-85). */
+int dtfe_dense_fwd_f32(const float* A, long lda, const float* W, long ldw, const float* bias, float* C,
+                       long ldc, int M, int N, int K, int act, int shard_reads, void* stream);
+/* dX[M,K] = (dY[M,N] . W[K,N]^T) * Hprev*(1-Hprev)   (MatMul grad + SigmoidGrad of tf.gradients,
+ * reference worker.py:72-73) */
+int dtfe_dense_bwd_dx_f32(const float* dY, long lddy, const float* W, long ldw, const float* Hprev, long ldh,
+                          float* dX, long lddx, int M, int N, int K, int act, int shard_reads, void* stream);
+/* W[K,N] += alpha * X[M,K]^T . dY[M,N]  - gradient push fused with the SGD apply
+ * (reference worker.py:75-79 apply_gradients on the global variables).  atomic=1: red.add (lossless
+ * Hogwild); atomic=0: unlocked read-modify-write like TF1 use_locking=False.  W may be NULL and/or
+ * G non-NULL to get the raw gradient (sync mode). */
+int dtfe_dense_bwd_dw_push_f32(const float* X, long ldx, const float* dY, long lddy, float* W, long ldw,
+                               float* G, long ldg, int M, int N, int K, float alpha, int atomic, void* stream);
+/* b[N] += alpha * sum_m dY[m,:]   (TF1 BiasAddGrad + ApplyGradientDescent) */
+int dtfe_bias_grad_push_f32(const float* dY, long lddy, int M, int N, float* b, float* gout, float alpha,
+                            int atomic, void* stream);
+
+/* ---- loss / metrics ------------------------------------------------------------------------ */
+/* Softmax cross-entropy forward+backward with per-row loss and argmax-correct flags
+ * (reference worker.py:59-68 loss, :87-90 accuracy).  Exactly one of label_ids (int32 [M]) and
+ * label_dense (float [M,C], one-hot or soft) is non-NULL.  dZ = (softmax - y) * scale. */
+int dtfe_softmax_xent_f32(const float* logits, long ldz, const int* label_ids, const float* label_dense,
+                          long ldl, int M, int C, float scale, float* dZ, long lddz, float* rowloss,
+                          int* rowcorrect, void* stream);
+/* Deterministic means: *out_loss = mean(rowloss), *out_acc = mean(rowcorrect), *out_count = sum. */
+int dtfe_mean_loss_acc(const float* rowloss, const int* rowcorrect, int M, float* out_loss, float* out_acc,
+                       int* out_count, void* stream);
+
+/* ---- flat push / pull / optimizers over peer memory ------------------------------------------ */
+/* shard[i] += alpha*grad[i]: the asynchronous push+apply as one kernel (reference worker.py:79). */
+int dtfe_push_sgd_f32(float* shard, const float* grad, size_t n, float alpha, int atomic, void* stream);
+int dtfe_push_sgd_bf16(void* shard_bf16, const float* grad, size_t n, float alpha, void* stream);
+/* dst[i] = shard[i] with L1-bypassing loads: the stand-alone pull (reference worker.py:81-85 sync_op). */
+int dtfe_pull_f32(float* dst, const float* shard, size_t n, void* stream);
+/* Adam at the owner: consumes and clears the accumulation slot workers pushed into
+ * (no counterpart in the reference, which only has GradientDescentOptimizer, worker.py:71). */
+int dtfe_adam_apply_f32(float* param, float* m, float* v, float* slot, size_t n, float lr_t, float beta1,
+                        float beta2, float eps, float grad_scale, void* stream);
+/* Synchronous SGD: every rank reduces ITS slice [begin,end) of all ranks' gradient buffers out of
+ * peer memory and applies it in place; flag barriers in peer memory on entry and exit.  One rank per
+ * GPU (the kernel spins on peers).  No counterpart in the reference (async only); semantic model is
+ * TF1 SyncReplicasOptimizer. */
+int dtfe_sync_rs_apply_f32(const float* const* grads, unsigned* const* flags, int rank, int world,
+                           float* param, size_t begin, size_t end, size_t param_off, float alpha,
+                           unsigned epoch, unsigned* local_sync, int* global_step_or_null, void* stream);
+int dtfe_sync_max_ranks(void);
+
+/* ---- the whole reference training step in one cooperative kernel ------------------------------- */
+/* pull -> fwd -> xent/accuracy -> bwd -> push+apply -> global_step for nsteps consecutive steps
+ * (reference worker.py:129-141, model worker.py:46-57).  Limits: B<=128, H<=128, C<=16, D/ks<=148. */
+typedef struct dtfe_mlp2_launch {
+  int B, D, H, C, ks;                 /* batch, inputs, hidden, classes, K-slice per CTA (8|16) */
+  float *W1, *b1, *W2, *b2;           /* shard memory: [D,H], [H], [H,C], [C] */
+  int* global_step;                   /* shard memory, int32 */
+  const float* X; long ldx;           /* dataset / batch rows */
+  const int* labels;                  /* class ids, indexed like X rows */
+  const int* batch_idx;               /* [nsteps*B] row indices or NULL */
+  long rows_per_step;                 /* batch_idx==NULL: row = step*rows_per_step + r */
+  float* workspace;                   /* dtfe_mlp2_step_workspace_words() 4-byte words, zeroed once */
+  float* loss_out; float* acc_out; int* step_out;   /* [nsteps] each */
+  float lr; int nsteps; int atomic; int train; int remote;
+  long long* dbg;                     /* NULL, or [nsteps][grid][8] globaltimer stamps */
+} dtfe_mlp2_launch;
+int dtfe_mlp2_step_grid(int D, int ks);
+size_t dtfe_mlp2_step_workspace_words(int B, int D, int H, int C, int ks);
+int dtfe_mlp2_step(const dtfe_mlp2_launch* launch, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DTFE_B200_H_ */

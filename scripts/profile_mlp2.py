@@ -18,7 +18,7 @@ names = [v.name for v in model.global_trainable]
 x, y = synthetic_arrays(55000, seed=0)
 ds = DeviceDataset(x, y.astype(np.int32), dev, seed=0)
 tr = GpuTrainer(spec, 100, 0.001, [store.tensor(n) for n in names], store.tensor("global/global_step"), dev,
-                steps_per_launch=nsteps)
+                steps_per_launch=nsteps, remote=('--remote' in sys.argv))
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 for i in range(launches):
     idx = ds.next_indices(100, nsteps)
@@ -27,3 +27,19 @@ for i in range(launches):
     e1.record()
     torch.cuda.synchronize()
     print(f"launch {i}: {e0.elapsed_time(e1) * 1e3 / nsteps:.2f} us/step")
+
+if "--stamps" in sys.argv:
+    G = tr.fused.k.grid
+    dbg = torch.zeros(nsteps * G * 8, dtype=torch.int64, device=dev)
+    tr.fused.dbg = dbg
+    idx = ds.next_indices(100, nsteps)
+    tr.run_indices(ds, idx, nsteps)
+    torch.cuda.synchronize()
+    t = dbg.view(nsteps, G, 8).double().cpu().numpy()
+    names = ["A:load+compute+store", "barrier1", "B:reduce..dA", "barrier2", "C:dW1+push", "fence", "done-atomic"]
+    s0 = t[2:]                       # skip first steps
+    for i, n in enumerate(names):
+        d = (s0[:, :, i + 1] - s0[:, :, i]) / 1e3
+        print(f"{n:24s} mean {d.mean():6.2f} us  max-over-CTAs {d.max(axis=1).mean():6.2f} us  min {d.min(axis=1).mean():6.2f}")
+    step = (s0[1:, :, 0] - s0[:-1, :, 0]) / 1e3
+    print(f"step period             {step.mean():6.2f} us")
