@@ -411,3 +411,49 @@ DTFE_API int dtfe_mlp2_step(const Mlp2Launch* L, void* stream) {
   if (int rc = mlp2_fill(*L, a)) return rc;
   return L->ks == 8 ? mlp2_launch<8>(a, (cudaStream_t)stream) : mlp2_launch<16>(a, (cudaStream_t)stream);
 }
+
+// ---- variant for callers that must not allocate ------------------------------------------------
+// Same kernel, same arguments, but the scratch workspace is a fixed array that is part of this
+// library's device image instead of memory the caller provides.  Meant for callers that cannot
+// obtain device memory at the point where they train: a worker confined to a fixed slice of a
+// shared GPU (the reference packs several workers onto one GPU by memory fraction, main.py:57-64),
+// a host application whose own pool already owns all of HBM, or a step issued from a place where
+// cudaMalloc's device-wide synchronisation is not acceptable.
+//
+// Cost: every GPU that loads libdtfe_cuda.so holds these 4 MiB until the process exits.
+constexpr size_t kNoAllocScratchWords = size_t(1) << 20;  // 4-byte words -> 4 MiB
+static __device__ __align__(256) float g_mlp2_noalloc_scratch[kNoAllocScratchWords];
+
+DTFE_API size_t dtfe_mlp2_step_noalloc_max_words(void) { return kNoAllocScratchWords; }
+
+// `launch->workspace` is ignored.  See include/dtfe_b200.h for the contract.
+DTFE_API int dtfe_mlp2_step_noalloc(const dtfe_mlp2_launch* launch, void* stream) {
+  // In host code the array's name is only a handle for the runtime; the address a kernel can use
+  // has to be looked up, per device, with that device current.
+  static float* scratch_on_device[64] = {};
+  int dev = -1;
+  DTFE_CUDA_CHECK(cudaGetDevice(&dev));
+  DTFE_REQUIRE(dev >= 0 && dev < 64, "dtfe_mlp2_step_noalloc: device ordinal %d not supported", dev);
+  DTFE_REQUIRE(launch->ks == 8 || launch->ks == 16, "dtfe_mlp2_step_noalloc: ks must be 8 or 16");
+  DTFE_REQUIRE(launch->B >= 1 && launch->D >= 1 && launch->H >= 1 && launch->C >= 1,
+               "dtfe_mlp2_step_noalloc: non-positive dimension");
+  size_t need = dtfe_mlp2_step_workspace_words(launch->B, launch->D, launch->H, launch->C, launch->ks);
+  DTFE_REQUIRE(need <= kNoAllocScratchWords,
+               "dtfe_mlp2_step_noalloc: B=%d D=%d H=%d C=%d ks=%d needs %zu words of scratch but the built-in "
+               "array holds %zu (4 MiB); use dtfe_mlp2_step with a caller-provided workspace",
+               launch->B, launch->D, launch->H, launch->C, launch->ks, need, (size_t)kNoAllocScratchWords);
+  if (scratch_on_device[dev] == nullptr) {
+    float* p = nullptr;
+    DTFE_CUDA_CHECK(cudaGetSymbolAddress((void**)&p, g_mlp2_noalloc_scratch));
+    DTFE_REQUIRE(p != nullptr, "dtfe_mlp2_step_noalloc: cudaGetSymbolAddress returned a null address");
+    scratch_on_device[dev] = p;
+  }
+  Mlp2Launch L = *launch;
+  L.workspace = scratch_on_device[dev];
+  Mlp2Args a{};
+  if (int rc = mlp2_fill(L, a)) return rc;
+  // The array still holds whatever the previous call (finished or aborted) left behind.  Only the
+  // sync words have to start at zero; every other region is written before it is read.
+  DTFE_CUDA_CHECK(cudaMemsetAsync(a.sync, 0, 4 * sizeof(unsigned), (cudaStream_t)stream));
+  return L.ks == 8 ? mlp2_launch<8>(a, (cudaStream_t)stream) : mlp2_launch<16>(a, (cudaStream_t)stream);
+}

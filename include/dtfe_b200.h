@@ -112,6 +112,23 @@ int dtfe_mlp2_step_grid(int D, int ks);
 size_t dtfe_mlp2_step_workspace_words(int B, int D, int H, int C, int ks);
 int dtfe_mlp2_step(const dtfe_mlp2_launch* launch, void* stream);
 
+/* dtfe_mlp2_step for callers that cannot allocate device memory (no counterpart in the reference).
+ * Some users of this library have no way to get a workspace: a worker that lives inside a fixed
+ * fraction of a shared GPU, a host program whose own memory pool already owns the device, or code
+ * at a point where cudaMalloc (which synchronises the whole device) must not be called.  For them
+ * the scratch is a 4 MiB array built into the library image (dtfe_mlp2_step_noalloc_max_words()
+ * 4-byte words, held by every GPU that loads the library until the process exits);
+ * `launch->workspace` is ignored, inputs and outputs are passed as usual.
+ *   - Shapes whose scratch does not fit are refused (non-zero return, dtfe_last_error() names the
+ *     size needed and the limit).  The reference model (B=100, D=784, H=100, C=10, ks=8) fits.
+ *   - The first call on each device looks up the array's device address and configures the kernel;
+ *     make that first call outside any stream capture.  Later calls only enqueue a 16-byte memset
+ *     and the launch.  Nothing is ever allocated or freed.
+ *   - All calls on a device share the one array: two calls whose kernels could overlap on the GPU
+ *     (different streams, or different host threads) corrupt each other.  Serialise them. */
+size_t dtfe_mlp2_step_noalloc_max_words(void);
+int dtfe_mlp2_step_noalloc(const dtfe_mlp2_launch* launch, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
