@@ -1,0 +1,277 @@
+"""CPU plumbing configuration: 1..P ps processes + W workers over torch.distributed/gloo
+(BASELINE.json config 1; reference run_single_gpu.sh with ``allow_soft_placement`` and no GPU,
+worker.py:120 - SURVEY 4.2, 5.8 last row).
+
+This reproduces the reference's *message pattern* literally: per step a worker does a pull
+(4 tensors ps->worker), a push (4 gradient tensors worker->ps, applied ON the ps with
+``var -= lr*grad``, no locking across workers), a read of global_step, and a separate increment
+(reference worker.py:131,135-137,141).  The ps is a passive server loop, like TF1's worker service.
+
+Wire protocol (all tensors CPU): a request is an int64[4] header {op, a0, a1, a2} sent to the ps
+rank, optionally followed by a payload; the ps answers on the same pair.  Each ps task owns the
+variables the placement function gave it, stored as one flat float32 vector + int32 global_step.
+"""
+from __future__ import annotations
+
+import functools
+import signal
+import struct
+import threading
+import time
+from typing import Dict, List, Optional, Sequence
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from ..cluster import ClusterSpec
+from ..variables import VariableDef
+from .client import ParamClient
+
+OP_PULL, OP_PUSH, OP_STEP_READ, OP_STEP_INC, OP_ASSIGN, OP_IS_READY, OP_SET_READY, OP_SHUTDOWN, OP_STOP_REQ, \
+    OP_STOP_QUERY, OP_ALLOC = range(1, 12)
+
+
+_SHUTDOWN_SIGNALS = {signal.SIGHUP, signal.SIGINT, signal.SIGTERM}
+
+
+def _float_to_bits(x: float) -> int:
+    return struct.unpack("<q", struct.pack("<d", x))[0]
+
+
+def _bits_to_float(b: int) -> float:
+    return struct.unpack("<d", struct.pack("<q", b))[0]
+
+
+class _TaskLayout:
+    """Flat layout of the float variables a ps task owns (+ whether it owns global_step)."""
+
+    def __init__(self, variables: Sequence[VariableDef], task: int):
+        self.task = task
+        self.float_vars: List[VariableDef] = []
+        self.offsets: Dict[str, int] = {}
+        self.has_step = False
+        n = 0
+        for v in variables:
+            if v.device.job != "ps" or v.device.task != task:
+                continue
+            if v.dtype == "int32":
+                self.has_step = True
+                continue
+            self.float_vars.append(v)
+            self.offsets[v.name] = n
+            n += v.numel
+        self.numel = n
+
+
+def init_gloo(cluster: ClusterSpec, job: str, task: int, timeout_s: float = 600.0) -> int:
+    """Join the gloo group; rank = ps tasks first, then workers.  Rendezvous on ps:0's port."""
+    import datetime
+    host, port = cluster.task_host_port("ps", 0)
+    rank = cluster.global_rank(job, task)
+    if not dist.is_initialized():
+        dist.init_process_group("gloo", init_method=f"tcp://{host}:{port}", rank=rank,
+                                world_size=cluster.world_size, timeout=datetime.timedelta(seconds=timeout_s))
+    return rank
+
+
+class GlooParamServer:
+    """The ps role: owns state, serves requests until told to shut down (reference main.py:66-70)."""
+
+    def __init__(self, task: int, num_workers: int, variables: Optional[Sequence[VariableDef]] = None):
+        # Like a TF1 ps, the server knows nothing about the model until a worker (the chief) tells it
+        # how much state to hold (OP_ALLOC); passing `variables` pre-sizes it (tests).
+        self.task = task
+        self.numel = _TaskLayout(variables, task).numel if variables is not None else 0
+        self.flat = torch.zeros(max(self.numel, 1), dtype=torch.float32)
+        self.step = torch.zeros(1, dtype=torch.int64)
+        self.ready = False
+        self.stop_requested = False
+        self.num_workers = num_workers
+        self.requests_served = 0
+
+    def serve_forever(self) -> None:
+        hdr = torch.zeros(4, dtype=torch.int64)
+        done_workers = 0
+        while True:
+            src = dist.recv(hdr)
+            op, a0 = int(hdr[0]), int(hdr[1])
+            n = self.numel
+            self.requests_served += 1
+            if op == OP_ALLOC:
+                if a0 != self.numel:
+                    self.numel = a0
+                    self.flat = torch.zeros(max(a0, 1), dtype=torch.float32)
+            elif op == OP_PULL:
+                dist.send(self.flat, dst=src)
+            elif op == OP_PUSH:
+                buf = torch.empty(max(n, 1), dtype=torch.float32)
+                dist.recv(buf, src=src)
+                # ApplyGradientDescent on the ps: var -= lr * grad (TF1 T10); unsynchronised across workers
+                self.flat.add_(buf, alpha=-_bits_to_float(a0))
+            elif op == OP_STEP_READ:
+                dist.send(self.step, dst=src)
+            elif op == OP_STEP_INC:
+                old = self.step.clone()
+                self.step += a0
+                dist.send(old, dst=src)
+            elif op == OP_ASSIGN:
+                buf = torch.empty(max(n, 1) + 1, dtype=torch.float32)
+                dist.recv(buf, src=src)
+                self.flat.copy_(buf[:max(n, 1)])
+                if a0 >= 0:
+                    self.step[0] = a0
+            elif op == OP_IS_READY:
+                dist.send(torch.tensor([1 if self.ready else 0], dtype=torch.int64), dst=src)
+            elif op == OP_SET_READY:
+                self.ready = True
+            elif op == OP_STOP_REQ:
+                self.stop_requested = True
+            elif op == OP_STOP_QUERY:
+                dist.send(torch.tensor([1 if self.stop_requested else 0], dtype=torch.int64), dst=src)
+            elif op == OP_SHUTDOWN:
+                done_workers += 1
+                if a0 == 1 or done_workers >= self.num_workers:
+                    return
+            else:
+                raise RuntimeError(f"ps: unknown op {op} from rank {src}")
+
+
+def _locked(fn):
+    # One request/response exchange at a time per client: the chief's checkpoint and step-counter
+    # threads share the process group with the training thread.
+    # The shutdown signals (which raise SystemExit from their handler, reference main.py:51-52) are held
+    # back for the duration of an exchange so that it is never abandoned half-way, which would leave
+    # the request/response streams of this worker and the ps out of step.
+    @functools.wraps(fn)
+    def wrapper(self, *a, **kw):
+        in_main = threading.current_thread() is threading.main_thread()
+        old = signal.pthread_sigmask(signal.SIG_BLOCK, _SHUTDOWN_SIGNALS) if in_main else None
+        try:
+            with self._lock:
+                return fn(self, *a, **kw)
+        finally:
+            if old is not None:
+                signal.pthread_sigmask(signal.SIG_SETMASK, old)
+    return wrapper
+
+
+class GlooParamClient(ParamClient):
+    def __init__(self, variables: Sequence[VariableDef], cluster: ClusterSpec):
+        self._lock = threading.RLock()
+        self.variables = [v for v in variables if v.device.job == "ps"]
+        self.cluster = cluster
+        self.num_ps = cluster.num_tasks("ps")
+        self.layouts = [_TaskLayout(self.variables, k) for k in range(self.num_ps)]
+        self.step_task = next((k for k, l in enumerate(self.layouts) if l.has_step), 0)
+        self._hdr = torch.zeros(4, dtype=torch.int64)
+        self.messages = 0
+
+    def _rank(self, k: int) -> int:
+        return self.cluster.global_rank("ps", k)
+
+    def _send_hdr(self, k: int, op: int, a0: int = 0) -> None:
+        self._hdr[0], self._hdr[1] = op, a0
+        dist.send(self._hdr, dst=self._rank(k))
+        self.messages += 1
+
+    # ---- data plane ---------------------------------------------------------------------------
+    @_locked
+    def pull(self) -> Dict[str, torch.Tensor]:
+        """reference ``sync_op`` (worker.py:81-85,131): fetch every trainable global variable."""
+        out: Dict[str, torch.Tensor] = {}
+        for k, lay in enumerate(self.layouts):
+            if lay.numel == 0:
+                continue
+            self._send_hdr(k, OP_PULL)
+            buf = torch.empty(lay.numel, dtype=torch.float32)
+            dist.recv(buf, src=self._rank(k))
+            for v in lay.float_vars:
+                o = lay.offsets[v.name]
+                out[v.name] = buf[o:o + v.numel].view(*v.shape)
+        return out
+
+    @_locked
+    def push(self, grads: Dict[str, torch.Tensor], lr: float) -> None:
+        """reference ``train_op`` apply half (worker.py:75-79): send gradients, ps applies."""
+        for k, lay in enumerate(self.layouts):
+            if lay.numel == 0:
+                continue
+            buf = torch.empty(lay.numel, dtype=torch.float32)
+            for v in lay.float_vars:
+                o = lay.offsets[v.name]
+                buf[o:o + v.numel] = grads[v.name].reshape(-1)
+            self._send_hdr(k, OP_PUSH, _float_to_bits(lr))
+            dist.send(buf, dst=self._rank(k))
+
+    @_locked
+    def read_step(self) -> int:
+        self._send_hdr(self.step_task, OP_STEP_READ)
+        t = torch.zeros(1, dtype=torch.int64)
+        dist.recv(t, src=self._rank(self.step_task))
+        return int(t.item())
+
+    @_locked
+    def increment_step(self, inc: int = 1) -> int:
+        """reference ``counter_op`` (worker.py:32,141); returns the pre-increment value."""
+        self._send_hdr(self.step_task, OP_STEP_INC, inc)
+        t = torch.zeros(1, dtype=torch.int64)
+        dist.recv(t, src=self._rank(self.step_task))
+        return int(t.item())
+
+    # ---- control plane --------------------------------------------------------------------------
+    def initialize(self, rng):
+        vals = {v.name: v.initializer(v.shape, v.dtype, rng) for v in self.variables}
+        self.assign_many(vals)
+
+    @_locked
+    def assign_many(self, values):
+        step = values.get(self.global_step_name)
+        for k, lay in enumerate(self.layouts):
+            self._send_hdr(k, OP_ALLOC, lay.numel)
+            buf = torch.zeros(max(lay.numel, 1) + 1, dtype=torch.float32)
+            for v in lay.float_vars:
+                o = lay.offsets[v.name]
+                buf[o:o + v.numel] = torch.from_numpy(np.ascontiguousarray(values[v.name], dtype=np.float32).reshape(-1))
+            s = int(np.asarray(step).reshape(())) if (lay.has_step and step is not None) else -1
+            self._send_hdr(k, OP_ASSIGN, s)
+            dist.send(buf, dst=self._rank(k))
+
+    @_locked
+    def snapshot(self, names=None):
+        pulled = self.pull()
+        out = {n: t.numpy().copy() for n, t in pulled.items()}
+        out[self.global_step_name] = np.array(self.read_step(), dtype=np.int32)
+        return {n: out[n] for n in names} if names is not None else out
+
+    @_locked
+    def mark_ready(self):
+        for k in range(self.num_ps):
+            self._send_hdr(k, OP_SET_READY)
+
+    @_locked
+    def report_uninitialized_variables(self):
+        for k, lay in enumerate(self.layouts):
+            self._send_hdr(k, OP_IS_READY)
+            t = torch.zeros(1, dtype=torch.int64)
+            dist.recv(t, src=self._rank(k))
+            if int(t.item()) == 0:
+                return [v.name for v in self.variables]
+        return []
+
+    @_locked
+    def request_stop(self):
+        self._send_hdr(0, OP_STOP_REQ)
+
+    @_locked
+    def stop_requested(self) -> bool:
+        self._send_hdr(0, OP_STOP_QUERY)
+        t = torch.zeros(1, dtype=torch.int64)
+        dist.recv(t, src=self._rank(0))
+        return bool(t.item())
+
+    @_locked
+    def shutdown_servers(self, force: bool = False) -> None:
+        """Tell every ps this worker is done (the ps exits once all workers said so)."""
+        for k in range(self.num_ps):
+            self._send_hdr(k, OP_SHUTDOWN, 1 if force else 0)

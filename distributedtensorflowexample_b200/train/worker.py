@@ -1,0 +1,202 @@
+"""The worker: replicated-model construction and the training loop (reference worker.py:7-159;
+SURVEY C8-C17, 3.3, 3.4).
+
+``Worker(job_name, task_index, server)`` mirrors the reference constructor; ``learn(dataset)`` is the
+same loop: pull -> batch -> forward/backward/push -> summary -> counter -> log/eval cadence ->
+``training_steps`` bound, under a Supervisor-managed session.
+
+Observable behaviour kept from the reference:
+  * ``step`` is the GLOBAL step observed during the train op, pre-increment (worker.py:136);
+  * ``step: {}\\t| cost: {}\\t| speed: {}step/sec`` when ``step % 100 == 0 and step != 0`` (speed =
+    global steps/sec as seen by this worker, first interval from session start, worker.py:143-148);
+  * ``test accuracy: {}`` on the full test set when ``step % 10000 == 0`` - including step 0
+    (worker.py:150-154);
+  * a loss/accuracy summary per step, keyed by the observed global step, in ``<logdir>_<task>``
+    (worker.py:96,139);
+  * stop when ``step >= training_steps`` (a bound on the global step, worker.py:158-159).
+On the GPU path ``steps_per_launch > 1`` fuses several steps into one kernel launch; the cadence
+rules are then evaluated for every step of the launch after it returns.
+"""
+from __future__ import annotations
+
+import os
+import sys
+import time
+from typing import Optional
+
+import numpy as np
+
+from ..flags import FLAGS
+from ..models.mlp import spec_from_flags
+from ..utils.checkpoint import FastSaver
+from ..utils.events import FileWriter, training_summary
+from .replica import build_replicated_model
+from .supervisor import Supervisor
+
+
+def _parse_fault(text: str):
+    """'kill_worker:1@50,delay_push:0.01' -> {'kill_worker': (1, 50), 'delay_push': 0.01}"""
+    out = {}
+    for part in (text or "").split(","):
+        part = part.strip()
+        if not part:
+            continue
+        name, _, arg = part.partition(":")
+        if name == "kill_worker":
+            task, _, step = arg.partition("@")
+            out[name] = (int(task), int(step))
+        elif name == "delay_push":
+            out[name] = float(arg)
+        else:
+            raise ValueError(f"unknown fault {part!r}")
+    return out
+
+
+class Worker:
+    def __init__(self, job_name: str, task_index: int, server, flags=FLAGS):
+        self.job_name, self.task_index, self.server, self.flags = job_name, task_index, server, flags
+        self.is_chief = task_index == 0
+        self.faults = _parse_fault(flags.fault)
+        seed = None if flags.seed < 0 else flags.seed
+        self.rng = np.random.default_rng(seed)
+        self.spec = spec_from_flags(flags.hidden, dtype=flags.dtype if server.backend == "cuda" else "float32")
+        # C8: two copies of the net, global on the ps job, local on this worker
+        self.model = build_replicated_model(self.spec, job_name, task_index, num_ps=server.num_ps,
+                                            ps_strategy=flags.ps_strategy)
+        self.global_step = self.model.global_step
+        if server.backend == "gloo":
+            self._build_cpu()
+        else:
+            self._build_cuda()
+        self.build_summary_op()
+        self.build_saver()
+
+    # ---- construction -------------------------------------------------------------------------
+    def _build_cpu(self) -> None:
+        from ..parallel.gloo_ps import GlooParamClient
+        from .cpu_step import CpuStepEngine
+        self.client = GlooParamClient(self.model.global_all, self.server.cluster)
+        self.engine = CpuStepEngine(self.model, self.client, self.flags.learning_rate,
+                                    push_delay_s=self.faults.get("delay_push", 0.0))
+        self.trainer = None
+
+    def _build_cuda(self) -> None:
+        import torch
+        from ..parallel.client import PeerParamClient
+        from ..parallel.ps import PeerParamStore
+        from .trainer import GpuTrainer
+        dev = torch.device("cuda", self.server.config.device_index)
+        store = PeerParamStore(self.model.global_all, self.server.num_ps, dev)
+        kv = self.server.store
+        if self.is_chief:   # the chief tells each ps how much state to host
+            for k in range(self.server.num_ps):
+                kv.set(f"shard/{k}/bytes", str(store.layout.shard_bytes[k]))
+        handles = {k: kv.get(f"shard/{k}/handle") for k in range(self.server.num_ps)}   # blocks until exported
+        store.open_handles(handles)
+        self.store = store
+        self.client = PeerParamClient(store)
+        names = [v.name for v in self.model.global_trainable]
+        self.trainer = GpuTrainer(self.spec, self.flags.batch_size, self.flags.learning_rate,
+                                  [store.tensor(n) for n in names], store.tensor(self.global_step.name), dev,
+                                  steps_per_launch=self.flags.steps_per_launch,
+                                  atomic=not self.flags.unlocked_apply, remote=True)
+        self.engine = None
+
+    def build_summary_op(self) -> None:
+        """reference worker.py:87-96: the writer (and its event file) exists from construction on."""
+        self.summary_writer = FileWriter(self.flags.logdir + "_%d" % self.task_index)
+
+    def build_saver(self) -> None:
+        """reference worker.py:102-103: FastSaver over the 4 global weights + global_step."""
+        self.saver = FastSaver([v.name for v in self.model.global_all])
+
+    def global_init_op(self) -> None:
+        self.client.initialize(self.rng)
+
+    def local_init_op(self) -> None:
+        if self.engine is not None:
+            self.engine.local_init_op(self.rng)
+
+    def graph_text(self) -> str:
+        lines = [f"# between-graph replica of worker {self.task_index}; model dims {list(self.spec.dims)}"]
+        for v in self.model.store.all_variables():
+            lines.append(f'node {{ name: "{v.name}" op: "VariableV2" device: "{v.device}" '
+                         f'attr {{ shape: {list(v.shape)} dtype: "{v.dtype}" trainable: {str(v.trainable).lower()} }} }}')
+        return "\n".join(lines) + "\n"
+
+    # ---- the loop -------------------------------------------------------------------------------
+    def learn(self, dataset) -> int:
+        f = self.flags
+        sv = Supervisor(is_chief=self.is_chief, logdir=f.logdir, saver=self.saver, client=self.client,
+                        summary_writer=self.summary_writer, save_model_secs=f.save_model_secs,
+                        save_summaries_secs=f.save_summaries_secs, init_op=self.global_init_op,
+                        local_init_op=self.local_init_op, recovery_wait_secs=f.recovery_wait_secs,
+                        graph_text=self.graph_text())
+        self.sv = sv
+        last_step = 0
+        with sv.managed_session() as sess:
+            if sv.restored_from:
+                print(f"restored from {sv.restored_from}", flush=True)
+            self._begin_time = time.time()
+            self._start_time = time.time()
+            self._start_step = 0
+            run = self._loop_cpu if self.trainer is None else self._loop_cuda
+            last_step = run(sv, dataset)
+        self.summary_writer.close()
+        return last_step
+
+    def _after_step(self, step: int, cost: float, acc: float, eval_fn) -> bool:
+        """Summary + cadence rules of reference worker.py:139-159. Returns True to stop."""
+        f = self.flags
+        self.summary_writer.add_summary(training_summary(cost, acc), step)
+        if "kill_worker" in self.faults and self.faults["kill_worker"][0] == self.task_index \
+                and step >= self.faults["kill_worker"][1]:
+            print(f"fault injection: worker {self.task_index} dies at step {step}", flush=True)
+            self.summary_writer.flush()
+            os._exit(17)
+        if step % f.log_every == 0 and step != 0:
+            elapsed = time.time() - self._start_time
+            print("step: {}\t| cost: {}\t| speed: {}step/sec".format(
+                step, cost, float((step - self._start_step) / max(elapsed, 1e-9))), flush=True)
+            self._start_time = time.time()
+            self._start_step = step
+        if step % f.eval_every == 0:
+            print("test accuracy: {}".format(eval_fn()), flush=True)
+        return step >= f.training_steps
+
+    def _loop_cpu(self, sv: Supervisor, dataset) -> int:
+        eng, f = self.engine, self.flags
+        step = 0
+        while not sv.should_stop():
+            eng.sync_op()                                                        # reference :131
+            batch_x, batch_y = dataset.train.next_batch(f.batch_size)           # :133
+            cost, acc, step = eng.train_op(batch_x, batch_y)                     # :135-137
+            eng.counter_op()                                                     # :141 (summary :139 is in _after_step)
+            if self._after_step(step, cost, acc, lambda: eng.accuracy(dataset.test.images, dataset.test.labels)):
+                break
+        return step
+
+    def _loop_cuda(self, sv: Supervisor, dataset) -> int:
+        import torch
+        from .gpu_step import DeviceDataset
+        f, tr = self.flags, self.trainer
+        dev = tr.device
+        seed = None if f.seed < 0 else f.seed + 1000 * self.task_index
+        train = DeviceDataset(dataset.train.images, dataset.train.label_ids, dev, seed=seed)
+        test_x = torch.as_tensor(dataset.test.images, dtype=torch.float32).to(dev)
+        test_y = torch.as_tensor(dataset.test.label_ids, dtype=torch.int32).to(dev)
+        eval_fn = lambda: tr.evaluate(test_x, test_y)
+        n = max(1, f.steps_per_launch)
+        step = 0
+        while not sv.should_stop():
+            loss_d, acc_d, step_d = tr.train_device_steps(train, n)
+            loss, acc, steps = loss_d.tolist(), acc_d.tolist(), step_d.tolist()   # one sync per launch
+            stop = False
+            for l, a, s in zip(loss, acc, steps):
+                step = s
+                if self._after_step(s, l, a, eval_fn):
+                    stop = True
+                    break
+            if stop:
+                break
+        return step

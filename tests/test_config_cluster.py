@@ -1,0 +1,155 @@
+"""CPU unit tests: flags, cluster spec, placement, variable scopes, memory fraction, launchers."""
+import math
+import os
+import subprocess
+import sys
+
+import pytest
+
+from distributedtensorflowexample_b200 import flags as F
+from distributedtensorflowexample_b200.cluster import ClusterSpec, cluster_spec
+from distributedtensorflowexample_b200.placement import (DeviceSpec, GreedyLoadBalancingStrategy, OpInfo,
+                                                         replica_device_setter)
+from distributedtensorflowexample_b200.utils import memory
+from distributedtensorflowexample_b200.variables import VariableStore, get_vars, random_normal_initializer
+
+
+def _flags():
+    fv = F.FlagValues()
+    F.define_reference_flags(fv)
+    F.define_framework_flags(fv)
+    return fv
+
+
+def test_reference_flag_defaults():
+    fv = _flags()
+    fv.parse([])
+    assert (fv.job_name, fv.task_index, fv.batch_size, fv.learning_rate) == ("ps", 0, 100, 0.001)
+    assert (fv.training_steps, fv.logdir, fv.num_workers, fv.num_gpus) == (10 ** 7, "./tmp/mnist/1", 2, 1)
+    assert fv.num_ps == 1 and fv.sync is False and fv.optimizer == "sgd"
+
+
+def test_flag_spellings_and_unknown_tolerated():
+    fv = _flags()
+    rest = fv.parse(["--num_workers", "16", "--num_gpus=4", "--job_name", "worker", "--task_index=3",
+                     "--totally_unknown=1", "--learning_rate", "0.1", "--sync", "--training_steps=1e4", "positional"])
+    assert (fv.num_workers, fv.num_gpus, fv.job_name, fv.task_index) == (16, 4, "worker", 3)
+    assert fv.learning_rate == 0.1 and fv.sync is True and fv.training_steps == 10000
+    assert rest == ["--totally_unknown=1", "positional"] and fv.unparsed == rest
+
+
+def test_flags_lazy_parse(monkeypatch):
+    fv = _flags()
+    monkeypatch.setattr(sys, "argv", ["prog", "--batch_size=7"])
+    assert fv.batch_size == 7              # parsed on first access, no explicit parse()/app.run()
+    fv.batch_size = 9
+    assert fv.batch_size == 9
+    with pytest.raises(AttributeError):
+        fv.nope
+    with pytest.raises(ValueError):
+        _flags().parse(["--task_index", "abc"])
+    fv2 = _flags(); fv2.parse(["--nosync", "--unlocked_apply=true"])
+    assert fv2.sync is False and fv2.unlocked_apply is True
+
+
+def test_cluster_spec_ports_and_order():
+    spec = cluster_spec(2, 1)
+    assert spec == {"ps": ["127.0.0.1:12222"], "worker": ["127.0.0.1:12223", "127.0.0.1:12224"]}
+    spec = cluster_spec(16, 3)
+    assert spec["ps"] == [f"127.0.0.1:{12222 + i}" for i in range(3)]
+    assert spec["worker"][0] == "127.0.0.1:12225" and spec["worker"][-1] == "127.0.0.1:12240"
+    cs = ClusterSpec(spec)
+    assert cs.num_tasks("worker") == 16 and cs.task_address("ps", 2) == "127.0.0.1:12224"
+    assert cs.task_host_port("worker", 1) == ("127.0.0.1", 12226)
+    assert cs.global_rank("ps", 1) == 1 and cs.global_rank("worker", 0) == 3 and cs.world_size == 19
+    with pytest.raises(ValueError):
+        cs.task_address("worker", 16)
+    with pytest.raises(ValueError):
+        ClusterSpec({"ps": ["nohostport"]})
+
+
+def test_device_spec_roundtrip_and_merge():
+    d = DeviceSpec.from_string("/job:worker/task:3/gpu:0")
+    assert (d.job, d.task, d.device_type, d.device_index) == ("worker", 3, "gpu", 0)
+    assert d.to_string() == "/job:worker/task:3/gpu:0"
+    assert DeviceSpec.from_string("/job:ps").merge_from(DeviceSpec.from_string("/task:1/cpu:0")).to_string() == "/job:ps/task:1/cpu:0"
+    with pytest.raises(ValueError):
+        DeviceSpec.from_string("garbage")
+
+
+@pytest.mark.parametrize("num_ps", [1, 2, 3])
+def test_replica_device_setter_round_robin(num_ps):
+    fn = replica_device_setter(num_ps, worker_device="/job:worker/task:0/cpu:0")
+    devs = [fn(OpInfo(f"v{i}", True, 4)) for i in range(5)]
+    assert devs == [f"/job:ps/task:{i % num_ps}" for i in range(5)]
+    assert fn(OpInfo("matmul", False)) == "/job:worker/task:0/cpu:0"
+    assert replica_device_setter(0, worker_device="/job:worker/task:0")(OpInfo("v", True)) == "/job:worker/task:0"
+
+
+def test_greedy_strategy_balances_bytes():
+    fn = replica_device_setter(2, ps_strategy=GreedyLoadBalancingStrategy(2))
+    sizes = [313600, 400, 4000, 40, 4]
+    devs = [fn(OpInfo(f"v{i}", True, s)) for i, s in enumerate(sizes)]
+    assert devs[0] == "/job:ps/task:0" and all(d == "/job:ps/task:1" for d in devs[1:])
+
+
+def test_variable_scopes_names_and_get_vars():
+    from distributedtensorflowexample_b200.models.mlp import reference_mlp_spec
+    from distributedtensorflowexample_b200.train.replica import build_replicated_model
+    m = build_replicated_model(reference_mlp_spec(), "worker", 1, num_ps=2)
+    g = [v.name for v in m.global_trainable]
+    assert g == ["global/dense/kernel", "global/dense/bias", "global/dense_1/kernel", "global/dense_1/bias"]
+    assert [v.name for v in m.local_trainable] == [n.replace("global", "local") for n in g]
+    assert [v.name for v in m.global_all] == g + ["global/global_step"]         # the saver's 5 tensors
+    assert m.global_step.dtype == "int32" and m.global_step.shape == () and not m.global_step.trainable
+    assert [v.shape for v in m.global_trainable] == [(784, 100), (100,), (100, 10), (10,)]
+    assert sum(v.numel for v in m.global_trainable) == 79510
+    assert [v.device.to_string() for v in m.global_all] == [f"/job:ps/task:{i % 2}" for i in range(5)]
+    assert all(v.device.to_string() == "/job:worker/task:1/gpu:0" for v in m.local_all)
+    assert [(l.name, gl.name) for l, gl in m.sync_pairs()][0] == ("local/dense/kernel", "global/dense/kernel")
+    assert m.global_trainable[0].initializer.kind == "random_normal" and m.global_trainable[0].initializer.stddev == 1.0
+    assert m.global_trainable[1].initializer.kind == "zeros"
+    # get_vars matches a regex prefix like tf.get_collection(key, scope)
+    assert len(get_vars(m.store, "glo")) == 4 and len(get_vars(m.store, "local/dense_1")) == 2
+    st = VariableStore()
+    with st.variable_scope("a"):
+        st.get_variable("x", [2], initializer=random_normal_initializer())
+        with pytest.raises(ValueError):
+            st.get_variable("x", [2])
+
+
+def test_memory_fraction_formula():
+    assert memory.per_process_gpu_memory_fraction(2, 1) == pytest.approx(0.45)
+    assert memory.per_process_gpu_memory_fraction(16, 4) == pytest.approx(0.225)
+    assert memory.per_process_gpu_memory_fraction(3, 2) == pytest.approx(0.45)
+    b = memory.banner(0.45).splitlines()
+    assert b[0] == "-" * 100 and b[1] == "Per-process GPU memory fraction: 0.45" and b[2] == "-" * 100
+
+
+def test_launcher_task_commands_modulo_mapping():
+    from distributedtensorflowexample_b200.launch import launcher
+    tasks = launcher.task_commands(16, 4, ["0", "1", "2", "3"])
+    assert [t["name"] for t in tasks][:3] == ["ps", "worker0", "worker1"] and len(tasks) == 17
+    assert [t["env"]["CUDA_VISIBLE_DEVICES"] for t in tasks[1:]] == [str(i % 4) for i in range(16)]
+    w5 = tasks[6]["argv"]
+    assert w5[w5.index("--job_name") + 1] == "worker" and w5[w5.index("--task_index") + 1] == "5"
+    assert "--task_index=0" in tasks[0]["argv"]
+    cpu = launcher.task_commands(2, 1, ["0"], device="cpu")
+    assert all(t["env"]["CUDA_VISIBLE_DEVICES"] == "" for t in cpu)        # like the reference's ps
+    cmds = launcher.launch_tmux("sess", tasks[:3], dry_run=True)
+    assert cmds[0] == ["tmux", "kill-session", "-t", "sess"]
+    assert cmds[1][:6] == ["tmux", "new-session", "-s", "sess", "-n", "ps"]
+    assert cmds[2][:2] == ["tmux", "new-window"] and cmds[-1][:2] == ["tmux", "a"]
+    with pytest.raises(ValueError):
+        launcher.task_commands(2, 4, ["0"])
+
+
+def test_shell_launchers_keep_reference_knobs():
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run(["bash", os.path.join(root, "run_multi_gpu.sh"), "--mode", "print"], capture_output=True,
+                         text=True, env={**os.environ, "MODE": "print"}, timeout=60).stdout
+    assert out.count("new-window") == 16 and "--num_workers 16 --num_gpus 4" in out
+    assert "CUDA_VISIBLE_DEVICES=3" in out and "--task_index 15" in out
+    out = subprocess.run(["bash", os.path.join(root, "run_single_gpu.sh")], capture_output=True, text=True,
+                         env={**os.environ, "MODE": "print"}, timeout=60).stdout
+    assert out.count("new-window") == 2 and "--num_workers 2 --num_gpus 1" in out
