@@ -197,8 +197,8 @@ def define_framework_flags(flag_values: FlagValues = FLAGS) -> FlagValues:
     DEFINE_string("data_dir", "MNIST_data", "Directory with the MNIST idx.gz files", flag_values)
     DEFINE_string("hidden", "100", "Comma-separated hidden layer widths (reference: 100)", flag_values)
     DEFINE_integer("seed", -1, "RNG seed (-1 = unseeded like the reference)", flag_values)
-    DEFINE_integer("save_model_secs", 30, "Chief checkpoint period in seconds (reference: 30)", flag_values)
-    DEFINE_integer("save_summaries_secs", 30, "Chief global_step/sec summary period (reference: 30)", flag_values)
+    DEFINE_float("save_model_secs", 30, "Chief checkpoint period in seconds (reference: 30)", flag_values)
+    DEFINE_float("save_summaries_secs", 30, "Chief global_step/sec summary period (reference: 30)", flag_values)
     DEFINE_integer("log_every", 100, "Print step/cost/speed when global step %% this == 0 (reference: 100)", flag_values)
     DEFINE_integer("eval_every", 10000, "Test-set accuracy when global step %% this == 0 (reference: 10000)", flag_values)
     DEFINE_integer("steps_per_launch", 1, "Training steps fused into one persistent kernel launch", flag_values)
@@ -208,5 +208,5 @@ def define_framework_flags(flag_values: FlagValues = FLAGS) -> FlagValues:
     DEFINE_boolean("unlocked_apply", False, "Apply pushes as unlocked read-modify-write like TF1 use_locking=False "
                    "(default: lossless red.add)", flag_values)
     DEFINE_string("fault", "", "Test-only fault injection, e.g. 'kill_worker:1@50' or 'delay_push:0.01'", flag_values)
-    DEFINE_integer("recovery_wait_secs", 30, "Non-chief poll period while waiting for the chief's init (TF1: 30)", flag_values)
+    DEFINE_float("recovery_wait_secs", 30, "Non-chief poll period while waiting for the chief's init (TF1: 30)", flag_values)
     return flag_values

@@ -89,13 +89,42 @@ class GlooParamServer:
         self.stop_requested = False
         self.num_workers = num_workers
         self.requests_served = 0
+        self.peer_errors = 0
+        self.dead = set()
+        self.reply_timeout_s = 5.0
+
+    def _reply(self, t: torch.Tensor, dst: int, op: int) -> None:
+        """Send a response without letting one vanished client wedge the server for everyone else."""
+        import datetime
+        try:
+            dist.isend(t, dst=dst).wait(timeout=datetime.timedelta(seconds=self.reply_timeout_s))
+        except RuntimeError as e:
+            self.peer_errors += 1
+            self.dead.add(dst)
+            print(f"ps:{self.task}: dropping reply to rank {dst} (op {op}): {str(e).splitlines()[0]}", flush=True)
 
     def serve_forever(self) -> None:
         hdr = torch.zeros(4, dtype=torch.int64)
         done_workers = 0
+        last_seq: Dict[int, int] = {}
         while True:
-            src = dist.recv(hdr)
-            op, a0 = int(hdr[0]), int(hdr[1])
+            hdr.zero_()
+            try:
+                src = dist.recv(hdr)
+            except RuntimeError:
+                # a worker process died (reference 5.3: a non-chief crash is harmless to the others);
+                # its half-open pair surfaces here - keep serving everyone else
+                self.peer_errors += 1
+                time.sleep(0.01)
+                continue
+            op, a0, seq = int(hdr[0]), int(hdr[1]), int(hdr[2])
+            # every request carries a per-client sequence number; anything else (an all-zero header or a
+            # replay from a connection that went away) is not a request
+            if op == 0 or src in self.dead or seq != last_seq.get(src, 0) + 1:
+                self.peer_errors += 1
+                time.sleep(0.001)
+                continue
+            last_seq[src] = seq
             n = self.numel
             self.requests_served += 1
             if op == OP_ALLOC:
@@ -103,18 +132,18 @@ class GlooParamServer:
                     self.numel = a0
                     self.flat = torch.zeros(max(a0, 1), dtype=torch.float32)
             elif op == OP_PULL:
-                dist.send(self.flat, dst=src)
+                self._reply(self.flat, src, op)
             elif op == OP_PUSH:
                 buf = torch.empty(max(n, 1), dtype=torch.float32)
                 dist.recv(buf, src=src)
                 # ApplyGradientDescent on the ps: var -= lr * grad (TF1 T10); unsynchronised across workers
                 self.flat.add_(buf, alpha=-_bits_to_float(a0))
             elif op == OP_STEP_READ:
-                dist.send(self.step, dst=src)
+                self._reply(self.step, src, op)
             elif op == OP_STEP_INC:
                 old = self.step.clone()
                 self.step += a0
-                dist.send(old, dst=src)
+                self._reply(old, src, op)
             elif op == OP_ASSIGN:
                 buf = torch.empty(max(n, 1) + 1, dtype=torch.float32)
                 dist.recv(buf, src=src)
@@ -122,13 +151,13 @@ class GlooParamServer:
                 if a0 >= 0:
                     self.step[0] = a0
             elif op == OP_IS_READY:
-                dist.send(torch.tensor([1 if self.ready else 0], dtype=torch.int64), dst=src)
+                self._reply(torch.tensor([1 if self.ready else 0], dtype=torch.int64), src, op)
             elif op == OP_SET_READY:
                 self.ready = True
             elif op == OP_STOP_REQ:
                 self.stop_requested = True
             elif op == OP_STOP_QUERY:
-                dist.send(torch.tensor([1 if self.stop_requested else 0], dtype=torch.int64), dst=src)
+                self._reply(torch.tensor([1 if self.stop_requested else 0], dtype=torch.int64), src, op)
             elif op == OP_SHUTDOWN:
                 done_workers += 1
                 if a0 == 1 or done_workers >= self.num_workers:
@@ -165,13 +194,15 @@ class GlooParamClient(ParamClient):
         self.layouts = [_TaskLayout(self.variables, k) for k in range(self.num_ps)]
         self.step_task = next((k for k, l in enumerate(self.layouts) if l.has_step), 0)
         self._hdr = torch.zeros(4, dtype=torch.int64)
+        self._seq = [0] * self.num_ps
         self.messages = 0
 
     def _rank(self, k: int) -> int:
         return self.cluster.global_rank("ps", k)
 
     def _send_hdr(self, k: int, op: int, a0: int = 0) -> None:
-        self._hdr[0], self._hdr[1] = op, a0
+        self._seq[k] += 1
+        self._hdr[0], self._hdr[1], self._hdr[2] = op, a0, self._seq[k]
         dist.send(self._hdr, dst=self._rank(k))
         self.messages += 1
 

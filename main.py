@@ -26,6 +26,8 @@ FLAGS = flags_lib.FLAGS
 
 
 def main() -> int:
+    import faulthandler, signal as _signal
+    faulthandler.register(_signal.SIGUSR1, all_threads=True)     # kill -USR1 <pid> dumps every thread's stack
     from distributedtensorflowexample_b200.data import find_data_dir, read_data_sets
     from distributedtensorflowexample_b200.train.server import Server, ServerConfig, resolve_backend
 

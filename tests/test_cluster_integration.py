@@ -30,7 +30,7 @@ def _free_base_port(n=8):
 
 def _cluster(tmp_path, num_workers=2, num_ps=1, extra=()):
     logdir = str(tmp_path / "log")
-    args = ["--logdir", logdir, "--seed", "1", "--recovery_wait_secs", "1", "--save_model_secs", "1",
+    args = ["--logdir", logdir, "--seed", "1", "--recovery_wait_secs", "0.5", "--save_model_secs", "0.2",
             "--base_port", str(_free_base_port()), "--data", "synthetic", *extra]
     tasks = launcher.task_commands(num_workers, 1, ["0"], num_ps=num_ps, device="cpu", extra=args)
     return launcher.HeadlessCluster(tasks, echo=False), logdir
@@ -82,7 +82,7 @@ def test_async_training_step_accounting_and_outputs(tmp_path, num_ps):
 
 
 def test_resume_from_checkpoint_after_restart(tmp_path):
-    cl, logdir = _cluster(tmp_path, extra=["--training_steps", "150"])
+    cl, logdir = _cluster(tmp_path, extra=["--training_steps", "800"])
     cl.start()
     assert all(c == 0 for c in cl.wait(timeout=240).values()), cl.lines
     time.sleep(0.2)
