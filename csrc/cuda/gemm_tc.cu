@@ -1,0 +1,463 @@
+// tcgen05 GEMM for sm_100a: TMA -> 128B-swizzled shared memory -> tcgen05.mma (bf16 operands,
+// fp32 accumulators in TMEM) -> tcgen05.ld epilogue, with the framework's fused epilogues:
+//
+//   EPI_STORE        D = acc                                   (plain GEMM, tests)
+//   EPI_BIAS_ACT     D = act(acc + bias[n])                    dense forward  (reference worker.py:50-53)
+//   EPI_ACTGRAD      D = acc * h*(1-h)                         dX with SigmoidGrad fused (worker.py:72-73)
+//   EPI_PUSH         W[m,n] += alpha*acc  via red.global.add   dW with the gradient push + SGD apply fused
+//                                                             (worker.py:75-79)
+//
+// Any operand may live in a peer GPU's HBM: the TMA descriptor is built on whatever device pointer
+// the caller passes, so "B = weights in the owning ps shard" makes the forward GEMM read the shard
+// over NVLink tile by tile - the pull fused with the GEMM (worker.py:81-85 + :50).
+//
+// Operand majors.  UMMA computes D[M,N] = A[M,K] * B[N,K]^T with each operand either K-major
+// (K contiguous in memory) or MN-major (M resp. N contiguous):
+//   forward  Z = X[B,in] . W[in,out]      : A K-major, B MN-major   (W is [K][N], N contiguous)
+//   dX       dX = dY[B,out] . W[in,out]^T : A K-major, B K-major    (W is [N][K], K contiguous)
+//   dW       dW = X[B,in]^T . dY[B,out]   : A MN-major, B MN-major  (both are [K][MN])
+//
+// Shared-memory tile layouts (bf16, BLOCK_K = 64 -> 128-byte swizzle rows):
+//   K-major  operand, R rows : one TMA box {64 k, R rows}; row r at r*128 B; SBO = 1024 B; the k-th
+//                              UMMA_K=16 slice starts 32 B further.
+//   MN-major operand, R cols : R/64 TMA boxes {64 mn, 64 k-rows}, box b at b*8192 B; k-row at
+//                              +128 B; LBO = 8192 B (next 64 mn), SBO = 1024 B (next 8 k-rows); the
+//                              k-th UMMA_K slice starts 2048 B further.
+// (Both verified against CuTe's make_umma_desc on the host; see DESIGN.md.)
+//
+// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer,
+// warps 2..5 = epilogue (TMEM lane quarter = warp_id % 4).
+#include "common.cuh"
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <mutex>
+
+namespace {
+
+constexpr int BM = 128, BK = 64, UMMA_K = 16;
+constexpr int kThreads = 192;
+
+enum { EPI_STORE = 0, EPI_BIAS_ACT = 1, EPI_ACTGRAD = 2, EPI_PUSH = 3 };
+enum { OUT_F32 = 0, OUT_BF16 = 1 };
+
+struct GemmTcArgs {
+  int M, N, K;
+  void* D; long ldd;               // output (or pushed-into shard) matrix, row-major [M][ldd]
+  int out_dtype;                   // OUT_F32 | OUT_BF16
+  const void* bias; int bias_dtype;  // [N]  (EPI_BIAS_ACT)
+  const __nv_bfloat16* H; long ldh;  // [M][ldh] activation output being differentiated (EPI_ACTGRAD)
+  float alpha;                     // EPI_PUSH scale (-lr)
+  int act;                         // 0 none, 1 sigmoid
+  float* G; long ldg;              // optional fp32 raw gradient copy (EPI_PUSH), may be null
+};
+
+// ---------------------------------------------------------------- PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred P1;\n\t"
+      "WAIT_LOOP:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t"
+      "@P1 bra DONE;\n\t"
+      "bra WAIT_LOOP;\n\t"
+      "DONE:\n\t"
+      "}" :: "r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void fence_barrier_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      :: "r"(smem_u32(smem_dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
+  asm volatile("prefetch.tensormap [%0];" :: "l"(map) : "memory");
+}
+
+__device__ __forceinline__ void tmem_alloc(uint32_t* smem_holder, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+               :: "r"(smem_u32(smem_holder)), "r"(ncols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
+               :: "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* r) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
+      "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// Shared-memory matrix descriptor (version 1, SWIZZLE_128B).  lbo/sbo in bytes.
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr >> 4) & 0x3fff);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3fff) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3fff) << 32;
+  d |= (uint64_t)1 << 46;   // descriptor version (Blackwell)
+  d |= (uint64_t)2 << 61;   // SWIZZLE_128B
+  return d;
+}
+
+// kind::f16 instruction descriptor: bf16 x bf16 -> f32
+__host__ __device__ constexpr uint32_t make_idesc(int M, int N, int a_mn_major, int b_mn_major) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn_major << 15) | ((uint32_t)b_mn_major << 16) |
+         ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+// ---------------------------------------------------------------- epilogue helpers
+__device__ __forceinline__ float ld_param(const void* p, int dtype, int i) {
+  return dtype == OUT_F32 ? __ldg((const float*)p + i) : __bfloat162float(((const __nv_bfloat16*)p)[i]);
+}
+
+template <int EPI>
+__device__ __forceinline__ void epilogue_chunk(const GemmTcArgs& g, int m, int n0, const uint32_t* acc_bits) {
+  // one row m, 32 consecutive columns n0..n0+31
+  float v[32];
+#pragma unroll
+  for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(acc_bits[j]);
+  const int nvalid = min(32, g.N - n0);
+  if (nvalid <= 0) return;
+  if (EPI == EPI_BIAS_ACT) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      if (j < nvalid) {
+        float z = v[j] + (g.bias ? ld_param(g.bias, g.bias_dtype, n0 + j) : 0.f);
+        v[j] = g.act == 1 ? dtfe::sigmoidf_fast(z) : z;
+      }
+    }
+  } else if (EPI == EPI_ACTGRAD) {
+    const __nv_bfloat16* h = g.H + (long)m * g.ldh + n0;
+    if (nvalid == 32 && ((reinterpret_cast<uintptr_t>(h) & 15) == 0)) {
+      const uint4* h4 = reinterpret_cast<const uint4*>(h);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        uint4 pk = __ldg(h4 + q);
+        const __nv_bfloat162* hp = reinterpret_cast<const __nv_bfloat162*>(&pk);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          float2 hf = __bfloat1622float2(hp[e]);
+          v[q * 8 + 2 * e] *= hf.x * (1.f - hf.x);
+          v[q * 8 + 2 * e + 1] *= hf.y * (1.f - hf.y);
+        }
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (j < nvalid) { float hf = __bfloat162float(h[j]); v[j] *= hf * (1.f - hf); }
+    }
+  }
+  if (EPI == EPI_PUSH) {
+    if (g.G) {
+      float* gp = g.G + (long)m * g.ldg + n0;
+#pragma unroll
+      for (int j = 0; j < 32; ++j) if (j < nvalid) gp[j] = v[j];
+    }
+    if (g.D == nullptr) return;
+    if (g.out_dtype == OUT_F32) {
+      float* w = (float*)g.D + (long)m * g.ldd + n0;
+      if (nvalid == 32 && ((reinterpret_cast<uintptr_t>(w) & 15) == 0)) {
+#pragma unroll
+        for (int q = 0; q < 8; ++q)
+          dtfe::red_add_sys_v4(w + 4 * q, make_float4(g.alpha * v[4 * q], g.alpha * v[4 * q + 1],
+                                                      g.alpha * v[4 * q + 2], g.alpha * v[4 * q + 3]));
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) if (j < nvalid) dtfe::red_add_sys(w + j, g.alpha * v[j]);
+      }
+    } else {
+      __nv_bfloat16* w = (__nv_bfloat16*)g.D + (long)m * g.ldd + n0;
+      if (nvalid == 32 && ((reinterpret_cast<uintptr_t>(w) & 15) == 0)) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          uint4 p;
+          p.x = dtfe::pack_bf16x2(g.alpha * v[8 * q + 0], g.alpha * v[8 * q + 1]);
+          p.y = dtfe::pack_bf16x2(g.alpha * v[8 * q + 2], g.alpha * v[8 * q + 3]);
+          p.z = dtfe::pack_bf16x2(g.alpha * v[8 * q + 4], g.alpha * v[8 * q + 5]);
+          p.w = dtfe::pack_bf16x2(g.alpha * v[8 * q + 6], g.alpha * v[8 * q + 7]);
+          dtfe::red_add_sys_v4_bf16x2(w + 8 * q, p);
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (j < nvalid) atomicAdd(w + j, __float2bfloat16(g.alpha * v[j]));
+      }
+    }
+    return;
+  }
+  // plain stores
+  if (g.out_dtype == OUT_F32) {
+    float* d = (float*)g.D + (long)m * g.ldd + n0;
+    if (nvalid == 32 && ((reinterpret_cast<uintptr_t>(d) & 15) == 0)) {
+#pragma unroll
+      for (int q = 0; q < 8; ++q)
+        reinterpret_cast<float4*>(d)[q] = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) if (j < nvalid) d[j] = v[j];
+    }
+  } else {
+    __nv_bfloat16* d = (__nv_bfloat16*)g.D + (long)m * g.ldd + n0;
+    if (nvalid == 32 && ((reinterpret_cast<uintptr_t>(d) & 15) == 0)) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        uint4 p;
+        p.x = dtfe::pack_bf16x2(v[8 * q + 0], v[8 * q + 1]);
+        p.y = dtfe::pack_bf16x2(v[8 * q + 2], v[8 * q + 3]);
+        p.z = dtfe::pack_bf16x2(v[8 * q + 4], v[8 * q + 5]);
+        p.w = dtfe::pack_bf16x2(v[8 * q + 6], v[8 * q + 7]);
+        reinterpret_cast<uint4*>(d)[q] = p;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) if (j < nvalid) d[j] = __float2bfloat16(v[j]);
+    }
+  }
+}
+
+// ---------------------------------------------------------------- the kernel
+// BN: tile width (128 or 256); A_MN/B_MN: operand majors; STAGES: smem ring depth.
+template <int BN, int A_MN, int B_MN, int EPI, int STAGES>
+__global__ void __launch_bounds__(kThreads, BN == 128 ? 2 : 1)
+k_gemm_tc(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, GemmTcArgs g) {
+  constexpr uint32_t A_BYTES = BM * BK * 2;   // 16 KB
+  constexpr uint32_t B_BYTES = BN * BK * 2;   // 16 / 32 KB
+  constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
+  constexpr uint32_t BOX_BYTES = 64 * BK * 2;  // one MN-major box: 64 mn x 64 k
+  constexpr uint32_t TMEM_COLS = BN;           // fp32 accumulator columns (power of two >= 32)
+
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  __shared__ __align__(8) uint64_t full_bar[STAGES];
+  __shared__ __align__(8) uint64_t empty_bar[STAGES];
+  __shared__ __align__(8) uint64_t tmem_full_bar;
+  __shared__ uint32_t tmem_base_holder;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+  const int num_kb = (g.K + BK - 1) / BK;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_a);
+    tma_prefetch_desc(&tmap_b);
+#pragma unroll
+    for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    mbar_init(&tmem_full_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(&tmem_base_holder, TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_holder;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        uint8_t* sa = smem + (size_t)stage * STAGE_BYTES;
+        uint8_t* sb = sa + A_BYTES;
+        mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
+        const int k0 = kb * BK;
+        if (A_MN) {
+#pragma unroll
+          for (int b = 0; b < BM / 64; ++b) tma_load_2d(sa + b * BOX_BYTES, &tmap_a, &full_bar[stage], m0 + b * 64, k0);
+        } else {
+          tma_load_2d(sa, &tmap_a, &full_bar[stage], k0, m0);
+        }
+        if (B_MN) {
+#pragma unroll
+          for (int b = 0; b < BN / 64; ++b) tma_load_2d(sb + b * BOX_BYTES, &tmap_b, &full_bar[stage], n0 + b * 64, k0);
+        } else {
+          tma_load_2d(sb, &tmap_b, &full_bar[stage], k0, n0);
+        }
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc(BM, BN, A_MN, B_MN);
+      int stage = 0; uint32_t phase = 0;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        const uint32_t sa = smem_u32(smem + (size_t)stage * STAGE_BYTES);
+        const uint32_t sb = sa + A_BYTES;
+#pragma unroll
+        for (int k = 0; k < BK / UMMA_K; ++k) {
+          const uint64_t adesc = A_MN ? make_smem_desc(sa + k * (UMMA_K * 128), BOX_BYTES, 1024)
+                                      : make_smem_desc(sa + k * (UMMA_K * 2), 16, 1024);
+          const uint64_t bdesc = B_MN ? make_smem_desc(sb + k * (UMMA_K * 128), BOX_BYTES, 1024)
+                                      : make_smem_desc(sb + k * (UMMA_K * 2), 16, 1024);
+          umma_bf16(tmem_base, adesc, bdesc, idesc, (kb | k) != 0);
+        }
+        umma_commit(&empty_bar[stage]);   // frees this smem stage once the MMAs above have read it
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+      umma_commit(&tmem_full_bar);        // accumulator complete
+    }
+  } else {
+    // ===================== epilogue (warps 2..5) =====================
+    const int q = warp & 3;               // TMEM lane quarter this warp may access
+    mbar_wait(&tmem_full_bar, 0);
+    tc_fence_after();
+    const int m = m0 + q * 32 + lane;
+#pragma unroll 1
+    for (int c = 0; c < BN; c += 32) {
+      uint32_t r[32];
+      tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c, r);
+      tmem_ld_wait();
+      if (m < g.M && n0 + c < g.N) epilogue_chunk<EPI>(g, m, n0 + c, r);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    __syncwarp();
+    tc_fence_after();
+    tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+// ---------------------------------------------------------------- host side
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+PFN_encodeTiled get_encode() {
+  static PFN_encodeTiled fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_encodeTiled>(p);
+  });
+  return fn;
+}
+
+// bf16 2-D tensor map over a row-major [rows][ld] matrix: inner dim = contiguous columns.
+int make_tmap(CUtensorMap* map, const void* base, uint64_t inner, uint64_t rows, uint64_t ld_elems,
+              uint32_t box_inner, uint32_t box_rows) {
+  PFN_encodeTiled enc = get_encode();
+  DTFE_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled is not available from this driver");
+  DTFE_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "gemm_tc: operand base must be 16-byte aligned");
+  DTFE_REQUIRE((ld_elems * 2) % 16 == 0, "gemm_tc: row pitch (%llu elements) must be a multiple of 8 for TMA",
+               (unsigned long long)ld_elems);
+  cuuint64_t dims[2] = {inner, rows};
+  cuuint64_t strides[1] = {ld_elems * 2};
+  cuuint32_t box[2] = {box_inner, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  DTFE_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  return 0;
+}
+
+template <int BN, int A_MN, int B_MN, int EPI>
+int launch_cfg(const CUtensorMap& ta, const CUtensorMap& tb, const GemmTcArgs& g, cudaStream_t stream) {
+  constexpr int STAGES = BN == 128 ? 3 : 4;   // 128: 97 KB -> two CTAs per SM; 256: 193 KB -> one
+  constexpr size_t smem = (size_t)STAGES * (BM * BK * 2 + BN * BK * 2) + 1024;
+  auto kern = k_gemm_tc<BN, A_MN, B_MN, EPI, STAGES>;
+  static bool configured[64] = {};
+  int dev;
+  DTFE_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 64 && !configured[dev]) {
+    DTFE_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured[dev] = true;
+  }
+  dim3 grid((g.N + BN - 1) / BN, (g.M + BM - 1) / BM);
+  kern<<<grid, kThreads, smem, stream>>>(ta, tb, g);
+  DTFE_LAUNCH_CHECK();
+  return 0;
+}
+
+template <int BN, int EPI>
+int launch_major(int a_mn, int b_mn, const CUtensorMap& ta, const CUtensorMap& tb, const GemmTcArgs& g,
+                 cudaStream_t s) {
+  if (!a_mn && b_mn) return launch_cfg<BN, 0, 1, EPI>(ta, tb, g, s);
+  if (!a_mn && !b_mn) return launch_cfg<BN, 0, 0, EPI>(ta, tb, g, s);
+  if (a_mn && b_mn) return launch_cfg<BN, 1, 1, EPI>(ta, tb, g, s);
+  return launch_cfg<BN, 1, 0, EPI>(ta, tb, g, s);
+}
+
+template <int BN>
+int launch_epi(int epi, int a_mn, int b_mn, const CUtensorMap& ta, const CUtensorMap& tb, const GemmTcArgs& g,
+               cudaStream_t s) {
+  switch (epi) {
+    case EPI_STORE: return launch_major<BN, EPI_STORE>(a_mn, b_mn, ta, tb, g, s);
+    case EPI_BIAS_ACT: return launch_major<BN, EPI_BIAS_ACT>(a_mn, b_mn, ta, tb, g, s);
+    case EPI_ACTGRAD: return launch_major<BN, EPI_ACTGRAD>(a_mn, b_mn, ta, tb, g, s);
+    case EPI_PUSH: return launch_major<BN, EPI_PUSH>(a_mn, b_mn, ta, tb, g, s);
+  }
+  dtfe_set_error("gemm_tc: unknown epilogue %d", epi);
+  return -1;
+}
+
+}  // namespace
+
+// D[M,N] (op)= A . B with bf16 operands and fp32 accumulation on the 5th-gen tensor cores.
+//   a_mn_major = 0: A is [M][lda] (K contiguous);  1: A is [K][lda] (M contiguous)
+//   b_mn_major = 0: B is [N][ldb] (K contiguous);  1: B is [K][ldb] (N contiguous)
+DTFE_API int dtfe_gemm_tc_bf16(const dtfe_gemm_tc* p, void* stream) {
+  DTFE_REQUIRE(p->M > 0 && p->N > 0 && p->K > 0, "gemm_tc: empty problem");
+  DTFE_REQUIRE(p->tile_n == 128 || p->tile_n == 256 || p->tile_n == 0, "gemm_tc: tile_n must be 0, 128 or 256");
+  int bn = p->tile_n ? p->tile_n : (p->N >= 2048 ? 256 : 128);
+  CUtensorMap ta, tb;
+  int rc;
+  if (p->a_mn_major) rc = make_tmap(&ta, p->A, (uint64_t)p->M, (uint64_t)p->K, (uint64_t)p->lda, 64, BK);
+  else rc = make_tmap(&ta, p->A, (uint64_t)p->K, (uint64_t)p->M, (uint64_t)p->lda, BK, BM);
+  if (rc) return rc;
+  if (p->b_mn_major) rc = make_tmap(&tb, p->B, (uint64_t)p->N, (uint64_t)p->K, (uint64_t)p->ldb, 64, BK);
+  else rc = make_tmap(&tb, p->B, (uint64_t)p->K, (uint64_t)p->N, (uint64_t)p->ldb, BK, (uint32_t)bn);
+  if (rc) return rc;
+  GemmTcArgs g{};
+  g.M = p->M; g.N = p->N; g.K = p->K;
+  g.D = p->D; g.ldd = p->ldd; g.out_dtype = p->out_bf16 ? OUT_BF16 : OUT_F32;
+  g.bias = p->bias; g.bias_dtype = p->bias_bf16 ? OUT_BF16 : OUT_F32;
+  g.H = (const __nv_bfloat16*)p->H; g.ldh = p->ldh;
+  g.alpha = p->alpha; g.act = p->act; g.G = p->G; g.ldg = p->ldg;
+  if (p->epilogue == EPI_ACTGRAD) DTFE_REQUIRE(p->H != nullptr, "gemm_tc: EPI_ACTGRAD needs H");
+  if (p->epilogue != EPI_PUSH) DTFE_REQUIRE(p->D != nullptr, "gemm_tc: D is null");
+  return bn == 256 ? launch_epi<256>(p->epilogue, p->a_mn_major, p->b_mn_major, ta, tb, g, (cudaStream_t)stream)
+                   : launch_epi<128>(p->epilogue, p->a_mn_major, p->b_mn_major, ta, tb, g, (cudaStream_t)stream);
+}

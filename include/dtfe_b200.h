@@ -129,6 +129,31 @@ int dtfe_mlp2_step(const dtfe_mlp2_launch* launch, void* stream);
 size_t dtfe_mlp2_step_noalloc_max_words(void);
 int dtfe_mlp2_step_noalloc(const dtfe_mlp2_launch* launch, void* stream);
 
+/* ---- tcgen05 GEMM with fused epilogues (bf16 operands, fp32 accumulation in TMEM) ---------------- */
+/* D[M,N] (op)= A . B through TMA -> swizzled smem -> tcgen05.mma -> TMEM -> tcgen05.ld.
+ *   a_mn_major = 0: A is [M][lda], K contiguous;   1: A is [K][lda], M contiguous
+ *   b_mn_major = 0: B is [N][ldb], K contiguous;   1: B is [K][ldb], N contiguous
+ * so with the reference's [in,out] kernels (worker.py:50-53):
+ *   forward  X.W        : A=X (0), B=W (1)      epilogue 1: D = act(acc + bias)      worker.py:50-53
+ *   dX       dY.W^T     : A=dY (0), B=W (0)     epilogue 2: D = acc * H*(1-H)        worker.py:72-73
+ *   dW push  X^T.dY     : A=X (1), B=dY (1)     epilogue 3: D += alpha*acc (red.add) worker.py:75-79
+ * Operands may be peer-mapped shard memory: B = shard weights makes the forward GEMM the pull
+ * (worker.py:81-85).  Row pitches must be multiples of 8 elements, bases 16-byte aligned.
+ * epilogue: 0 store, 1 bias+act (act: 0 none, 1 sigmoid), 2 sigmoid-grad with H, 3 push into D
+ * (D may be NULL when only the raw fp32 gradient G is wanted).  tile_n: 0 auto, 128, 256. */
+typedef struct dtfe_gemm_tc {
+  int M, N, K;
+  const void* A; long lda; int a_mn_major;
+  const void* B; long ldb; int b_mn_major;
+  void* D; long ldd; int out_bf16;
+  int epilogue;
+  const void* bias; int bias_bf16; int act;
+  const void* H; long ldh;
+  float alpha; float* G; long ldg;
+  int tile_n;
+} dtfe_gemm_tc;
+int dtfe_gemm_tc_bf16(const dtfe_gemm_tc* p, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

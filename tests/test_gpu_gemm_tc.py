@@ -1,0 +1,68 @@
+"""GPU numerics of the tcgen05 GEMM against fp32 PyTorch on the same bf16-rounded operands."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _mk(shape, seed, scale=1.0):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    return (torch.randn(*shape, device="cuda", generator=g) * scale).bfloat16()
+
+
+def _check(out, ref, K):
+    tol = 2e-2 * (K ** 0.5) * 0.05 + 1e-2
+    err = (out.float() - ref).abs().max().item()
+    scale = ref.abs().max().item() + 1e-6
+    assert err <= 1e-2 * scale + tol * 0 + 2e-2 * (1 if out.dtype == torch.bfloat16 else 0) * scale, (err, scale)
+
+
+@pytest.mark.parametrize("tile_n", [128, 256])
+@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (256, 256, 256), (100, 100, 784), (300, 520, 200), (1024, 1024, 1024)])
+@pytest.mark.parametrize("a_mn,b_mn", [(0, 0), (0, 1), (1, 1), (1, 0)])
+def test_gemm_tc_store_all_majors(M, N, K, a_mn, b_mn, tile_n):
+    from distributedtensorflowexample_b200.ops import gemm_tc as G
+    pad = lambda n: (n + 7) // 8 * 8
+    A = _mk((K, pad(M)) if a_mn else (M, pad(K)), 1)
+    B = _mk((K, pad(N)) if b_mn else (N, pad(K)), 2)
+    Av = A[:, :M] if a_mn else A[:, :K]
+    Bv = B[:, :N] if b_mn else B[:, :K]
+    D = torch.full((M, N), float("nan"), device="cuda")
+    G.gemm_tc(Av, Bv, M, N, K, bool(a_mn), bool(b_mn), D, tile_n=tile_n)
+    torch.cuda.synchronize()
+    Af = Av.float().T if a_mn else Av.float()
+    Bf = Bv.float() if b_mn else Bv.float().T
+    ref = Af @ Bf
+    assert torch.isfinite(D).all()
+    err = (D - ref).abs().max().item()
+    assert err <= 2e-3 * ref.abs().max().item() + 1e-3, (err, ref.abs().max().item())
+
+
+@pytest.mark.parametrize("B_,din,dout", [(100, 784, 104), (256, 512, 384), (4096, 784, 1024)])
+def test_dense_layer_ops_tc(B_, din, dout):
+    from distributedtensorflowexample_b200.ops import gemm_tc as G
+    x = torch.rand(B_, din, device="cuda").bfloat16()
+    W = _mk((din, dout), 3, 0.05)
+    b = _mk((1, dout), 4)[0]
+    out = torch.empty(B_, dout, device="cuda", dtype=torch.bfloat16)
+    G.dense_fwd_tc(x, W, b, 1, out)
+    ref = torch.sigmoid(x.float() @ W.float() + b.float())
+    assert (out.float() - ref).abs().max().item() < 1e-2
+    # dX with sigmoid-grad of the layer input
+    dY = _mk((B_, dout), 5, 0.1)
+    Hprev = torch.rand(B_, din, device="cuda").bfloat16()
+    dX = torch.empty(B_, din, device="cuda", dtype=torch.bfloat16)
+    G.dense_bwd_dx_tc(dY, W, Hprev, dX)
+    ref_dx = (dY.float() @ W.float().T) * Hprev.float() * (1 - Hprev.float())
+    assert (dX.float() - ref_dx).abs().max().item() < 2e-2 * ref_dx.abs().max().item() + 1e-3
+    # dW push into an fp32 and a bf16 shard, plus the raw gradient
+    ref_g = x.float().T @ dY.float()
+    W32 = W.float().clone()
+    Gout = torch.empty(din, dout, device="cuda")
+    G.dense_bwd_dw_push_tc(x, dY, W32, -0.01, grad_out=Gout)
+    assert (Gout - ref_g).abs().max().item() < 2e-3 * ref_g.abs().max().item() + 1e-3
+    assert (W32 - (W.float() - 0.01 * ref_g)).abs().max().item() < 1e-3 * (1 + ref_g.abs().max().item() * 0.01)
+    Wb = W.clone()
+    G.dense_bwd_dw_push_tc(x, dY, Wb, -0.01)
+    want = W.float() - 0.01 * ref_g
+    assert (Wb.float() - want).abs().max().item() < 2e-2 * want.abs().max().item() + 1e-3
