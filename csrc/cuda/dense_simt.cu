@@ -149,6 +149,45 @@ __global__ void __launch_bounds__(256) k_colsum_push(const float* D, long ldd, i
   }
 }
 
+// bf16 variant: lanes own column pairs (bf16x2 loads, 128 B per warp-row), rows split over gridDim.y;
+// every (column block, row slice) pushes its partial sum - the push is additive, so no second pass.
+__global__ void __launch_bounds__(256) k_colsum_push_bf16(const __nv_bfloat16* __restrict__ D, long ldd, int M, int N,
+                                                          void* b, int b_bf16, float* gout, float alpha) {
+  __shared__ float red[8][64 + 2];
+  int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int n = blockIdx.x * 64 + lane * 2;
+  int rows_per = (M + gridDim.y - 1) / gridDim.y;
+  int r0 = blockIdx.y * rows_per, r1 = min(M, r0 + rows_per);
+  float s0 = 0.f, s1 = 0.f;
+  if (n + 1 < N) {
+    for (int m = r0 + warp; m < r1; m += 8) {
+      __nv_bfloat162 v = *reinterpret_cast<const __nv_bfloat162*>(D + (long)m * ldd + n);
+      float2 f = __bfloat1622float2(v);
+      s0 += f.x; s1 += f.y;
+    }
+  } else if (n < N) {
+    for (int m = r0 + warp; m < r1; m += 8) s0 += __bfloat162float(D[(long)m * ldd + n]);
+  }
+  red[warp][lane * 2] = s0; red[warp][lane * 2 + 1] = s1;
+  __syncthreads();
+  if (warp == 0) {
+    float t0 = 0.f, t1 = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) { t0 += red[w][lane * 2]; t1 += red[w][lane * 2 + 1]; }
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      int c = n + e;
+      float t = e ? t1 : t0;
+      if (c >= N) continue;
+      if (gout) atomicAdd(gout + c, t);
+      if (b) {
+        if (b_bf16) atomicAdd((__nv_bfloat16*)b + c, __float2bfloat16(alpha * t));
+        else dtfe::red_add_sys((float*)b + c, alpha * t);
+      }
+    }
+  }
+}
+
 }  // namespace
 
 // C[M,N] = act(A[M,K] . W[K,N] + bias[N]).  W uses the reference's [in,out] kernel layout.
@@ -191,6 +230,18 @@ DTFE_API int dtfe_dense_bwd_dw_push_f32(const float* X, long ldx, const float* d
 DTFE_API int dtfe_bias_grad_push_f32(const float* dY, long lddy, int M, int N, float* b, float* gout,
                                      float alpha, int atomic, void* stream) {
   k_colsum_push<<<(N + 31) / 32, 256, 0, (cudaStream_t)stream>>>(dY, lddy, M, N, b, gout, alpha, atomic);
+  DTFE_LAUNCH_CHECK();
+  return 0;
+}
+
+// bf16 activations-gradient in, bias (bf16 or fp32 shard) updated in place; gout (fp32, pre-zeroed) optional.
+DTFE_API int dtfe_bias_grad_push_bf16(const void* dY_bf16, long lddy, int M, int N, void* b, int b_is_bf16,
+                                      float* gout, float alpha, void* stream) {
+  DTFE_REQUIRE(lddy % 2 == 0 && ((uintptr_t)dY_bf16 % 4) == 0, "dtfe_bias_grad_push_bf16: dY must be 4-byte aligned with even pitch");
+  int ysplit = M >= 2048 ? 8 : 1;
+  dim3 grid((N + 63) / 64, ysplit);
+  k_colsum_push_bf16<<<grid, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)dY_bf16, lddy, M, N, b, b_is_bf16,
+                                                             gout, alpha);
   DTFE_LAUNCH_CHECK();
   return 0;
 }

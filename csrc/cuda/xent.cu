@@ -15,7 +15,8 @@ __global__ void __launch_bounds__(256) k_xent(const float* __restrict__ Z, long 
                                               const int* __restrict__ ids,
                                               const float* __restrict__ dense, long ldl, int M, int C,
                                               float scale, float* __restrict__ dZ, long lddz,
-                                              float* __restrict__ rowloss, int* __restrict__ rowcorrect) {
+                                              float* __restrict__ rowloss, int* __restrict__ rowcorrect,
+                                              __nv_bfloat16* __restrict__ dZb, long lddzb) {
   int lane = threadIdx.x & 31;
   int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (row >= M) return;
@@ -57,16 +58,22 @@ __global__ void __launch_bounds__(256) k_xent(const float* __restrict__ Z, long 
       int oa = __shfl_xor_sync(0xffffffffu, label_arg, o);
       if (om > label_max || (om == label_max && oa < label_arg)) { label_max = om; label_arg = oa; }
     }
-    if (dZ)
-      for (int c = lane; c < C; c += 32)
-        dZ[(long)row * lddz + c] = (__expf(z[c] - mx) * inv * ysum - y[c]) * scale;
+    if (dZ || dZb)
+      for (int c = lane; c < C; c += 32) {
+        float d = (__expf(z[c] - mx) * inv * ysum - y[c]) * scale;
+        if (dZ) dZ[(long)row * lddz + c] = d;
+        if (dZb) dZb[(long)row * lddzb + c] = __float2bfloat16(d);
+      }
   } else {
     int yid = ids[row];
     label_arg = yid;
     loss = lse - z[yid];  // every lane computes the same value
-    if (dZ)
-      for (int c = lane; c < C; c += 32)
-        dZ[(long)row * lddz + c] = (__expf(z[c] - mx) * inv - (c == yid ? 1.f : 0.f)) * scale;
+    if (dZ || dZb)
+      for (int c = lane; c < C; c += 32) {
+        float d = (__expf(z[c] - mx) * inv - (c == yid ? 1.f : 0.f)) * scale;
+        if (dZ) dZ[(long)row * lddz + c] = d;
+        if (dZb) dZb[(long)row * lddzb + c] = __float2bfloat16(d);
+      }
   }
   if (lane == 0) {
     if (rowloss) rowloss[row] = loss;
@@ -107,7 +114,18 @@ DTFE_API int dtfe_softmax_xent_f32(const float* logits, long ldz, const int* lab
                "dtfe_softmax_xent_f32: pass exactly one of label_ids / label_dense");
   int rows_per_block = 8;
   k_xent<<<(M + rows_per_block - 1) / rows_per_block, 256, 0, (cudaStream_t)stream>>>(
-      logits, ldz, label_ids, label_dense, ldl, M, C, scale, dZ, lddz, rowloss, rowcorrect);
+      logits, ldz, label_ids, label_dense, ldl, M, C, scale, dZ, lddz, rowloss, rowcorrect, nullptr, 0);
+  DTFE_LAUNCH_CHECK();
+  return 0;
+}
+
+// Same, additionally writing a bf16 copy of dZ (the operand format of the tcgen05 backward GEMMs).
+DTFE_API int dtfe_softmax_xent_f32_bf16grad(const float* logits, long ldz, const int* label_ids, int M, int C,
+                                            float scale, float* dZ, long lddz, void* dZ_bf16, long lddzb,
+                                            float* rowloss, int* rowcorrect, void* stream) {
+  DTFE_REQUIRE(label_ids != nullptr, "dtfe_softmax_xent_f32_bf16grad: label_ids is null");
+  k_xent<<<(M + 7) / 8, 256, 0, (cudaStream_t)stream>>>(logits, ldz, label_ids, nullptr, 0, M, C, scale, dZ, lddz,
+                                                        rowloss, rowcorrect, (__nv_bfloat16*)dZ_bf16, lddzb);
   DTFE_LAUNCH_CHECK();
   return 0;
 }

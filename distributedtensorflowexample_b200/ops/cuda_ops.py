@@ -33,6 +33,8 @@ _SIGS = {
     "dtfe_dense_bwd_dw_push_f32": ([_P, c_long, _P, c_long, _P, c_long, _P, c_long, c_int, c_int, c_int, c_float, c_int, _P], c_int),
     "dtfe_bias_grad_push_f32": ([_P, c_long, c_int, c_int, _P, _P, c_float, c_int, _P], c_int),
     "dtfe_softmax_xent_f32": ([_P, c_long, _P, _P, c_long, c_int, c_int, c_float, _P, c_long, _P, _P, _P], c_int),
+    "dtfe_softmax_xent_f32_bf16grad": ([_P, c_long, _P, c_int, c_int, c_float, _P, c_long, _P, c_long, _P, _P, _P], c_int),
+    "dtfe_bias_grad_push_bf16": ([_P, c_long, c_int, c_int, _P, c_int, _P, c_float, _P], c_int),
     "dtfe_mean_loss_acc": ([_P, _P, c_int, _P, _P, _P, _P], c_int),
     "dtfe_push_sgd_f32": ([_P, _P, c_size_t, c_float, c_int, _P], c_int),
     "dtfe_push_sgd_bf16": ([_P, _P, c_size_t, c_float, _P], c_int),
@@ -217,6 +219,22 @@ def softmax_xent(logits, labels, scale: float, dZ=None, rowloss=None, rowcorrect
                                       dense.stride(0) if dense is not None else 0, M, C, scale, _ptr(dZ),
                                       dZ.stride(0) if dZ is not None else 0, _ptr(rowloss), _ptr(rowcorrect),
                                       _stream()), "dtfe_softmax_xent_f32")
+
+
+def softmax_xent_bf16grad(logits, label_ids, scale: float, dZ, dZ_bf16, rowloss=None, rowcorrect=None):
+    """softmax_xent that also emits the bf16 dZ operand of the tcgen05 backward GEMMs."""
+    M, C = logits.shape
+    check(lib().dtfe_softmax_xent_f32_bf16grad(logits.data_ptr(), logits.stride(0), label_ids.data_ptr(), M, C, scale,
+                                               _ptr(dZ), dZ.stride(0) if dZ is not None else 0, dZ_bf16.data_ptr(),
+                                               dZ_bf16.stride(0), _ptr(rowloss), _ptr(rowcorrect), _stream()),
+          "dtfe_softmax_xent_f32_bf16grad")
+
+
+def bias_grad_push_bf16(dY, b, alpha: float, grad_out=None):
+    M, N = dY.shape
+    check(lib().dtfe_bias_grad_push_bf16(dY.data_ptr(), dY.stride(0), M, N, _ptr(b),
+                                         int(b is not None and b.dtype == torch.bfloat16), _ptr(grad_out), alpha,
+                                         _stream()), "dtfe_bias_grad_push_bf16")
 
 
 def mean_loss_acc(rowloss, rowcorrect, M: int, out_loss=None, out_acc=None, out_count=None):

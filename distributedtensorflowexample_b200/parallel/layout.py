@@ -29,8 +29,9 @@ class Entry:
     offset: int        # bytes from shard base
     shape: tuple
     dtype: str
-    nbytes: int
+    nbytes: int        # bytes reserved in the shard (rows * pitch * itemsize for 2-D tensors)
     trainable: bool
+    pitch: int = 0     # row pitch in elements of 2-D tensors (0 = dense)
 
 
 def _align(n: int, a: int = ALIGN) -> int:
@@ -52,9 +53,15 @@ class ShardLayout:
             if not 0 <= k < num_shards:
                 raise ValueError(f"variable {v.name} placed on ps task {k} but there are {num_shards} shards")
             off = _align(cursor[k])
-            self.entries[v.name] = Entry(v.name, k, off, tuple(v.shape), v.dtype, v.nbytes, v.trainable)
+            nbytes, pitch = v.nbytes, 0
+            if len(v.shape) == 2 and v.dtype == "bfloat16" and v.shape[1] % 8:
+                # TMA needs 16-byte row pitches: bf16 matrices whose width is not a multiple of 8
+                # (the 10-wide output layer) get padded rows inside the shard
+                pitch = (v.shape[1] + 7) // 8 * 8
+                nbytes = v.shape[0] * pitch * 2
+            self.entries[v.name] = Entry(v.name, k, off, tuple(v.shape), v.dtype, nbytes, v.trainable, pitch)
             self.order.append(v.name)
-            cursor[k] = off + v.nbytes
+            cursor[k] = off + nbytes
         self.shard_bytes = [_align(c) for c in cursor]
 
     def __getitem__(self, name: str) -> Entry:

@@ -107,8 +107,13 @@ class PeerParamStore:
         t = self._views.get(name)
         if t is None:
             e = self.layout[name]
-            t = self._ops.tensor_from_ptr(self.base_ptr(e.shard) + e.offset, e.shape if e.shape else (1,),
-                                          _TORCH_DTYPES[e.dtype], self.device, owner=self)
+            if e.pitch:
+                full = self._ops.tensor_from_ptr(self.base_ptr(e.shard) + e.offset, (e.shape[0], e.pitch),
+                                                 _TORCH_DTYPES[e.dtype], self.device, owner=self)
+                t = full[:, :e.shape[1]]
+            else:
+                t = self._ops.tensor_from_ptr(self.base_ptr(e.shard) + e.offset, e.shape if e.shape else (1,),
+                                              _TORCH_DTYPES[e.dtype], self.device, owner=self)
             self._views[name] = t
         return t
 

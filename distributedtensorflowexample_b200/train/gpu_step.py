@@ -171,3 +171,72 @@ class LayerwiseStepper:
             correct += cnt
             total += m
         return correct, total
+
+
+class TcStepper:
+    """bf16 tensor-core engine for any MLPSpec with ``param_dtype='bfloat16'`` (the wide benchmark
+    family 784-8192-8192-10): every GEMM runs on ``tcgen05.mma`` via ``ops.gemm_tc`` with its
+    elementwise neighbour fused - bias+sigmoid into the forward GEMM, the sigmoid gradient into the dX
+    GEMM, the gradient push + SGD apply (``red.add`` into the shard, possibly over NVLink) into the dW
+    GEMM - and the forward GEMMs read the weights straight from the owning shard through TMA (pull).
+
+    Matrices whose width is not a multiple of 8 (the 10 logits) are kept with a padded row pitch."""
+
+    def __init__(self, spec: MLPSpec, batch: int, params: Sequence[torch.Tensor], global_step: torch.Tensor,
+                 lr: float, device, tile_n: int = 0):
+        from ..ops import gemm_tc
+        self.G = gemm_tc
+        self.spec, self.batch, self.lr, self.tile_n = spec, batch, lr, tile_n
+        self.params = list(params)
+        self.global_step = global_step
+        dev = torch.device(device)
+        dims = spec.dims
+        pad8 = lambda n: (n + 7) // 8 * 8
+        bf = dict(device=dev, dtype=torch.bfloat16)
+        self.acts = [torch.empty(batch, pad8(d), **bf)[:, :d] for d in dims[1:-1]]
+        C = dims[-1]
+        self.logits = torch.empty(batch, pad8(C), device=dev, dtype=torch.float32)[:, :C]
+        self.dz = torch.empty(batch, pad8(C), device=dev, dtype=torch.float32)[:, :C]
+        self.dz_bf = torch.zeros(batch, pad8(C), **bf)[:, :C]
+        self.dacts = [torch.empty(batch, pad8(d), **bf)[:, :d] for d in dims[1:-1]]
+        self.rowloss = torch.empty(batch, device=dev, dtype=torch.float32)
+        self.rowcorrect = torch.empty(batch, device=dev, dtype=torch.int32)
+        self.loss = torch.zeros(1, device=dev, dtype=torch.float32)
+        self.acc = torch.zeros(1, device=dev, dtype=torch.float32)
+        self.step = torch.zeros(1, device=dev, dtype=torch.int32)
+        L = spec.num_layers
+        self.launches_per_call = L + 2 + (L - 1) + 2 * L + 1
+
+    def forward(self, X: torch.Tensor, acts=None, logits=None) -> torch.Tensor:
+        acts = self.acts if acts is None else acts
+        logits = self.logits if logits is None else logits
+        h = X
+        L = self.spec.num_layers
+        for l in range(L):
+            W, b = self.params[2 * l], self.params[2 * l + 1]
+            last = l == L - 1
+            out = logits if last else acts[l]
+            self.G.dense_fwd_tc(h, W, b, ops.ACT_NONE if last else ops.ACT_SIGMOID, out, tile_n=self.tile_n)
+            h = out
+        return logits
+
+    def run(self, X: torch.Tensor, labels: torch.Tensor, train: bool = True) -> None:
+        B = X.shape[0]
+        self.forward(X)
+        ops.softmax_xent_bf16grad(self.logits, labels, 1.0 / B, self.dz, self.dz_bf, self.rowloss, self.rowcorrect)
+        ops.mean_loss_acc(self.rowloss, self.rowcorrect, B, self.loss, self.acc)
+        if not train:
+            return
+        alpha = -self.lr
+        d = self.dz_bf
+        L = self.spec.num_layers
+        for l in reversed(range(L)):
+            W, b = self.params[2 * l], self.params[2 * l + 1]
+            h_in = X if l == 0 else self.acts[l - 1]
+            d_prev = None
+            if l > 0:   # against the pre-update weights, so before this layer's push
+                d_prev = self.G.dense_bwd_dx_tc(d, W, h_in, self.dacts[l - 1], tile_n=self.tile_n)
+            self.G.dense_bwd_dw_push_tc(h_in, d, W, alpha, tile_n=self.tile_n)
+            ops.bias_grad_push_bf16(d, b, alpha)
+            d = d_prev
+        ops.global_step_add(self.global_step, 1, self.step)

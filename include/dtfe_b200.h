@@ -62,6 +62,10 @@ int dtfe_dense_bwd_dw_push_f32(const float* X, long ldx, const float* dY, long l
 int dtfe_bias_grad_push_f32(const float* dY, long lddy, int M, int N, float* b, float* gout, float alpha,
                             int atomic, void* stream);
 
+/* bf16 gradient in; bias may be a bf16 or an fp32 shard (TF1 BiasAddGrad + apply on the wide bf16 path). */
+int dtfe_bias_grad_push_bf16(const void* dY_bf16, long lddy, int M, int N, void* b, int b_is_bf16, float* gout,
+                             float alpha, void* stream);
+
 /* ---- loss / metrics ------------------------------------------------------------------------ */
 /* Softmax cross-entropy forward+backward with per-row loss and argmax-correct flags
  * (reference worker.py:59-68 loss, :87-90 accuracy).  Exactly one of label_ids (int32 [M]) and
@@ -69,6 +73,10 @@ int dtfe_bias_grad_push_f32(const float* dY, long lddy, int M, int N, float* b, 
 int dtfe_softmax_xent_f32(const float* logits, long ldz, const int* label_ids, const float* label_dense,
                           long ldl, int M, int C, float scale, float* dZ, long lddz, float* rowloss,
                           int* rowcorrect, void* stream);
+/* Same with class ids only, additionally writing a bf16 copy of dZ for the tcgen05 backward GEMMs. */
+int dtfe_softmax_xent_f32_bf16grad(const float* logits, long ldz, const int* label_ids, int M, int C, float scale,
+                                   float* dZ, long lddz, void* dZ_bf16, long lddzb, float* rowloss,
+                                   int* rowcorrect, void* stream);
 /* Deterministic means: *out_loss = mean(rowloss), *out_acc = mean(rowcorrect), *out_count = sum. */
 int dtfe_mean_loss_acc(const float* rowloss, const int* rowcorrect, int M, float* out_loss, float* out_acc,
                        int* out_count, void* stream);
