@@ -91,9 +91,11 @@ constexpr int kMaxRanks = 16;
 struct SyncArgs {
   const float* grads[kMaxRanks];  // every rank's gradient buffer (peer-mapped), full model length
   unsigned* flags[kMaxRanks];     // every rank's flag array (peer-mapped): [2][kMaxRanks] u32
-  float* param;                   // this rank's owned shard memory (local HBM), indexed like grads
-  size_t begin, end;              // owned element range inside the flat gradient vector
-  size_t param_off;               // param element i lives at param[i - param_off]
+  // Up to kMaxSeg owned variables: flat-gradient range [begin,end) of each and where its parameters
+  // live (this rank's shard, local HBM); parameter element i of segment s is param[s][i - begin[s]].
+  int nseg;
+  float* param[8];
+  size_t begin[8], end[8];
   float alpha;                    // -lr / W
   int rank, world;
   unsigned epoch;                 // strictly increasing per call, starts at 1
@@ -115,29 +117,31 @@ __global__ void __launch_bounds__(256) k_sync_rs_apply(SyncArgs a) {
   }
   __syncthreads();
 
-  // (b) reduce my slice over all ranks' buffers (peer loads) and apply in place.
-  size_t n = a.end - a.begin;
+  // (b) reduce my slices over all ranks' buffers (peer loads) and apply in place.
   size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   size_t stride = (size_t)gridDim.x * blockDim.x;
-  bool vec_ok = ((a.begin | a.param_off) % 4 == 0);
-  size_t nv = vec_ok ? n / 4 : 0;
-  for (size_t v = tid; v < nv; v += stride) {
-    size_t i = a.begin + v * 4;
-    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int q = 0; q < a.world; ++q) {
-      float4 g = dtfe::ld_relaxed_sys_v4(a.grads[q] + i);
-      s.x += g.x; s.y += g.y; s.z += g.z; s.w += g.w;
+  for (int sg = 0; sg < a.nseg; ++sg) {
+    const size_t begin = a.begin[sg], n = a.end[sg] - begin;
+    float* param = a.param[sg];
+    bool vec_ok = (begin % 4 == 0) && ((reinterpret_cast<uintptr_t>(param) & 15) == 0);
+    size_t nv = vec_ok ? n / 4 : 0;
+    for (size_t v = tid; v < nv; v += stride) {
+      size_t i = begin + v * 4;
+      float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int q = 0; q < a.world; ++q) {
+        float4 g = dtfe::ld_relaxed_sys_v4(a.grads[q] + i);
+        s.x += g.x; s.y += g.y; s.z += g.z; s.w += g.w;
+      }
+      float4* w = reinterpret_cast<float4*>(param + v * 4);
+      float4 o = *w;
+      o.x += a.alpha * s.x; o.y += a.alpha * s.y; o.z += a.alpha * s.z; o.w += a.alpha * s.w;
+      *w = o;
     }
-    float4* w = reinterpret_cast<float4*>(a.param + (i - a.param_off));
-    float4 o = *w;
-    o.x += a.alpha * s.x; o.y += a.alpha * s.y; o.z += a.alpha * s.z; o.w += a.alpha * s.w;
-    *w = o;
-  }
-  for (size_t e = nv * 4 + tid; e < n; e += stride) {
-    size_t i = a.begin + e;
-    float s = 0.f;
-    for (int q = 0; q < a.world; ++q) s += dtfe::ld_relaxed_sys(a.grads[q] + i);
-    a.param[i - a.param_off] += a.alpha * s;
+    for (size_t e = nv * 4 + tid; e < n; e += stride) {
+      float s = 0.f;
+      for (int q = 0; q < a.world; ++q) s += dtfe::ld_relaxed_sys(a.grads[q] + begin + e);
+      param[e] += a.alpha * s;
+    }
   }
 
   // (c) depart: once the whole grid has applied, publish and wait until every owner has too,
@@ -203,19 +207,27 @@ DTFE_API int dtfe_adam_apply_f32(float* param, float* m, float* v, float* slot, 
 }
 
 // One call per rank per step, all ranks, ONE RANK PER GPU (the kernel spins on peer flags).
+// The rank reduces and applies the `nseg` variables it owns; ranks owning nothing pass nseg = 0 and
+// only take part in the barriers.
 DTFE_API int dtfe_sync_rs_apply_f32(const float* const* grads, unsigned* const* flags, int rank, int world,
-                                    float* param, size_t begin, size_t end, size_t param_off, float alpha,
-                                    unsigned epoch, unsigned* local_sync, int* global_step_or_null,
-                                    void* stream) {
+                                    int nseg, float* const* seg_param, const size_t* seg_begin,
+                                    const size_t* seg_end, float alpha, unsigned epoch, unsigned* local_sync,
+                                    int* global_step_or_null, void* stream) {
   DTFE_REQUIRE(world >= 1 && world <= kMaxRanks, "dtfe_sync_rs_apply_f32: world must be in [1,%d]", kMaxRanks);
-  DTFE_REQUIRE(end >= begin, "dtfe_sync_rs_apply_f32: bad range");
+  DTFE_REQUIRE(nseg >= 0 && nseg <= 8, "dtfe_sync_rs_apply_f32: nseg must be in [0,8]");
   SyncArgs a{};
   for (int i = 0; i < world; ++i) { a.grads[i] = grads[i]; a.flags[i] = flags[i]; }
-  a.param = param; a.begin = begin; a.end = end; a.param_off = param_off; a.alpha = alpha;
-  a.rank = rank; a.world = world; a.epoch = epoch; a.local_sync = local_sync;
+  size_t total = 0;
+  a.nseg = nseg;
+  for (int s = 0; s < nseg; ++s) {
+    DTFE_REQUIRE(seg_end[s] >= seg_begin[s], "dtfe_sync_rs_apply_f32: bad range in segment %d", s);
+    a.param[s] = seg_param[s]; a.begin[s] = seg_begin[s]; a.end[s] = seg_end[s];
+    total += seg_end[s] - seg_begin[s];
+  }
+  a.alpha = alpha; a.rank = rank; a.world = world; a.epoch = epoch; a.local_sync = local_sync;
   a.global_step = global_step_or_null;
   // All CTAs must be co-resident (they wait on block 0): cap at one wave and launch cooperatively.
-  int grid = grid_for(end - begin, 8);
+  int grid = grid_for(total, 8);
   if (grid > 148) grid = 148;
   void* args[] = {&a};
   DTFE_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)k_sync_rs_apply, dim3(grid), dim3(256), args, 0,

@@ -40,8 +40,8 @@ _SIGS = {
     "dtfe_push_sgd_bf16": ([_P, _P, c_size_t, c_float, _P], c_int),
     "dtfe_pull_f32": ([_P, _P, c_size_t, _P], c_int),
     "dtfe_adam_apply_f32": ([_P, _P, _P, _P, c_size_t, c_float, c_float, c_float, c_float, c_float, _P], c_int),
-    "dtfe_sync_rs_apply_f32": ([POINTER(_P), POINTER(_P), c_int, c_int, _P, c_size_t, c_size_t, c_size_t, c_float,
-                                c_uint, _P, _P, _P], c_int),
+    "dtfe_sync_rs_apply_f32": ([POINTER(_P), POINTER(_P), c_int, c_int, c_int, POINTER(_P), POINTER(c_size_t),
+                                POINTER(c_size_t), c_float, c_uint, _P, _P, _P], c_int),
     "dtfe_sync_max_ranks": ([], c_int),
     "dtfe_mlp2_step_grid": ([c_int, c_int], c_int),
     "dtfe_mlp2_step_workspace_words": ([c_int, c_int, c_int, c_int, c_int], c_size_t),
@@ -265,14 +265,19 @@ def adam_apply(param, m, v, slot, lr_t: float, beta1: float, beta2: float, eps: 
                                     lr_t, beta1, beta2, eps, grad_scale, _stream()), "dtfe_adam_apply_f32")
 
 
-def sync_rs_apply(grad_ptrs: Sequence[int], flag_ptrs: Sequence[int], rank: int, world: int, param: torch.Tensor,
-                  begin: int, end: int, param_off: int, alpha: float, epoch: int, local_sync: torch.Tensor,
+def sync_rs_apply(grad_ptrs: Sequence[int], flag_ptrs: Sequence[int], rank: int, world: int,
+                  segments: Sequence, alpha: float, epoch: int, local_sync: torch.Tensor,
                   global_step: Optional[torch.Tensor]):
-    """Synchronous SGD: reduce-scatter of all workers' gradients fused with the apply."""
+    """Synchronous SGD: reduce-scatter of all workers' gradients fused with the apply.
+    ``segments``: (param_tensor, begin, end) for every variable this rank owns."""
     G = (_P * world)(*grad_ptrs)
     F = (_P * world)(*flag_ptrs)
-    check(lib().dtfe_sync_rs_apply_f32(G, F, rank, world, param.data_ptr(), begin, end, param_off, alpha, epoch,
-                                       local_sync.data_ptr(), _ptr(global_step), _stream()), "dtfe_sync_rs_apply_f32")
+    n = len(segments)
+    P = (_P * max(n, 1))(*[t.data_ptr() for t, _, _ in segments])
+    Bg = (c_size_t * max(n, 1))(*[b for _, b, _ in segments])
+    En = (c_size_t * max(n, 1))(*[e for _, _, e in segments])
+    check(lib().dtfe_sync_rs_apply_f32(G, F, rank, world, n, P, Bg, En, alpha, epoch, local_sync.data_ptr(),
+                                       _ptr(global_step), _stream()), "dtfe_sync_rs_apply_f32")
 
 
 # --------------------------------------------------------------------------------------

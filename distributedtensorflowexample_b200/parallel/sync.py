@@ -1,0 +1,90 @@
+"""Synchronous SGD over peer memory (no counterpart in the reference, which is async
+only - the semantic model is TF1's SyncReplicasOptimizer: aggregate all replicas' gradients, apply the
+mean once, global_step += 1 per aggregated update).
+
+Each rank keeps a flat fp32 gradient buffer in IPC-exportable memory.  After its backward pass has
+written the buffer, every rank launches ``dtfe_sync_rs_apply_f32`` once: barrier on flags in peer
+memory -> each owner reduces the slices of the variables it owns out of all ranks' buffers (peer
+loads over NVLink) and applies ``-lr/W * sum`` in place in its shard -> barrier.  That is a
+reduce-scatter fused with the update; there is no all-gather because the next forward reads the
+parameters from the owners' shards anyway (the fused pull).  One rank per GPU.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional, Sequence
+
+import torch
+import torch.distributed as dist
+
+from ..ops import cuda_ops as ops
+from .ps import PeerParamStore
+
+
+class SyncGroup:
+    def __init__(self, store: PeerParamStore, trainable_names: Sequence[str], rank: int, world: int,
+                 owner_of_shard=lambda k, world: k % world):
+        self.store, self.rank, self.world = store, rank, world
+        self.device = store.device
+        self.names = list(trainable_names)
+        # flat layout of the gradient vector: every variable starts on a 4-element boundary
+        self.ranges: Dict[str, tuple] = {}
+        n = 0
+        for name in self.names:
+            numel = store.tensor(name).numel()
+            self.ranges[name] = (n, n + numel)
+            n = (n + numel + 3) // 4 * 4
+        self.total = n
+        max_ranks = ops.lib().dtfe_sync_max_ranks()
+        with torch.cuda.device(self.device):
+            self._grad_ptr = ops.shard_alloc(max(self.total, 4) * 4)
+            self._flag_ptr = ops.shard_alloc(2 * max_ranks * 4)
+        self.gradbuf = ops.tensor_from_ptr(self._grad_ptr, (max(self.total, 4),), torch.float32, self.device, owner=self)
+        self.local_sync = torch.zeros(4, dtype=torch.int32, device=self.device)
+        self.epoch = 0
+        # exchange IPC handles
+        mine = (ops.ipc_export(self._grad_ptr), ops.ipc_export(self._flag_ptr))
+        self._opened: List[int] = []
+        if world > 1:
+            allh = [None] * world
+            dist.all_gather_object(allh, mine)
+            self.grad_ptrs, self.flag_ptrs = [], []
+            with torch.cuda.device(self.device):
+                for r, (gh, fh) in enumerate(allh):
+                    if r == rank:
+                        self.grad_ptrs.append(self._grad_ptr); self.flag_ptrs.append(self._flag_ptr)
+                    else:
+                        g, f = ops.ipc_open(gh), ops.ipc_open(fh)
+                        self._opened += [g, f]
+                        self.grad_ptrs.append(g); self.flag_ptrs.append(f)
+            dist.barrier()
+        else:
+            self.grad_ptrs, self.flag_ptrs = [self._grad_ptr], [self._flag_ptr]
+        # segments this rank owns
+        self.segments = []
+        for name in self.names:
+            if owner_of_shard(store.shard_of(name), world) == rank:
+                b, e = self.ranges[name]
+                self.segments.append((store.tensor(name).view(-1), b, e))
+        gs_owner = owner_of_shard(store.shard_of("global/global_step"), world)
+        self.global_step = store.tensor("global/global_step") if gs_owner == rank else None
+
+    def grad_views(self, shapes: Dict[str, tuple]) -> List[torch.Tensor]:
+        """Per-variable views into the flat gradient buffer, in ``names`` order."""
+        out = []
+        for name in self.names:
+            b, e = self.ranges[name]
+            out.append(self.gradbuf[b:e].view(*shapes[name]))
+        return out
+
+    def reduce_scatter_apply(self, lr: float) -> None:
+        self.epoch += 1
+        ops.sync_rs_apply(self.grad_ptrs, self.flag_ptrs, self.rank, self.world, self.segments,
+                          -lr / self.world, self.epoch, self.local_sync, self.global_step)
+
+    def close(self) -> None:
+        for p in self._opened:
+            try:
+                ops.ipc_close(p)
+            except Exception:
+                pass
+        self._opened = []

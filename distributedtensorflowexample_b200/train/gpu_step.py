@@ -22,9 +22,9 @@ class DeviceDataset:
     dataset rows of the next ``nsteps`` batches with TF1 ``DataSet.next_batch`` semantics (reshuffle at
     every epoch boundary, straddling batches take the rest of the old epoch first)."""
 
-    def __init__(self, images, label_ids, device, seed: Optional[int] = None):
+    def __init__(self, images, label_ids, device, seed: Optional[int] = None, dtype=torch.float32):
         self.device = torch.device(device)
-        self.images = torch.as_tensor(images, dtype=torch.float32).to(self.device).contiguous()
+        self.images = torch.as_tensor(images, dtype=torch.float32).to(self.device).to(dtype).contiguous()
         self.labels = torch.as_tensor(label_ids, dtype=torch.int32).to(self.device).contiguous()
         self.n = self.images.shape[0]
         self._gen = torch.Generator(device=self.device)

@@ -16,7 +16,7 @@ import numpy as np
 import torch
 
 from ..models.mlp import MLPSpec
-from .gpu_step import DeviceDataset, FusedMlp2Stepper, LayerwiseStepper
+from .gpu_step import DeviceDataset, FusedMlp2Stepper, LayerwiseStepper, TcStepper
 
 
 class GpuTrainer:
@@ -29,7 +29,10 @@ class GpuTrainer:
         self.global_step = global_step
         self.steps_per_launch = max(1, steps_per_launch)
         if engine == "auto":
-            engine = "fused" if FusedMlp2Stepper.supports(spec, batch) else "layerwise"
+            if spec.param_dtype == "bfloat16":
+                engine = "tc"
+            else:
+                engine = "fused" if FusedMlp2Stepper.supports(spec, batch) else "layerwise"
         self.engine = engine
         self.launch_count = 0
         if engine == "fused":
@@ -39,8 +42,12 @@ class GpuTrainer:
         elif engine == "layerwise":
             self.fused = None
             self.layer = LayerwiseStepper(spec, batch, self.params, global_step, lr, self.device, atomic=atomic)
+        elif engine == "tc":
+            self.fused = None
+            self.layer = TcStepper(spec, batch, self.params, global_step, lr, self.device)
         else:
             raise ValueError(engine)
+        self.input_dtype = torch.bfloat16 if engine == "tc" else torch.float32
         # host-fed path state
         self._copy_stream: Optional[torch.cuda.Stream] = None
         self._stage: List[Tuple[torch.Tensor, torch.Tensor, torch.cuda.Event, torch.cuda.Event]] = []
@@ -87,7 +94,7 @@ class GpuTrainer:
         self._copy_stream = torch.cuda.Stream(device=self.device)
         D = self.spec.dims[0]
         for _ in range(2):
-            self._stage.append((torch.empty(self.batch, D, device=self.device, dtype=torch.float32),
+            self._stage.append((torch.empty(self.batch, D, device=self.device, dtype=self.input_dtype),
                                 torch.empty(self.batch, device=self.device, dtype=torch.int32),
                                 torch.cuda.Event(), torch.cuda.Event()))
         self._host_out = torch.zeros(ring, 3, dtype=torch.float32).pin_memory()
@@ -122,13 +129,20 @@ class GpuTrainer:
         return row
 
     def h2d_bytes_per_step(self) -> int:
-        return self.batch * self.spec.dims[0] * 4 + self.batch * 4
+        return self.batch * self.spec.dims[0] * (2 if self.input_dtype == torch.bfloat16 else 4) + self.batch * 4
 
     def d2h_bytes_per_step(self) -> int:
         return 4
 
     # ---- evaluation ------------------------------------------------------------------
     def evaluate(self, X: torch.Tensor, labels: torch.Tensor) -> float:
+        if isinstance(self.layer, TcStepper):
+            correct = total = 0
+            B = self.batch
+            for s in range(0, X.shape[0] - B + 1, B):           # whole batches (buffers are batch-sized)
+                self.layer.run(X[s:s + B].to(torch.bfloat16), labels[s:s + B], train=False)
+                correct += int(round(self.layer.acc.item() * B)); total += B
+            return correct / max(total, 1)
         correct, total = self.layer.eval_counts(X, labels)
         return float(correct.item()) / float(total)
 

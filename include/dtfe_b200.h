@@ -91,12 +91,12 @@ int dtfe_pull_f32(float* dst, const float* shard, size_t n, void* stream);
  * (no counterpart in the reference, which only has GradientDescentOptimizer, worker.py:71). */
 int dtfe_adam_apply_f32(float* param, float* m, float* v, float* slot, size_t n, float lr_t, float beta1,
                         float beta2, float eps, float grad_scale, void* stream);
-/* Synchronous SGD: every rank reduces ITS slice [begin,end) of all ranks' gradient buffers out of
- * peer memory and applies it in place; flag barriers in peer memory on entry and exit.  One rank per
+/* Synchronous SGD: every rank reduces the flat-gradient ranges [seg_begin,seg_end) of the variables it
+ * owns out of all ranks' gradient buffers in peer memory and applies them in place (seg_param); flag barriers in peer memory on entry and exit.  One rank per
  * GPU (the kernel spins on peers).  No counterpart in the reference (async only); semantic model is
  * TF1 SyncReplicasOptimizer. */
-int dtfe_sync_rs_apply_f32(const float* const* grads, unsigned* const* flags, int rank, int world,
-                           float* param, size_t begin, size_t end, size_t param_off, float alpha,
+int dtfe_sync_rs_apply_f32(const float* const* grads, unsigned* const* flags, int rank, int world, int nseg,
+                           float* const* seg_param, const size_t* seg_begin, const size_t* seg_end, float alpha,
                            unsigned epoch, unsigned* local_sync, int* global_step_or_null, void* stream);
 int dtfe_sync_max_ranks(void);
 

@@ -1,0 +1,99 @@
+"""Run under torchrun with >= 2 GPUs (spawned by tests/test_gpu_multi.py):
+  async : 2 workers push lossless red.add updates into shards on both GPUs - conservation check;
+  sync  : reduce-scatter+apply over peer memory == single-process large-batch SGD."""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from distributedtensorflowexample_b200.data import synthetic_arrays
+from distributedtensorflowexample_b200.models import oracle
+from distributedtensorflowexample_b200.models.mlp import reference_mlp_spec
+from distributedtensorflowexample_b200.parallel.spmd import build_spmd_store
+from distributedtensorflowexample_b200.parallel.sync import SyncGroup
+from distributedtensorflowexample_b200.train.gpu_step import LayerwiseStepper, FusedMlp2Stepper
+
+
+def main():
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
+    dev = torch.device("cuda", int(os.environ["LOCAL_RANK"]))
+    dist.init_process_group("nccl", device_id=dev)
+    spec = reference_mlp_spec()
+    B, lr = 100, 0.05
+    x, y = synthetic_arrays(4000, seed=7)
+    X = torch.tensor(x, device=dev); Y = torch.tensor(y.astype(np.int32), device=dev)
+
+    # ---------------- sync: must equal one worker with the concatenated batch -----------------
+    model, store = build_spmd_store(spec, rank, world, dev, seed=3)
+    names = [v.name for v in model.global_trainable]
+    p0 = [store.read(n).astype(np.float64) for n in names]
+    sg = SyncGroup(store, names, rank, world)
+    shapes = {n: tuple(store.tensor(n).shape) for n in names}
+    st = LayerwiseStepper(spec, B, [store.tensor(n) for n in names], store.tensor("global/global_step"), lr, dev,
+                          grad_buffers=sg.grad_views(shapes))
+    nsteps = 5
+    for s in range(nsteps):
+        rows = slice((s * world + rank) * B, (s * world + rank + 1) * B)
+        st.run(X[rows], Y[rows])
+        sg.reduce_scatter_apply(lr)
+    torch.cuda.synchronize(); dist.barrier()
+    ref = [p.copy() for p in p0]
+    for s in range(nsteps):
+        rows = slice(s * world * B, (s + 1) * world * B)
+        oracle.sgd_step(ref, x[rows].astype(np.float64), y[rows].astype(np.int64), lr)
+    for n, r in zip(names, ref):
+        np.testing.assert_allclose(store.read(n), r, rtol=1e-3, atol=2e-4, err_msg=f"sync {n}")
+    assert store.read("global/global_step").item() == nsteps, store.read("global/global_step")
+    dist.barrier()
+    sg.close(); store.close()
+
+    # ---------------- async: conservation of pushed deltas with exact arithmetic ---------------
+    model, store = build_spmd_store(spec, rank, world, dev, seed=4)
+    from distributedtensorflowexample_b200.ops import cuda_ops as ops
+    for n in names:                      # power-of-two test values: fp32 adds are exact, order cannot matter
+        if rank == 0:
+            store.tensor(n).zero_()
+    dist.barrier()
+    reps = 64
+    for n in names:
+        t = store.tensor(n).view(-1)
+        g = torch.full_like(t, 0.25 * (rank + 1)) if t.device == dev else None
+        g = torch.full((t.numel(),), 0.25 * (rank + 1), device=dev)
+        for _ in range(reps):
+            ops.push_sgd(t, g, -1.0, atomic=True)
+    torch.cuda.synchronize(); dist.barrier()
+    expect = -reps * 0.25 * sum(r + 1 for r in range(world))
+    for n in names:
+        got = store.read(n)
+        assert np.all(got == expect), (n, got.min(), got.max(), expect)
+    dist.barrier()
+
+    # ---------------- async training with the fused kernel over remote shards --------------------
+    if rank == 0:
+        store.initialize(np.random.default_rng(1))
+    dist.barrier()
+    f = FusedMlp2Stepper(spec, B, [store.tensor(n) for n in names], store.tensor("global/global_step"), lr, dev,
+                         max_steps_per_launch=20, remote=True)
+    idx = torch.randint(0, 4000, (20 * B,), device=dev, dtype=torch.int32)
+    gs0 = 0
+    for it in range(3):
+        f.run(X, Y, nsteps=20, batch_idx=idx)
+    torch.cuda.synchronize(); dist.barrier()
+    assert store.read("global/global_step").item() == 3 * 20 * world        # global_step == sum of pushes
+    loss = f.loss[:20].cpu().numpy()
+    assert np.isfinite(loss).all() and loss[-1] < 9.0
+    steps_seen = f.step[:20].cpu().numpy()
+    assert (np.diff(steps_seen) > 0).all()                                   # strictly increasing observations
+    dist.barrier()
+    store.close()
+    if rank == 0:
+        print("MULTIGPU_OK")
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

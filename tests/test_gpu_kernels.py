@@ -137,9 +137,9 @@ def test_sync_rs_apply_single_rank():
     flags = torch.zeros(2 * ops.lib().dtfe_sync_max_ranks(), device="cuda", dtype=torch.int32)
     local_sync = torch.zeros(4, device="cuda", dtype=torch.int32)
     gs = torch.zeros(1, device="cuda", dtype=torch.int32)
-    ops.sync_rs_apply([grads.data_ptr()], [flags.data_ptr()], 0, 1, param, 0, n, 0, -0.1, 1, local_sync, gs)
+    ops.sync_rs_apply([grads.data_ptr()], [flags.data_ptr()], 0, 1, [(param[:1000], 0, 1000), (param[1000:], 1000, n)], -0.1, 1, local_sync, gs)
     torch.testing.assert_close(param.double(), ref, rtol=1e-6, atol=1e-6)
     assert gs.item() == 1
-    ops.sync_rs_apply([grads.data_ptr()], [flags.data_ptr()], 0, 1, param, 0, n, 0, -0.1, 2, local_sync, gs)
+    ops.sync_rs_apply([grads.data_ptr()], [flags.data_ptr()], 0, 1, [(param, 0, n)], -0.1, 2, local_sync, gs)
     torch.testing.assert_close(param.double(), ref - 0.1 * grads.double(), rtol=1e-6, atol=1e-5)
     assert gs.item() == 2
