@@ -89,6 +89,7 @@ __device__ __forceinline__ void push1(float* p, float v, int atomic) {
 
 template <int KS>
 __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
+  static_assert(KS % 4 == 0 && KS <= 16, "KS must be 4, 8, 12 or 16");
   extern __shared__ __align__(16) float smem[];
   const int B = a.B, D = a.D, H = a.H, C = a.C;
   const int HP = H;  // row pitch of H-wide smem tiles
@@ -103,6 +104,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
   float* red = dzs + 2 * kMaxC;           // [256]
   float* dZs = red + kThreads;            // [B][C]
   float* dAs = dZs + kMaxB * kMaxC;       // [B][H]  (phase C)
+  (void)red;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const unsigned G = gridDim.x;
@@ -111,53 +113,90 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
   unsigned bar_target = 0;
   const float invB = 1.f / (float)B;
 
+  // ---- software prefetch state -------------------------------------------------------------------
+  // Batch rows are data dependent (index -> row), i.e. two chained global loads.  Indices are fetched
+  // two steps ahead and the X slice one step ahead, so neither latency is ever on the critical path.
+  constexpr int kXPer = (kMaxB * KS + kThreads - 1) / kThreads;
+  float xnext[kXPer];
+  long rownext[kXPer];
+  auto fetch_rows = [&](int st) {
+#pragma unroll
+    for (int i = 0; i < kXPer; ++i) {
+      int e = tid + i * kThreads;
+      long row = 0;
+      if (e < B * KS && st < a.nsteps) {
+        int r = e / KS;
+        row = a.batch_idx ? (long)__ldg(a.batch_idx + (long)st * B + r) : (long)st * a.rows_per_step + r;
+      }
+      rownext[i] = row;
+    }
+  };
+  auto fetch_x = [&](int st) {   // consumes rownext (rows of step st)
+#pragma unroll
+    for (int i = 0; i < kXPer; ++i) {
+      int e = tid + i * kThreads;
+      float v = 0.f;
+      if (e < B * KS && st < a.nsteps) {
+        int k = k0 + e % KS;
+        if (k < D) v = __ldg(a.X + rownext[i] * a.ldx + k);
+      }
+      xnext[i] = v;
+    }
+  };
+  fetch_rows(0);
+  fetch_x(0);
+  fetch_rows(1);
+
+  const int slot = tid >> 7, t = tid & 127, wq = warp & 3;   // phase B roles: 2 rows per CTA, 4 warps each
+
   for (int s = 0; s < a.nsteps; ++s) {
     // ------------------------------ phase A ------------------------------------
     DBG_STAMP(0);
-    for (int e = tid; e < B * KS; e += kThreads) {
-      int r = e / KS, kk = e % KS;
-      long row = a.batch_idx ? (long)a.batch_idx[(long)s * B + r] : (long)s * a.rows_per_step + r;
-      int k = k0 + kk;
-      Xs[e] = (k < D) ? __ldg(a.X + row * a.ldx + k) : 0.f;
+#pragma unroll
+    for (int i = 0; i < kXPer; ++i) {
+      int e = tid + i * kThreads;
+      if (e < B * KS) Xs[e] = xnext[i];
     }
     for (int e = tid; e < KS * H; e += kThreads) {
       int kk = e / H, j = e % H;
       int k = k0 + kk;
       Ws[kk * HP + j] = (k < D) ? dtfe::ld_relaxed_sys(a.W1 + (long)k * H + j) : 0.f;
     }
+    // label of the first row this thread's slot handles in phase B (latency hidden behind phase A)
+    int ylab = 0;
+    {
+      int r = 2 * g + slot;
+      if (r < B) {
+        long row = a.batch_idx ? (long)__ldg(a.batch_idx + (long)s * B + r) : (long)s * a.rows_per_step + r;
+        ylab = __ldg(a.labels + row);
+      }
+    }
     __syncthreads();
     {
-      float acc[16][4];
+      // W slice in registers once; X rows as broadcast float4 loads: KS/4 + 0 shared loads per 4*KS FMAs
+      float w[KS][4];
 #pragma unroll
-      for (int i = 0; i < 16; ++i)
-#pragma unroll
-        for (int jj = 0; jj < 4; ++jj) acc[i][jj] = 0.f;
-#pragma unroll
-      for (int kk = 0; kk < KS; ++kk) {
-        float wv[4];
+      for (int kk = 0; kk < KS; ++kk)
 #pragma unroll
         for (int jj = 0; jj < 4; ++jj) {
           int j = lane + 32 * jj;
-          wv[jj] = (j < H) ? Ws[kk * HP + j] : 0.f;
+          w[kk][jj] = (j < H) ? Ws[kk * HP + j] : 0.f;
         }
-#pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          int r = warp + 8 * i;
-          float xv = (r < B) ? Xs[r * KS + kk] : 0.f;
-#pragma unroll
-          for (int jj = 0; jj < 4; ++jj) acc[i][jj] = fmaf(xv, wv[jj], acc[i][jj]);
-        }
-      }
       float* P = a.part + (long)g * B * H;
+      for (int r = warp; r < B; r += 8) {
+        float x[KS];
 #pragma unroll
-      for (int i = 0; i < 16; ++i) {
-        int r = warp + 8 * i;
-        if (r < B) {
+        for (int q = 0; q < KS / 4; ++q) {
+          float4 v = *reinterpret_cast<const float4*>(Xs + r * KS + 4 * q);
+          x[4 * q] = v.x; x[4 * q + 1] = v.y; x[4 * q + 2] = v.z; x[4 * q + 3] = v.w;
+        }
 #pragma unroll
-          for (int jj = 0; jj < 4; ++jj) {
-            int j = lane + 32 * jj;
-            if (j < H) __stcg(P + (long)r * H + j, acc[i][jj]);
-          }
+        for (int jj = 0; jj < 4; ++jj) {
+          float acc = 0.f;
+#pragma unroll
+          for (int kk = 0; kk < KS; ++kk) acc = fmaf(x[kk], w[kk][jj], acc);
+          int j = lane + 32 * jj;
+          if (j < H) __stcg(P + (long)r * H + j, acc);
         }
       }
     }
@@ -166,75 +205,115 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
     DBG_STAMP(2);
 
     // ------------------------------ phase B ------------------------------------
-    // Small parameters are read after the barrier so that every CTA sees the pushes
-    // all CTAs made in the previous step's phase C.
-    for (int e = tid; e < H * C; e += kThreads) W2s[e] = dtfe::ld_relaxed_sys(a.W2 + e);
-    if (tid < H) b1s[tid] = dtfe::ld_relaxed_sys(a.b1 + tid);
-    if (tid < C) b2s[tid] = dtfe::ld_relaxed_sys(a.b2 + tid);
-    __syncthreads();
-    {
-      const int slot = tid >> 7, t = tid & 127, wq = warp & 3;
-      for (int r0 = 2 * g; r0 < B; r0 += 2 * (int)G) {
-        const int r = r0 + slot;
-        const bool rv = r < B;
-        float h = 0.f;
-        if (rv && t < H) {
-          float z = b1s[t];
-          const float* P = a.part + (long)r * H + t;
-          const long gs = (long)B * H;
-          unsigned q = 0;
-          for (; q + 8 <= G; q += 8) {
-            float v[8];
+    // Next step's X slice and the rows after that: issued now, consumed a whole step later.
+    fetch_x(s + 1);
+    fetch_rows(s + 2);
+    // Small parameters are read after the barrier so that every CTA sees the pushes all CTAs made in
+    // the previous step's phase C.  They go to registers first; the reduction loads below are issued
+    // before anything waits, so all of it shares one L2 round trip.
+    constexpr int kW2Per = (kMaxH * kMaxC + kThreads - 1) / kThreads;
+    float w2r[kW2Per];
 #pragma unroll
-            for (int u = 0; u < 8; ++u) v[u] = __ldcg(P + (long)(q + u) * gs);
+    for (int i = 0; i < kW2Per; ++i) {
+      int e = tid + i * kThreads;
+      w2r[i] = (e < H * C) ? dtfe::ld_relaxed_sys(a.W2 + e) : 0.f;
+    }
+    float b1r = (tid < H) ? dtfe::ld_relaxed_sys(a.b1 + tid) : 0.f;
+    float b2r = (tid < C) ? dtfe::ld_relaxed_sys(a.b2 + tid) : 0.f;
+    bool params_in_smem = false;
+    for (int r0 = 2 * g; r0 < B || !params_in_smem; r0 += 2 * (int)G) {
+      const int r = r0 + slot;
+      const bool rv = r < B;
+      float z = 0.f;
+      if (rv && t < H) {
+        const float* P = a.part + (long)r * H + t;
+        const long gs = (long)B * H;
+        // G independent loads: two batches of 16 in flight so the L2 latency is paid about once
+        float z0 = 0.f, z1 = 0.f, z2 = 0.f, z3 = 0.f;
+        unsigned q = 0;
+        float cur[16];
+        const unsigned nb = G / 16;
+        if (nb > 0) {
 #pragma unroll
-            for (int u = 0; u < 8; ++u) z += v[u];
-          }
-          for (; q < G; ++q) z += __ldcg(P + (long)q * gs);
-          h = dtfe::sigmoidf_fast(z);
-          hs[slot * kMaxH + t] = h;
-          __stcg(a.Hbuf + (long)r * H + t, h);
-        }
-        __syncthreads();
-        for (int c = wq; c < C; c += 4) {
-          float p = 0.f;
-          for (int u = lane; u < H; u += 32) p = fmaf(hs[slot * kMaxH + u], W2s[u * C + c], p);
-          p = dtfe::warp_sum(p);
-          if (lane == 0) zs[slot * kMaxC + c] = p + b2s[c];
-        }
-        __syncthreads();
-        if (wq == 0 && rv) {
-          float z = (lane < C) ? zs[slot * kMaxC + lane] : -INFINITY;
-          float mx = z; int am = (lane < C) ? lane : 0x7fffffff;
+          for (int u = 0; u < 16; ++u) cur[u] = __ldcg(P + (long)u * gs);
+          for (unsigned bi = 1; bi <= nb; ++bi) {
+            float nxt[16];
+            if (bi < nb) {
 #pragma unroll
-          for (int o = 16; o > 0; o >>= 1) {
-            float om = __shfl_xor_sync(0xffffffffu, mx, o);
-            int oa = __shfl_xor_sync(0xffffffffu, am, o);
-            if (om > mx || (om == mx && oa < am)) { mx = om; am = oa; }
+              for (int u = 0; u < 16; ++u) nxt[u] = __ldcg(P + (long)(bi * 16 + u) * gs);
+            }
+#pragma unroll
+            for (int u = 0; u < 16; u += 4) { z0 += cur[u]; z1 += cur[u + 1]; z2 += cur[u + 2]; z3 += cur[u + 3]; }
+            if (bi < nb) {
+#pragma unroll
+              for (int u = 0; u < 16; ++u) cur[u] = nxt[u];
+            }
           }
-          float ex = (lane < C) ? __expf(z - mx) : 0.f;
-          float se = dtfe::warp_sum(ex);
-          long row = a.batch_idx ? (long)a.batch_idx[(long)s * B + r] : (long)s * a.rows_per_step + r;
-          int y = a.labels[row];
-          float zy = __shfl_sync(0xffffffffu, z, y);
-          if (lane < C) {
-            float dz = (ex / se - (lane == y ? 1.f : 0.f)) * invB;
-            dzs[slot * kMaxC + lane] = dz;
-            __stcg(a.dZ + (long)r * C + lane, dz);
-          }
-          if (lane == 0) {
-            __stcg(a.rowloss + r, mx + __logf(se) - zy);
-            __stcg(a.rowcorrect + r, (am == y) ? 1 : 0);
-          }
+          q = nb * 16;
         }
-        __syncthreads();
-        if (rv && t < H) {
-          float dh = 0.f;
-          for (int c = 0; c < C; ++c) dh = fmaf(dzs[slot * kMaxC + c], W2s[t * C + c], dh);
-          __stcg(a.dA + (long)r * H + t, dh * h * (1.f - h));
-        }
-        __syncthreads();
+        for (; q < G; ++q) z0 += __ldcg(P + (long)q * gs);
+        z = (z0 + z1) + (z2 + z3);
       }
+      if (!params_in_smem) {
+#pragma unroll
+        for (int i = 0; i < kW2Per; ++i) {
+          int e = tid + i * kThreads;
+          if (e < H * C) W2s[e] = w2r[i];
+        }
+        if (tid < H) b1s[tid] = b1r;
+        if (tid < C) b2s[tid] = b2r;
+        params_in_smem = true;
+      }
+      __syncthreads();
+      if (r0 >= B) break;                    // CTA without rows: parameters staged, nothing else to do
+      float h = 0.f;
+      if (rv && t < H) {
+        h = dtfe::sigmoidf_fast(z + b1s[t]);
+        hs[slot * kMaxH + t] = h;
+        __stcg(a.Hbuf + (long)r * H + t, h);
+      }
+      __syncthreads();
+      for (int c = wq; c < C; c += 4) {
+        float p = 0.f;
+        for (int u = lane; u < H; u += 32) p = fmaf(hs[slot * kMaxH + u], W2s[u * C + c], p);
+        p = dtfe::warp_sum(p);
+        if (lane == 0) zs[slot * kMaxC + c] = p + b2s[c];
+      }
+      __syncthreads();
+      if (wq == 0 && rv) {
+        float zc = (lane < C) ? zs[slot * kMaxC + lane] : -INFINITY;
+        float mx = zc; int am = (lane < C) ? lane : 0x7fffffff;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+          float om = __shfl_xor_sync(0xffffffffu, mx, o);
+          int oa = __shfl_xor_sync(0xffffffffu, am, o);
+          if (om > mx || (om == mx && oa < am)) { mx = om; am = oa; }
+        }
+        float ex = (lane < C) ? __expf(zc - mx) : 0.f;
+        float se = dtfe::warp_sum(ex);
+        int y = ylab;
+        if (r0 != 2 * g) {                   // later rounds (B > 2*G): fetch the label now
+          long row = a.batch_idx ? (long)a.batch_idx[(long)s * B + r] : (long)s * a.rows_per_step + r;
+          y = a.labels[row];
+        }
+        float zy = __shfl_sync(0xffffffffu, zc, y);
+        if (lane < C) {
+          float dz = (ex / se - (lane == y ? 1.f : 0.f)) * invB;
+          dzs[slot * kMaxC + lane] = dz;
+          __stcg(a.dZ + (long)r * C + lane, dz);
+        }
+        if (lane == 0) {
+          __stcg(a.rowloss + r, mx + __logf(se) - zy);
+          __stcg(a.rowcorrect + r, (am == y) ? 1 : 0);
+        }
+      }
+      __syncthreads();
+      if (rv && t < H) {
+        float dh = 0.f;
+        for (int c = 0; c < C; ++c) dh = fmaf(dzs[slot * kMaxC + c], W2s[t * C + c], dh);
+        __stcg(a.dA + (long)r * H + t, dh * h * (1.f - h));
+      }
+      __syncthreads();
     }
     DBG_STAMP(3);
     grid_barrier(a.sync, bar_target, G);
@@ -255,58 +334,109 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
     }
     if (a.train) {
       const float nlr = -a.lr;
+      // Small-gradient duty of this warp: hidden unit t = g + G*(warp/2) (+ 4G per extra round);
+      // even warps produce the dW2 row, odd warps db1.  The H column an even warp needs is requested
+      // now, so its L2 latency hides behind the dA load and the dW1 loop.
+      const int pair = warp >> 1;
+      const int t_first = g + (int)G * pair;
+      float hcol[4] = {0.f, 0.f, 0.f, 0.f};
+      if ((warp & 1) == 0 && t_first < H) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          int b = lane + 32 * i;
+          if (b < B) hcol[i] = __ldcg(a.Hbuf + (long)b * H + t_first);
+        }
+      }
       for (int e = tid; e < (B * H) / 4; e += kThreads)
         reinterpret_cast<float4*>(dAs)[e] = __ldcg(reinterpret_cast<const float4*>(a.dA) + e);
       for (int e = (B * H) / 4 * 4 + tid; e < B * H; e += kThreads) dAs[e] = __ldcg(a.dA + e);
       for (int e = tid; e < B * C; e += kThreads) dZs[e] = __ldcg(a.dZ + e);
       __syncthreads();
-      // dW1 rows [k0, k0+KS): warp <-> row (KS=8) or two rows (KS=16); lanes <-> columns
-      for (int kk = warp; kk < KS; kk += 8) {
-        int k = k0 + kk;
-        if (k >= D) break;
-        float acc[4] = {0.f, 0.f, 0.f, 0.f};
-        for (int b = 0; b < B; ++b) {
-          float xv = Xs[b * KS + kk];
-#pragma unroll
-          for (int jj = 0; jj < 4; ++jj) {
-            int j = lane + 32 * jj;
-            float d = (j < H) ? dAs[b * HP + j] : 0.f;
-            acc[jj] = fmaf(xv, d, acc[jj]);
+      {
+        // dW1 rows [k0, k0+KS): a warp owns 4 consecutive rows (one broadcast float4 of X per batch row)
+        // and a contiguous block of columns, so each dA value fetched from shared memory feeds 4 FMAs.
+        constexpr int kGroups = KS / 4, kParts = 8 / kGroups;
+        const int grp = warp % kGroups, part = warp / kGroups;
+        const int cq = (H + kParts - 1) / kParts;          // columns per part (<= 64)
+        const int j0 = part * cq + lane, j1 = j0 + 32;
+        const bool v0 = lane < cq && j0 < H, v1 = lane + 32 < cq && j1 < H;
+        float acc0[4] = {0.f, 0.f, 0.f, 0.f}, acc1[4] = {0.f, 0.f, 0.f, 0.f};
+        float bcc0[4] = {0.f, 0.f, 0.f, 0.f}, bcc1[4] = {0.f, 0.f, 0.f, 0.f};
+        const float* xp = Xs + grp * 4;
+        int b = 0;
+        for (; b + 2 <= B; b += 2) {          // two independent chains
+          float4 xa = *reinterpret_cast<const float4*>(xp + b * KS);
+          float4 xb = *reinterpret_cast<const float4*>(xp + (b + 1) * KS);
+          float da0 = v0 ? dAs[b * HP + j0] : 0.f, db0 = v0 ? dAs[(b + 1) * HP + j0] : 0.f;
+          acc0[0] = fmaf(xa.x, da0, acc0[0]); acc0[1] = fmaf(xa.y, da0, acc0[1]);
+          acc0[2] = fmaf(xa.z, da0, acc0[2]); acc0[3] = fmaf(xa.w, da0, acc0[3]);
+          bcc0[0] = fmaf(xb.x, db0, bcc0[0]); bcc0[1] = fmaf(xb.y, db0, bcc0[1]);
+          bcc0[2] = fmaf(xb.z, db0, bcc0[2]); bcc0[3] = fmaf(xb.w, db0, bcc0[3]);
+          if (kParts < 4) {                   // wide parts (KS = 16): a second column per lane
+            float da1 = v1 ? dAs[b * HP + j1] : 0.f, db1 = v1 ? dAs[(b + 1) * HP + j1] : 0.f;
+            acc1[0] = fmaf(xa.x, da1, acc1[0]); acc1[1] = fmaf(xa.y, da1, acc1[1]);
+            acc1[2] = fmaf(xa.z, da1, acc1[2]); acc1[3] = fmaf(xa.w, da1, acc1[3]);
+            bcc1[0] = fmaf(xb.x, db1, bcc1[0]); bcc1[1] = fmaf(xb.y, db1, bcc1[1]);
+            bcc1[2] = fmaf(xb.z, db1, bcc1[2]); bcc1[3] = fmaf(xb.w, db1, bcc1[3]);
+          }
+        }
+        for (; b < B; ++b) {
+          float4 xa = *reinterpret_cast<const float4*>(xp + b * KS);
+          float da0 = v0 ? dAs[b * HP + j0] : 0.f;
+          acc0[0] = fmaf(xa.x, da0, acc0[0]); acc0[1] = fmaf(xa.y, da0, acc0[1]);
+          acc0[2] = fmaf(xa.z, da0, acc0[2]); acc0[3] = fmaf(xa.w, da0, acc0[3]);
+          if (kParts < 4) {
+            float da1 = v1 ? dAs[b * HP + j1] : 0.f;
+            acc1[0] = fmaf(xa.x, da1, acc1[0]); acc1[1] = fmaf(xa.y, da1, acc1[1]);
+            acc1[2] = fmaf(xa.z, da1, acc1[2]); acc1[3] = fmaf(xa.w, da1, acc1[3]);
           }
         }
 #pragma unroll
-        for (int jj = 0; jj < 4; ++jj) {
-          int j = lane + 32 * jj;
-          if (j < H) push1(a.W1 + (long)k * H + j, nlr * acc[jj], a.atomic);
+        for (int q = 0; q < 4; ++q) {
+          int k = k0 + grp * 4 + q;
+          if (k < D) {
+            if (v0) push1(a.W1 + (long)k * H + j0, nlr * (acc0[q] + bcc0[q]), a.atomic);
+            if (kParts < 4 && v1) push1(a.W1 + (long)k * H + j1, nlr * (acc1[q] + bcc1[q]), a.atomic);
+          }
         }
       }
-      // small gradients: hidden unit t handled by CTA t % G
-      for (int t = g; t < H; t += (int)G) {
-        if (warp == 0) {  // dW2[t][:] = sum_b H[b][t] * dZ[b][:]
+      // small gradients
+      for (int tt = t_first; tt < H; tt += 4 * (int)G) {
+        if ((warp & 1) == 0) {  // dW2[tt][:] = sum_b H[b][tt] * dZ[b][:]
+          if (tt != t_first) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              int b = lane + 32 * i;
+              hcol[i] = (b < B) ? __ldcg(a.Hbuf + (long)b * H + tt) : 0.f;
+            }
+          }
           float accc[kMaxC];
 #pragma unroll
           for (int c = 0; c < kMaxC; ++c) accc[c] = 0.f;
-          for (int b = lane; b < B; b += 32) {
-            float hv = __ldcg(a.Hbuf + (long)b * H + t);
 #pragma unroll
-            for (int c = 0; c < kMaxC; ++c)
-              if (c < C) accc[c] = fmaf(hv, dZs[b * C + c], accc[c]);
+          for (int i = 0; i < 4; ++i) {
+            int b = lane + 32 * i;
+            if (b < B) {
+#pragma unroll
+              for (int c = 0; c < kMaxC; ++c)
+                if (c < C) accc[c] = fmaf(hcol[i], dZs[b * C + c], accc[c]);
+            }
           }
 #pragma unroll
           for (int c = 0; c < kMaxC; ++c) {
             if (c < C) {
               float v = dtfe::warp_sum(accc[c]);
-              if (lane == 0) push1(a.W2 + (long)t * C + c, nlr * v, a.atomic);
+              if (lane == 0) push1(a.W2 + (long)tt * C + c, nlr * v, a.atomic);
             }
           }
-        } else if (warp == 1) {  // db1[t] = sum_b dA[b][t]
+        } else {  // db1[tt] = sum_b dA[b][tt]
           float v = 0.f;
-          for (int b = lane; b < B; b += 32) v += dAs[b * HP + t];
+          for (int b = lane; b < B; b += 32) v += dAs[b * HP + tt];
           v = dtfe::warp_sum(v);
-          if (lane == 0) push1(a.b1 + t, nlr * v, a.atomic);
+          if (lane == 0) push1(a.b1 + tt, nlr * v, a.atomic);
         }
       }
-      if (g == (int)G - 1 && warp == 2) {  // db2[c] = sum_b dZ[b][c]
+      if (g == (int)G - 1 && warp == 7) {  // db2[c] = sum_b dZ[b][c]
         for (int c = 0; c < C; ++c) {
           float v = 0.f;
           for (int b = lane; b < B; b += 32) v += dZs[b * C + c];
@@ -456,4 +586,77 @@ DTFE_API int dtfe_mlp2_step_noalloc(const dtfe_mlp2_launch* launch, void* stream
   // sync words have to start at zero; every other region is written before it is read.
   DTFE_CUDA_CHECK(cudaMemsetAsync(a.sync, 0, 4 * sizeof(unsigned), (cudaStream_t)stream));
   return L.ks == 8 ? mlp2_launch<8>(a, (cudaStream_t)stream) : mlp2_launch<16>(a, (cudaStream_t)stream);
+}
+
+// ---- host-fed training loop (the reference's feed_dict path, worker.py:133-137) -----------------
+// One call runs `nsteps` steps, each fed by its own batch in pinned host memory: the H2D copies go
+// through a private copy stream into two staging buffers (batch i+1 is copied while batch i
+// trains), the step kernel waits on the copy's event, and the step's loss is copied back D2H on the
+// compute stream.  Doing the loop here instead of in Python keeps the per-step host cost at a few
+// microseconds of driver calls.
+namespace {
+struct HostFeed {
+  int B, D, dev;
+  float* xs[2];
+  int* ys[2];
+  cudaStream_t copy;
+  cudaEvent_t copied[2], consumed[2];
+};
+}  // namespace
+
+DTFE_API int dtfe_hostfeed_create(int B, int D, void** out) {
+  DTFE_REQUIRE(B >= 1 && D >= 1, "dtfe_hostfeed_create: bad shape");
+  HostFeed* h = new HostFeed();
+  h->B = B; h->D = D;
+  DTFE_CUDA_CHECK(cudaGetDevice(&h->dev));
+  for (int i = 0; i < 2; ++i) {
+    DTFE_CUDA_CHECK(cudaMalloc(&h->xs[i], (size_t)B * D * sizeof(float)));
+    DTFE_CUDA_CHECK(cudaMalloc(&h->ys[i], (size_t)B * sizeof(int)));
+    DTFE_CUDA_CHECK(cudaEventCreateWithFlags(&h->copied[i], cudaEventDisableTiming));
+    DTFE_CUDA_CHECK(cudaEventCreateWithFlags(&h->consumed[i], cudaEventDisableTiming));
+  }
+  DTFE_CUDA_CHECK(cudaStreamCreateWithFlags(&h->copy, cudaStreamNonBlocking));
+  *out = h;
+  return 0;
+}
+
+DTFE_API int dtfe_hostfeed_destroy(void* handle) {
+  HostFeed* h = static_cast<HostFeed*>(handle);
+  if (!h) return 0;
+  for (int i = 0; i < 2; ++i) {
+    cudaFree(h->xs[i]); cudaFree(h->ys[i]);
+    cudaEventDestroy(h->copied[i]); cudaEventDestroy(h->consumed[i]);
+  }
+  cudaStreamDestroy(h->copy);
+  delete h;
+  return 0;
+}
+
+// launch: B/D/H/C/ks, parameter pointers, workspace, lr, atomic, train, remote are used; X/labels/
+// batch_idx/nsteps are supplied per step from the host batches.  loss_host (pinned, [nsteps]) receives
+// one float per step; launch->acc_out / step_out keep the last step's values on the device.
+DTFE_API int dtfe_mlp2_train_host(void* handle, const dtfe_mlp2_launch* launch, const float* const* x_host,
+                                  const int* const* y_host, int nsteps, float* loss_host, void* stream) {
+  HostFeed* h = static_cast<HostFeed*>(handle);
+  DTFE_REQUIRE(h != nullptr, "dtfe_mlp2_train_host: null feed handle");
+  DTFE_REQUIRE(launch->B == h->B && launch->D == h->D, "dtfe_mlp2_train_host: feed was created for B=%d D=%d", h->B, h->D);
+  cudaStream_t st = (cudaStream_t)stream;
+  Mlp2Launch L = *launch;
+  L.nsteps = 1; L.batch_idx = nullptr; L.rows_per_step = 0; L.ldx = h->D; L.dbg = nullptr;
+  Mlp2Args a{};
+  for (int i = 0; i < nsteps; ++i) {
+    const int s = i & 1;
+    DTFE_CUDA_CHECK(cudaStreamWaitEvent(h->copy, h->consumed[s], 0));
+    DTFE_CUDA_CHECK(cudaMemcpyAsync(h->xs[s], x_host[i], (size_t)h->B * h->D * sizeof(float), cudaMemcpyHostToDevice, h->copy));
+    DTFE_CUDA_CHECK(cudaMemcpyAsync(h->ys[s], y_host[i], (size_t)h->B * sizeof(int), cudaMemcpyHostToDevice, h->copy));
+    DTFE_CUDA_CHECK(cudaEventRecord(h->copied[s], h->copy));
+    DTFE_CUDA_CHECK(cudaStreamWaitEvent(st, h->copied[s], 0));
+    L.X = h->xs[s]; L.labels = h->ys[s];
+    if (int rc = mlp2_fill(L, a)) return rc;
+    int rc = L.ks == 8 ? mlp2_launch<8>(a, st) : mlp2_launch<16>(a, st);
+    if (rc) return rc;
+    DTFE_CUDA_CHECK(cudaEventRecord(h->consumed[s], st));
+    DTFE_CUDA_CHECK(cudaMemcpyAsync(loss_host + i, L.loss_out, sizeof(float), cudaMemcpyDeviceToHost, st));
+  }
+  return 0;
 }

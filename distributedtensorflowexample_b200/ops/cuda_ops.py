@@ -46,6 +46,9 @@ _SIGS = {
     "dtfe_mlp2_step_grid": ([c_int, c_int], c_int),
     "dtfe_mlp2_step_workspace_words": ([c_int, c_int, c_int, c_int, c_int], c_size_t),
     "dtfe_mlp2_step": ([_P, _P], c_int),
+    "dtfe_hostfeed_create": ([c_int, c_int, POINTER(_P)], c_int),
+    "dtfe_hostfeed_destroy": ([_P], c_int),
+    "dtfe_mlp2_train_host": ([_P, _P, POINTER(_P), POINTER(_P), c_int, _P, _P], c_int),
 }
 
 _lib = None
@@ -312,6 +315,47 @@ class Mlp2Step:
         self.acc = torch.zeros(max_steps, dtype=torch.float32, device=self.device)
         self.step = torch.zeros(max_steps, dtype=torch.int32, device=self.device)
         self.grid = lib().dtfe_mlp2_step_grid(D, ks)
+
+    def _launch_struct(self, W1, b1, W2, b2, global_step, lr, atomic, train, remote, out_offset=0):
+        L = _Mlp2Launch()
+        L.B, L.D, L.H, L.C, L.ks = self.B, self.D, self.H, self.C, self.ks
+        L.W1, L.b1, L.W2, L.b2 = W1.data_ptr(), b1.data_ptr(), W2.data_ptr(), b2.data_ptr()
+        L.global_step = global_step.data_ptr()
+        L.workspace = self.workspace.data_ptr()
+        L.loss_out = self.loss.data_ptr() + 4 * out_offset
+        L.acc_out = self.acc.data_ptr() + 4 * out_offset
+        L.step_out = self.step.data_ptr() + 4 * out_offset
+        L.lr, L.atomic, L.train, L.remote = lr, int(atomic), int(train), int(remote)
+        return L
+
+    def train_host(self, W1, b1, W2, b2, global_step, x_host, y_host, loss_host, lr: float, atomic: bool = True,
+                   remote: bool = True):
+        """Native host-fed loop: ``x_host``/``y_host`` are lists of pinned CPU tensors (one batch per step),
+        ``loss_host`` a pinned float32 tensor with one slot per step."""
+        if getattr(self, "_feed", None) is None:
+            h = _P()
+            with torch.cuda.device(self.device):
+                check(lib().dtfe_hostfeed_create(self.B, self.D, ctypes.byref(h)), "dtfe_hostfeed_create")
+            self._feed = h
+        n = len(x_host)
+        for x, y in zip(x_host, y_host):
+            if not (x.is_pinned() and y.is_pinned() and x.dtype == torch.float32 and y.dtype == torch.int32
+                    and x.is_contiguous() and tuple(x.shape) == (self.B, self.D)):
+                raise TypeError("host batches must be pinned, contiguous float32 [B,D] / int32 [B] tensors")
+        if not loss_host.is_pinned() or loss_host.numel() < n:
+            raise TypeError("loss_host must be a pinned float32 tensor with one element per step")
+        XP = (_P * n)(*[x.data_ptr() for x in x_host])
+        YP = (_P * n)(*[y.data_ptr() for y in y_host])
+        L = self._launch_struct(W1, b1, W2, b2, global_step, lr, atomic, True, remote)
+        check(lib().dtfe_mlp2_train_host(self._feed, ctypes.byref(L), XP, YP, n, loss_host.data_ptr(), _stream()),
+              "dtfe_mlp2_train_host")
+
+    def __del__(self):
+        try:
+            if getattr(self, "_feed", None) is not None:
+                lib().dtfe_hostfeed_destroy(self._feed)
+        except Exception:
+            pass
 
     def run(self, W1, b1, W2, b2, global_step, X, labels, lr: float, nsteps: int = 1, batch_idx=None,
             rows_per_step: int = 0, atomic: bool = True, train: bool = True, out_offset: int = 0,

@@ -128,6 +128,22 @@ class GpuTrainer:
         row[0:1].copy_(loss_t[0:1], non_blocking=True)
         return row
 
+    def train_host_batches(self, x_list, y_list, loss_host: torch.Tensor) -> torch.Tensor:
+        """Feed ``len(x_list)`` batches from pinned host memory, one training step each (the reference's
+        ``sess.run(train_op, feed_dict=...)`` loop, worker.py:133-137), with the loop itself in native code
+        when the fused engine is active.  ``loss_host[i]`` (pinned) holds step i's loss once the stream has
+        drained."""
+        if self.fused is not None:
+            W1, b1, W2, b2 = self.params
+            self.fused.k.train_host(W1, b1, W2, b2, self.global_step, x_list, y_list, loss_host, self.lr,
+                                    atomic=self.fused.atomic, remote=self.fused.remote)
+            self.launch_count += len(x_list)
+        else:
+            for i, (x, y) in enumerate(zip(x_list, y_list)):
+                row = self.train_host_batch(x, y, out_index=i)
+                loss_host[i:i + 1].copy_(self.layer.loss, non_blocking=True)
+        return loss_host
+
     def h2d_bytes_per_step(self) -> int:
         return self.batch * self.spec.dims[0] * (2 if self.input_dtype == torch.bfloat16 else 4) + self.batch * 4
 

@@ -120,6 +120,15 @@ int dtfe_mlp2_step_grid(int D, int ks);
 size_t dtfe_mlp2_step_workspace_words(int B, int D, int H, int C, int ks);
 int dtfe_mlp2_step(const dtfe_mlp2_launch* launch, void* stream);
 
+/* Host-fed loop (the reference's feed_dict path, worker.py:133-137): `nsteps` steps, step i fed from the
+ * pinned host buffers x_host[i] ([B,D] fp32) / y_host[i] ([B] int32) through double-buffered staging
+ * and a private copy stream; the loss of step i is copied back to loss_host[i] (pinned).  The feed
+ * handle owns the staging buffers, events and copy stream. */
+int dtfe_hostfeed_create(int B, int D, void** out);
+int dtfe_hostfeed_destroy(void* handle);
+int dtfe_mlp2_train_host(void* handle, const dtfe_mlp2_launch* launch, const float* const* x_host,
+                         const int* const* y_host, int nsteps, float* loss_host, void* stream);
+
 /* dtfe_mlp2_step for callers that cannot allocate device memory (no counterpart in the reference).
  * Some users of this library have no way to get a workspace: a worker that lives inside a fixed
  * fraction of a shared GPU, a host program whose own memory pool already owns the device, or code

@@ -131,13 +131,22 @@ def test_trainer_device_and_host_paths_agree():
     spec = reference_mlp_spec()
     x, y = _data(2000)
     outs = []
-    for mode in ("device", "host"):
+    for mode in ("device", "host", "host_native"):
         model, store, names = _store(spec, seed=11)
         tr = GpuTrainer(spec, 100, 0.01, [store.tensor(n) for n in names], store.tensor("global/global_step"),
                         "cuda:0", steps_per_launch=5)
         ds = DeviceDataset(x, y, "cuda:0", seed=7)
         if mode == "device":
             tr.train_device_steps(ds, 10)
+        elif mode == "host_native":
+            xs, ys = [], []
+            for s in range(10):
+                rows = ds.next_indices(100, 1).cpu().long()
+                xs.append(torch.tensor(x)[rows].contiguous().pin_memory()); ys.append(torch.tensor(y)[rows].contiguous().pin_memory())
+            losses = torch.zeros(10).pin_memory()
+            tr.train_host_batches(xs, ys, losses)
+            torch.cuda.synchronize()
+            assert torch.isfinite(losses).all() and losses[0] > 0
         else:
             xp = torch.tensor(x).pin_memory(); yp = torch.tensor(y).pin_memory()
             for s in range(10):
@@ -148,6 +157,7 @@ def test_trainer_device_and_host_paths_agree():
         torch.cuda.synchronize()
         outs.append([store.read(n) for n in names] + [store.read("global/global_step")])
         store.close()
-    for a, b in zip(*outs):
-        np.testing.assert_allclose(a, b, rtol=1e-5, atol=1e-6)
+    for other in outs[1:]:
+        for a, b in zip(outs[0], other):
+            np.testing.assert_allclose(a, b, rtol=1e-5, atol=1e-6)
     assert outs[0][-1].item() == 10
