@@ -92,7 +92,7 @@ def run(args, rank, world, dev) -> int:
     idx = torch.randint(0, n - B, (K + Wm,), generator=torch.Generator().manual_seed(rank)).tolist()
 
     use_graph = os.environ.get("DTFE_BASELINE_GRAPH") == "1"
-    xs, ys = torch.empty(B, dims[0], device=dev, dtype=dtype), torch.empty(B, device=dev, dtype=torch.int32)
+    xs, ys = torch.zeros(B, dims[0], device=dev, dtype=dtype), torch.zeros(B, device=dev, dtype=torch.int32)
     graph = None
     if use_graph:
         s = torch.cuda.Stream()

@@ -356,6 +356,193 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CU
   }
 }
 
+// ---------------------------------------------------------------- 2-CTA persistent kernel
+// cta_group::2: a cluster of two CTAs (one TPC) computes a 256 x BN2 tile.  Each CTA stages its own 128
+// rows of A and its own half of B (BN2/2 rows), the leader CTA issues tcgen05.mma.cta_group::2 which reads
+// both CTAs' shared memory and writes 128 accumulator rows into each CTA's TMEM.  Shared-memory traffic
+// per FLOP is half of the 1-CTA 128x128 kernel's.  The kernel is persistent (clusters stride over the
+// tiles) and the accumulator is double-buffered in TMEM (2 x 256 columns), so the epilogue of tile i
+// overlaps the MMAs of tile i+1.
+constexpr int BN2 = 256;
+constexpr int kStages2 = 6;
+constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;   // clears the CTA-rank bit of a shared::cluster address
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tma_load_2d_2sm(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
+  // completes on the LEADER CTA's barrier (rank bit cleared), whichever CTA issues it
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      :: "r"(smem_u32(smem_dst)), "l"(map), "r"(smem_u32(bar) & kPeerBitMask), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void umma_bf16_2sm(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum) : "memory");
+}
+__device__ __forceinline__ void umma_commit_2sm(uint64_t* bar) {
+  // arrives on the barrier at this offset in BOTH CTAs of the pair
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+               :: "r"(smem_u32(bar)), "h"((uint16_t)3) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_leader(uint64_t* bar) {
+  // arrive on the leader CTA's copy of `bar` from either CTA
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];"
+               :: "r"(smem_u32(bar) & kPeerBitMask) : "memory");
+}
+__device__ __forceinline__ void tmem_alloc_2sm(uint32_t* smem_holder, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;"
+               :: "r"(smem_u32(smem_holder)), "r"(ncols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_2sm(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" :: "r"(taddr), "r"(ncols) : "memory");
+}
+
+template <int A_MN, int B_MN, int EPI>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+k_gemm_tc2(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, GemmTcArgs g) {
+  constexpr uint32_t A_BYTES = BM * BK * 2;            // this CTA's 128 rows of A
+  constexpr uint32_t B_BYTES = (BN2 / 2) * BK * 2;     // this CTA's half of B
+  constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;  // 32 KB
+  constexpr uint32_t BOX_BYTES = 64 * BK * 2;
+  constexpr uint32_t TMEM_COLS = 2 * BN2;              // two accumulator stages
+
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  __shared__ __align__(8) uint64_t full_bar[kStages2];
+  __shared__ __align__(8) uint64_t empty_bar[kStages2];
+  __shared__ __align__(8) uint64_t tmem_full_bar[2];
+  __shared__ __align__(8) uint64_t tmem_empty_bar[2];
+  __shared__ uint32_t tmem_base_holder;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  const int num_kb = (g.K + BK - 1) / BK;
+  const int tiles_m = (g.M + 2 * BM - 1) / (2 * BM), tiles_n = (g.N + BN2 - 1) / BN2;
+  const int num_tiles = tiles_m * tiles_n;
+  const int cluster_id = blockIdx.x >> 1, num_clusters = gridDim.x >> 1;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_a);
+    tma_prefetch_desc(&tmap_b);
+#pragma unroll
+    for (int s = 0; s < kStages2; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+#pragma unroll
+    for (int s = 0; s < 2; ++s) { mbar_init(&tmem_full_bar[s], 1); mbar_init(&tmem_empty_bar[s], 8); }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc_2sm(&tmem_base_holder, TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();            // barriers of both CTAs initialised before any cross-CTA signal
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_holder;
+
+  if (warp == 0) {
+    // ===================== TMA producer (both CTAs) =====================
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+        const int m0 = (tile % tiles_m) * (2 * BM) + (int)rank * BM;      // this CTA's rows of A / D
+        const int n0 = (tile / tiles_m) * BN2 + (int)rank * (BN2 / 2);    // this CTA's half of B
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem + (size_t)stage * STAGE_BYTES;
+          uint8_t* sb = sa + A_BYTES;
+          if (leader) mbar_expect_tx(&full_bar[stage], 2 * STAGE_BYTES);   // both CTAs' bytes land on the leader
+          const int k0 = kb * BK;
+          if (A_MN) {
+#pragma unroll
+            for (int b = 0; b < BM / 64; ++b) tma_load_2d_2sm(sa + b * BOX_BYTES, &tmap_a, &full_bar[stage], m0 + b * 64, k0);
+          } else {
+            tma_load_2d_2sm(sa, &tmap_a, &full_bar[stage], k0, m0);
+          }
+          if (B_MN) {
+#pragma unroll
+            for (int b = 0; b < (BN2 / 2) / 64; ++b) tma_load_2d_2sm(sb + b * BOX_BYTES, &tmap_b, &full_bar[stage], n0 + b * 64, k0);
+          } else {
+            tma_load_2d_2sm(sb, &tmap_b, &full_bar[stage], k0, n0);
+          }
+          if (++stage == kStages2) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (leader CTA only) =====================
+    if (leader && lane == 0) {
+      constexpr uint32_t idesc = make_idesc(2 * BM, BN2, A_MN, B_MN);
+      int stage = 0; uint32_t phase = 0;
+      int as = 0; uint32_t aphase = 0;
+      for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+        mbar_wait(&tmem_empty_bar[as], aphase ^ 1);      // both CTAs' epilogues drained this accumulator
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + (uint32_t)(as * BN2);
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + (size_t)stage * STAGE_BYTES);
+          const uint32_t sb = sa + A_BYTES;
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            const uint64_t adesc = A_MN ? make_smem_desc(sa + k * (UMMA_K * 128), BOX_BYTES, 1024)
+                                        : make_smem_desc(sa + k * (UMMA_K * 2), 16, 1024);
+            const uint64_t bdesc = B_MN ? make_smem_desc(sb + k * (UMMA_K * 128), BOX_BYTES, 1024)
+                                        : make_smem_desc(sb + k * (UMMA_K * 2), 16, 1024);
+            umma_bf16_2sm(tmem_d, adesc, bdesc, idesc, (kb | k) != 0);
+          }
+          umma_commit_2sm(&empty_bar[stage]);            // frees the stage in both CTAs
+          if (++stage == kStages2) { stage = 0; phase ^= 1; }
+        }
+        umma_commit_2sm(&tmem_full_bar[as]);             // accumulator ready, both CTAs' epilogues
+        if (++as == 2) { as = 0; aphase ^= 1; }
+      }
+    }
+  } else {
+    // ===================== epilogue (warps 2..5, both CTAs) =====================
+    const int q = warp & 3;
+    int as = 0; uint32_t aphase = 0;
+    for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+      const int m0 = (tile % tiles_m) * (2 * BM) + (int)rank * BM;
+      const int n0 = (tile / tiles_m) * BN2;
+      mbar_wait(&tmem_full_bar[as], aphase);
+      tc_fence_after();
+      const int m = m0 + q * 32 + lane;
+#pragma unroll 1
+      for (int c = 0; c < BN2; c += 32) {
+        uint32_t r[32];
+        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN2 + c), r);
+        tmem_ld_wait();
+        if (m < g.M && n0 + c < g.N) epilogue_chunk<EPI>(g, m, n0 + c, r);
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_leader(&tmem_empty_bar[as]);
+      if (++as == 2) { as = 0; aphase ^= 1; }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();            // nobody exits (or frees TMEM) while its peer may still signal it
+  if (warp == 1) {
+    __syncwarp();
+    tc_fence_after();
+    tmem_dealloc_2sm(tmem_base, TMEM_COLS);
+  }
+}
+
 // ---------------------------------------------------------------- host side
 typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                     const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -411,6 +598,48 @@ int launch_cfg(const CUtensorMap& ta, const CUtensorMap& tb, const GemmTcArgs& g
   return 0;
 }
 
+template <int A_MN, int B_MN, int EPI>
+int launch_cfg2(const CUtensorMap& ta, const CUtensorMap& tb, const GemmTcArgs& g, cudaStream_t stream) {
+  constexpr size_t smem = (size_t)kStages2 * (BM * BK * 2 + (BN2 / 2) * BK * 2) + 1024;
+  auto kern = k_gemm_tc2<A_MN, B_MN, EPI>;
+  static bool configured[64] = {};
+  static int sm_count[64] = {};
+  int dev;
+  DTFE_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 64 && !configured[dev]) {
+    DTFE_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    DTFE_CUDA_CHECK(cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev));
+    configured[dev] = true;
+  }
+  int tiles = ((g.M + 2 * BM - 1) / (2 * BM)) * ((g.N + BN2 - 1) / BN2);
+  int clusters = (dev < 64 ? sm_count[dev] : 148) / 2;
+  if (clusters > tiles) clusters = tiles;
+  kern<<<dim3(2 * clusters), kThreads, smem, stream>>>(ta, tb, g);
+  DTFE_LAUNCH_CHECK();
+  return 0;
+}
+
+template <int EPI>
+int launch_major2(int a_mn, int b_mn, const CUtensorMap& ta, const CUtensorMap& tb, const GemmTcArgs& g,
+                  cudaStream_t s) {
+  if (!a_mn && b_mn) return launch_cfg2<0, 1, EPI>(ta, tb, g, s);
+  if (!a_mn && !b_mn) return launch_cfg2<0, 0, EPI>(ta, tb, g, s);
+  if (a_mn && b_mn) return launch_cfg2<1, 1, EPI>(ta, tb, g, s);
+  return launch_cfg2<1, 0, EPI>(ta, tb, g, s);
+}
+
+int launch_epi2(int epi, int a_mn, int b_mn, const CUtensorMap& ta, const CUtensorMap& tb, const GemmTcArgs& g,
+                cudaStream_t s) {
+  switch (epi) {
+    case EPI_STORE: return launch_major2<EPI_STORE>(a_mn, b_mn, ta, tb, g, s);
+    case EPI_BIAS_ACT: return launch_major2<EPI_BIAS_ACT>(a_mn, b_mn, ta, tb, g, s);
+    case EPI_ACTGRAD: return launch_major2<EPI_ACTGRAD>(a_mn, b_mn, ta, tb, g, s);
+    case EPI_PUSH: return launch_major2<EPI_PUSH>(a_mn, b_mn, ta, tb, g, s);
+  }
+  dtfe_set_error("gemm_tc: unknown epilogue %d", epi);
+  return -1;
+}
+
 template <int BN, int EPI>
 int launch_major(int a_mn, int b_mn, const CUtensorMap& ta, const CUtensorMap& tb, const GemmTcArgs& g,
                  cudaStream_t s) {
@@ -440,8 +669,12 @@ int launch_epi(int epi, int a_mn, int b_mn, const CUtensorMap& ta, const CUtenso
 //   b_mn_major = 0: B is [N][ldb] (K contiguous);  1: B is [K][ldb] (N contiguous)
 DTFE_API int dtfe_gemm_tc_bf16(const dtfe_gemm_tc* p, void* stream) {
   DTFE_REQUIRE(p->M > 0 && p->N > 0 && p->K > 0, "gemm_tc: empty problem");
-  DTFE_REQUIRE(p->tile_n == 128 || p->tile_n == 256 || p->tile_n == 0, "gemm_tc: tile_n must be 0, 128 or 256");
-  int bn = p->tile_n ? p->tile_n : (p->N >= 2048 ? 256 : 128);
+  DTFE_REQUIRE(p->tile_n == 128 || p->tile_n == 256 || p->tile_n == 0 || p->tile_n == 512,
+               "gemm_tc: tile_n must be 0 (auto), 128, 256 (1-CTA kernels) or 512 (= 2-CTA 256x256 persistent kernel)");
+  // auto: the 2-CTA kernel whenever the problem has at least one full 256x256 tile per SM pair
+  const bool two_cta = p->tile_n == 512 ||
+                       (p->tile_n == 0 && p->M >= 512 && p->N >= 512 && (long)p->M * p->N >= 256L * 256L * 74);
+  int bn = two_cta ? 128 : (p->tile_n ? p->tile_n : (p->N >= 2048 ? 256 : 128));   // B box rows: 128 = half of BN2
   CUtensorMap ta, tb;
   int rc;
   if (p->a_mn_major) rc = make_tmap(&ta, p->A, (uint64_t)p->M, (uint64_t)p->K, (uint64_t)p->lda, 64, BK);
@@ -458,6 +691,7 @@ DTFE_API int dtfe_gemm_tc_bf16(const dtfe_gemm_tc* p, void* stream) {
   g.alpha = p->alpha; g.act = p->act; g.G = p->G; g.ldg = p->ldg;
   if (p->epilogue == EPI_ACTGRAD) DTFE_REQUIRE(p->H != nullptr, "gemm_tc: EPI_ACTGRAD needs H");
   if (p->epilogue != EPI_PUSH) DTFE_REQUIRE(p->D != nullptr, "gemm_tc: D is null");
+  if (two_cta) return launch_epi2(p->epilogue, p->a_mn_major, p->b_mn_major, ta, tb, g, (cudaStream_t)stream);
   return bn == 256 ? launch_epi<256>(p->epilogue, p->a_mn_major, p->b_mn_major, ta, tb, g, (cudaStream_t)stream)
                    : launch_epi<128>(p->epilogue, p->a_mn_major, p->b_mn_major, ta, tb, g, (cudaStream_t)stream);
 }

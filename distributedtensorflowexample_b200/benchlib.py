@@ -49,6 +49,8 @@ def run_mnist(args, rank: int, world: int, dev, ClockSampler) -> int:
     # every step gathers 100 random rows of it, so inputs never sit in L2 from the previous step.
     x, y = synthetic_arrays(55000, seed=1234 + rank)
     ds = DeviceDataset(x, y.astype(np.int32), dev, seed=rank)
+    if args.mode == "sync":
+        return _run_mnist_sync(args, rank, world, dev, ClockSampler, spec, model, store, names, ds, x, y, B, lr, K, W)
     engine = args.engine if args.engine != "tc" else "layerwise"
     tr = GpuTrainer(spec, B, lr, params, gs, dev, steps_per_launch=spl, engine=engine,
                     remote=not store.all_local())
@@ -121,6 +123,52 @@ def run_mnist(args, rank: int, world: int, dev, ClockSampler) -> int:
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+    return 0
+
+
+def _run_mnist_sync(args, rank, world, dev, ClockSampler, spec, model, store, names, ds, x, y, B, lr, K, W) -> int:
+    """Synchronous SGD: layer-wise kernels write gradients to a peer-visible buffer, then ONE kernel per
+    rank does barrier + reduce-scatter + apply + barrier over peer memory (parallel/sync.py)."""
+    from .parallel.sync import SyncGroup
+    from .train.gpu_step import LayerwiseStepper
+    sg = SyncGroup(store, names, rank, world)
+    shapes = {n: tuple(store.tensor(n).shape) for n in names}
+    st = LayerwiseStepper(spec, B, [store.tensor(n) for n in names], store.tensor("global/global_step"), lr, dev,
+                          grad_buffers=sg.grad_views(shapes))
+    idx = ds.next_indices(B, K + W).long()
+
+    def step(i):
+        rows = idx[i * B:(i + 1) * B]
+        st.run(ds.images.index_select(0, rows), ds.labels.index_select(0, rows))
+        sg.reduce_scatter_apply(lr)
+
+    for i in range(W):
+        step(i)
+    _barrier(world)
+    clocks = ClockSampler(dev.index or 0)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    clocks.start()
+    e0.record()
+    for i in range(K):
+        step(W + i)
+    e1.record()
+    torch.cuda.synchronize()
+    clk = clocks.stop()
+    ms = _max_over_ranks(e0.elapsed_time(e1), world, dev)
+    _barrier(world)
+    out = {"metric": METRIC, "value": world * B * K / (ms * 1e-3), "unit": "examples/sec", "n_gpus": world,
+           "steps": K, "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak",
+           "vs_baseline": None, "dtype": "fp32", "data": "synthetic", "impl": "ours",
+           "config": {"model": "MNIST MLP 784-100-10", "global_batch": B * world, "batch_per_worker": B,
+                      "parallelism": f"sync-ps dp{world}: reduce-scatter fused with apply over peer memory",
+                      "engine": "layerwise fp32 + sync_rs_apply"},
+           "gpu_launches": (st.launches_per_call + 1) * K, "clocks": clk,
+           "global_step_after": int(store.tensor("global/global_step").item())}
+    if rank == 0:
+        print(json.dumps(out), flush=True)
+    sg.close(); store.close()
+    if world > 1:
+        dist.barrier(); dist.destroy_process_group()
     return 0
 
 

@@ -37,7 +37,7 @@ cases = [
 for name, flops, ours, ref in cases:
     t_ref = timeit(ref, flush=flush)
     r = {"case": name, "torch_ms": round(t_ref, 4), "torch_tflops": round(flops / t_ref / 1e9, 1)}
-    for tn in (128, 256):
+    for tn in (128, 256, 512):
         t = timeit(lambda: ours(tn), flush=flush)
         r[f"ours_bn{tn}_ms"] = round(t, 4)
         r[f"ours_bn{tn}_tflops"] = round(flops / t / 1e9, 1)

@@ -17,8 +17,8 @@ def _check(out, ref, K):
     assert err <= 1e-2 * scale + tol * 0 + 2e-2 * (1 if out.dtype == torch.bfloat16 else 0) * scale, (err, scale)
 
 
-@pytest.mark.parametrize("tile_n", [128, 256])
-@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (256, 256, 256), (100, 100, 784), (300, 520, 200), (1024, 1024, 1024)])
+@pytest.mark.parametrize("tile_n", [128, 256, 512])
+@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (256, 256, 256), (100, 100, 784), (300, 520, 200), (1024, 1024, 1024), (2048, 1536, 520)])
 @pytest.mark.parametrize("a_mn,b_mn", [(0, 0), (0, 1), (1, 1), (1, 0)])
 def test_gemm_tc_store_all_majors(M, N, K, a_mn, b_mn, tile_n):
     from distributedtensorflowexample_b200.ops import gemm_tc as G
