@@ -673,8 +673,9 @@ DTFE_API int dtfe_gemm_tc_bf16(const dtfe_gemm_tc* p, void* stream) {
                "gemm_tc: tile_n must be 0 (auto), 128, 256 (1-CTA kernels) or 512 (= 2-CTA 256x256 persistent kernel)");
   // auto: the 2-CTA kernel whenever the problem has at least one full 256x256 tile per SM pair
   const bool two_cta = p->tile_n == 512 ||
-                       (p->tile_n == 0 && p->M >= 512 && p->N >= 512 && (long)p->M * p->N >= 256L * 256L * 74);
-  int bn = two_cta ? 128 : (p->tile_n ? p->tile_n : (p->N >= 2048 ? 256 : 128));   // B box rows: 128 = half of BN2
+                       (p->tile_n == 0 && p->M >= 512 && p->N >= 512 && p->K >= 1024 &&
+                        (long)p->M * p->N >= 256L * 256L * 74);
+  int bn = two_cta ? 128 : (p->tile_n ? p->tile_n : 128);   // B box rows: 128 = half of BN2
   CUtensorMap ta, tb;
   int rc;
   if (p->a_mn_major) rc = make_tmap(&ta, p->A, (uint64_t)p->M, (uint64_t)p->K, (uint64_t)p->lda, 64, BK);
