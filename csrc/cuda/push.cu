@@ -101,21 +101,60 @@ struct SyncArgs {
   unsigned epoch;                 // strictly increasing per call, starts at 1
   unsigned* local_sync;           // [4] u32 in local HBM: {go, done_count, _, _}
   int* global_step;               // non-null on the owner of shard 0
+  const unsigned* abort_flag;     // optional: a peer-visible word that turns non-zero when a rank leaves
+  unsigned long long timeout_ns;  // give up spinning after this long (0 = never)
 };
 
+__device__ __forceinline__ unsigned long long gtimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+// Spin until *flag >= epoch.  Returns false if the wait was abandoned: a rank announced it is leaving
+// (abort_flag, e.g. the shard header's stop word set by a worker's signal path) or the timeout expired.
+// An abandoned wait must never hang the GPU: the kernel then skips the update and reports it.
+__device__ __forceinline__ bool spin_until(const unsigned* flag, unsigned epoch, const SyncArgs& a,
+                                           unsigned long long t0) {
+  unsigned it = 0;
+  while (dtfe::ld_acquire_sys(flag) < epoch) {
+    __nanosleep(20);
+    if ((++it & 0x3ff) == 0) {
+      if (a.abort_flag && dtfe::ld_acquire_sys(a.abort_flag) != 0) return false;
+      if (a.timeout_ns && gtimer_ns() - t0 > a.timeout_ns) return false;
+    }
+  }
+  return true;
+}
+
 __global__ void __launch_bounds__(256) k_sync_rs_apply(SyncArgs a) {
+  // local_sync words: [0] go (epoch once all gradients are in, 0xffffffff on abort) [1] done count
+  //                   [2] abort status of the last call (0 ok, 1 entry barrier, 2 exit barrier)
+  const unsigned long long t0 = gtimer_ns();
   // (a) arrive: tell every peer "my gradients for this epoch are complete", then wait for all.
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     __threadfence_system();
     for (int p = 0; p < a.world; ++p) dtfe::st_release_sys(a.flags[p] + a.rank, a.epoch);
-    for (int q = 0; q < a.world; ++q)
-      while (dtfe::ld_acquire_sys(a.flags[a.rank] + q) < a.epoch) { __nanosleep(20); }
-    asm volatile("st.release.gpu.global.u32 [%0], %1;" :: "l"(a.local_sync), "r"(a.epoch) : "memory");
+    bool ok = true;
+    for (int q = 0; q < a.world && ok; ++q) ok = spin_until(a.flags[a.rank] + q, a.epoch, a, t0);
+    a.local_sync[2] = ok ? 0u : 1u;
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" :: "l"(a.local_sync), "r"(ok ? a.epoch : 0xffffffffu) : "memory");
   }
+  __shared__ unsigned s_go;
   if (threadIdx.x == 0) {
-    while (dtfe::ld_acquire_gpu(a.local_sync) < a.epoch) { __nanosleep(20); }
+    unsigned v;
+    while ((v = dtfe::ld_acquire_gpu(a.local_sync)) < a.epoch) { __nanosleep(20); }
+    s_go = v;
   }
   __syncthreads();
+  if (s_go == 0xffffffffu) {            // abandoned: leave parameters untouched
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      unsigned prev = atomicAdd(a.local_sync + 1, 1u);
+      if (prev == gridDim.x - 1) { a.local_sync[1] = 0; a.local_sync[0] = a.epoch; }
+    }
+    return;
+  }
 
   // (b) reduce my slices over all ranks' buffers (peer loads) and apply in place.
   size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -157,8 +196,9 @@ __global__ void __launch_bounds__(256) k_sync_rs_apply(SyncArgs a) {
       __threadfence_system();
       for (int p = 0; p < a.world; ++p)
         dtfe::st_release_sys(a.flags[p] + kMaxRanks + a.rank, a.epoch);
-      for (int q = 0; q < a.world; ++q)
-        while (dtfe::ld_acquire_sys(a.flags[a.rank] + kMaxRanks + q) < a.epoch) { __nanosleep(20); }
+      bool ok = true;
+      for (int q = 0; q < a.world && ok; ++q) ok = spin_until(a.flags[a.rank] + kMaxRanks + q, a.epoch, a, t0);
+      if (!ok) a.local_sync[2] = 2u;
     }
   }
 }
@@ -212,7 +252,8 @@ DTFE_API int dtfe_adam_apply_f32(float* param, float* m, float* v, float* slot, 
 DTFE_API int dtfe_sync_rs_apply_f32(const float* const* grads, unsigned* const* flags, int rank, int world,
                                     int nseg, float* const* seg_param, const size_t* seg_begin,
                                     const size_t* seg_end, float alpha, unsigned epoch, unsigned* local_sync,
-                                    int* global_step_or_null, void* stream) {
+                                    int* global_step_or_null, const unsigned* abort_flag_or_null,
+                                    double timeout_s, void* stream) {
   DTFE_REQUIRE(world >= 1 && world <= kMaxRanks, "dtfe_sync_rs_apply_f32: world must be in [1,%d]", kMaxRanks);
   DTFE_REQUIRE(nseg >= 0 && nseg <= 8, "dtfe_sync_rs_apply_f32: nseg must be in [0,8]");
   SyncArgs a{};
@@ -226,6 +267,8 @@ DTFE_API int dtfe_sync_rs_apply_f32(const float* const* grads, unsigned* const* 
   }
   a.alpha = alpha; a.rank = rank; a.world = world; a.epoch = epoch; a.local_sync = local_sync;
   a.global_step = global_step_or_null;
+  a.abort_flag = abort_flag_or_null;
+  a.timeout_ns = timeout_s > 0 ? (unsigned long long)(timeout_s * 1e9) : 0ull;
   // All CTAs must be co-resident (they wait on block 0): cap at one wave and launch cooperatively.
   int grid = grid_for(total, 8);
   if (grid > 148) grid = 148;

@@ -41,7 +41,7 @@ _SIGS = {
     "dtfe_pull_f32": ([_P, _P, c_size_t, _P], c_int),
     "dtfe_adam_apply_f32": ([_P, _P, _P, _P, c_size_t, c_float, c_float, c_float, c_float, c_float, _P], c_int),
     "dtfe_sync_rs_apply_f32": ([POINTER(_P), POINTER(_P), c_int, c_int, c_int, POINTER(_P), POINTER(c_size_t),
-                                POINTER(c_size_t), c_float, c_uint, _P, _P, _P], c_int),
+                                POINTER(c_size_t), c_float, c_uint, _P, _P, _P, ctypes.c_double, _P], c_int),
     "dtfe_sync_max_ranks": ([], c_int),
     "dtfe_mlp2_step_grid": ([c_int, c_int], c_int),
     "dtfe_mlp2_step_workspace_words": ([c_int, c_int, c_int, c_int, c_int], c_size_t),
@@ -270,7 +270,7 @@ def adam_apply(param, m, v, slot, lr_t: float, beta1: float, beta2: float, eps: 
 
 def sync_rs_apply(grad_ptrs: Sequence[int], flag_ptrs: Sequence[int], rank: int, world: int,
                   segments: Sequence, alpha: float, epoch: int, local_sync: torch.Tensor,
-                  global_step: Optional[torch.Tensor]):
+                  global_step: Optional[torch.Tensor], abort_flag_ptr: Optional[int] = None, timeout_s: float = 20.0):
     """Synchronous SGD: reduce-scatter of all workers' gradients fused with the apply.
     ``segments``: (param_tensor, begin, end) for every variable this rank owns."""
     G = (_P * world)(*grad_ptrs)
@@ -280,7 +280,8 @@ def sync_rs_apply(grad_ptrs: Sequence[int], flag_ptrs: Sequence[int], rank: int,
     Bg = (c_size_t * max(n, 1))(*[b for _, b, _ in segments])
     En = (c_size_t * max(n, 1))(*[e for _, _, e in segments])
     check(lib().dtfe_sync_rs_apply_f32(G, F, rank, world, n, P, Bg, En, alpha, epoch, local_sync.data_ptr(),
-                                       _ptr(global_step), _stream()), "dtfe_sync_rs_apply_f32")
+                                       _ptr(global_step), abort_flag_ptr, timeout_s, _stream()),
+          "dtfe_sync_rs_apply_f32")
 
 
 # --------------------------------------------------------------------------------------

@@ -22,7 +22,9 @@ from .ps import PeerParamStore
 
 class SyncGroup:
     def __init__(self, store: PeerParamStore, trainable_names: Sequence[str], rank: int, world: int,
-                 owner_of_shard=lambda k, world: k % world):
+                 owner_of_shard=lambda k, world: k % world, exchange=None, timeout_s: float = 20.0):
+        """``exchange(blob) -> [blob of rank 0, ..., blob of rank W-1]``; default: torch.distributed
+        all_gather_object (SPMD).  Launcher-mode workers pass a TCPStore-based exchange."""
         self.store, self.rank, self.world = store, rank, world
         self.device = store.device
         self.names = list(trainable_names)
@@ -44,9 +46,16 @@ class SyncGroup:
         # exchange IPC handles
         mine = (ops.ipc_export(self._grad_ptr), ops.ipc_export(self._flag_ptr))
         self._opened: List[int] = []
+        self.timeout_s = timeout_s
+        # workers leaving (signal, crash handler) raise the stop word of shard 0; spinning peers see it
+        from .layout import H_STOP
+        self._abort_ptr = store.base_ptr(0) + 4 * H_STOP
         if world > 1:
-            allh = [None] * world
-            dist.all_gather_object(allh, mine)
+            if exchange is None:
+                allh = [None] * world
+                dist.all_gather_object(allh, mine)
+            else:
+                allh = exchange(mine)
             self.grad_ptrs, self.flag_ptrs = [], []
             with torch.cuda.device(self.device):
                 for r, (gh, fh) in enumerate(allh):
@@ -56,7 +65,8 @@ class SyncGroup:
                         g, f = ops.ipc_open(gh), ops.ipc_open(fh)
                         self._opened += [g, f]
                         self.grad_ptrs.append(g); self.flag_ptrs.append(f)
-            dist.barrier()
+            if exchange is None:
+                dist.barrier()
         else:
             self.grad_ptrs, self.flag_ptrs = [self._grad_ptr], [self._flag_ptr]
         # segments this rank owns
@@ -79,7 +89,12 @@ class SyncGroup:
     def reduce_scatter_apply(self, lr: float) -> None:
         self.epoch += 1
         ops.sync_rs_apply(self.grad_ptrs, self.flag_ptrs, self.rank, self.world, self.segments,
-                          -lr / self.world, self.epoch, self.local_sync, self.global_step)
+                          -lr / self.world, self.epoch, self.local_sync, self.global_step,
+                          abort_flag_ptr=self._abort_ptr, timeout_s=self.timeout_s)
+
+    def aborted(self) -> int:
+        """0 if the last reduce_scatter_apply completed, else which barrier gave up (needs a sync)."""
+        return int(self.local_sync[2].item())
 
     def close(self) -> None:
         for p in self._opened:

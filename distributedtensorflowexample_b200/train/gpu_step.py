@@ -94,7 +94,13 @@ class LayerwiseStepper:
     first: dX against the *pre-update* weights, then dW/db with the push fused -> global_step."""
 
     def __init__(self, spec: MLPSpec, batch: int, params: Sequence[torch.Tensor], global_step: torch.Tensor,
-                 lr: float, device, atomic: bool = True, grad_buffers: Optional[Sequence[torch.Tensor]] = None):
+                 lr: float, device, atomic: bool = True, grad_buffers: Optional[Sequence[torch.Tensor]] = None,
+                 adam: Optional[dict] = None):
+        """``adam``: {'slots': [...], 'm': [...], 'v': [...], 't': int32 tensor, 'apply': bool, betas/eps} - gradients
+        are pushed (red.add, unscaled) into the owner-side slots; the rank with ``apply=True`` (the chief)
+        then runs the owner-side Adam kernel over every variable, consuming and clearing the slots."""
+        self.adam = adam
+        self._adam_t = 0
         self.spec, self.batch, self.lr, self.atomic = spec, batch, lr, atomic
         self.params = list(params)
         self.global_step = global_step
@@ -143,13 +149,24 @@ class LayerwiseStepper:
             d_prev = None
             if l > 0:
                 d_prev = ops.dense_bwd_dx(d, W, h_in, ops.ACT_SIGMOID, out=self.dacts[l - 1], shard_reads=True)
-            if self.grad_buffers is None:
+            if self.adam is not None:
+                ops.dense_bwd_dw_push(h_in, d, self.adam["slots"][2 * l], 1.0, atomic=True)
+                ops.bias_grad_push(d, self.adam["slots"][2 * l + 1], 1.0, atomic=True)
+            elif self.grad_buffers is None:
                 ops.dense_bwd_dw_push(h_in, d, W, alpha, atomic=self.atomic)
                 ops.bias_grad_push(d, b, alpha, atomic=self.atomic)
             else:
                 ops.dense_bwd_dw_push(h_in, d, None, 0.0, grad_out=self.grad_buffers[2 * l])
                 ops.bias_grad_push(d, None, 0.0, grad_out=self.grad_buffers[2 * l + 1])
             d = d_prev
+        if self.adam is not None and self.adam.get("apply", True):
+            import math
+            self._adam_t += 1
+            b1, b2, eps = self.adam.get("beta1", 0.9), self.adam.get("beta2", 0.999), self.adam.get("eps", 1e-8)
+            lr_t = self.lr * math.sqrt(1.0 - b2 ** self._adam_t) / (1.0 - b1 ** self._adam_t)
+            for i, p in enumerate(self.params):
+                ops.adam_apply(p.view(-1), self.adam["m"][i].view(-1), self.adam["v"][i].view(-1),
+                               self.adam["slots"][i].view(-1), lr_t, b1, b2, eps)
         if self.grad_buffers is None:
             ops.global_step_add(self.global_step, 1, self.step)
 

@@ -60,8 +60,11 @@ class ReplicatedModel:
         return list(zip(loc, glo))
 
 
+ADAM_SLOTS = ("Adam", "Adam_1", "grad_slot")   # TF1 slot names for m and v, plus the push mailbox
+
+
 def build_replicated_model(spec: MLPSpec, job_name: str = "worker", task_index: int = 0, num_ps: int = 1,
-                           ps_strategy: str = "round_robin") -> ReplicatedModel:
+                           ps_strategy: str = "round_robin", optimizer: str = "sgd") -> ReplicatedModel:
     store = VariableStore()
     global_device = f"/job:{job_name}/task:{task_index}/cpu:0"
     local_device = f"/job:{job_name}/task:{task_index}/gpu:0"
@@ -71,6 +74,17 @@ def build_replicated_model(spec: MLPSpec, job_name: str = "worker", task_index: 
         with store.variable_scope("global"):
             build_mlp_variables(store, spec)
             gs = store.get_variable("global_step", [], "int32", constant_initializer(0), trainable=False)
+    if optimizer == "adam":
+        # Optimizer state lives with the shard that owns the variable (owner-side apply): TF1 names the
+        # moments <var>/Adam and <var>/Adam_1; <var>/grad_slot is the mailbox workers push into.
+        for v in get_vars(store, "global"):
+            with store.device(v.device):
+                for slot in ADAM_SLOTS:
+                    store.get_variable(f"{v.name}/{slot}", v.shape, "float32", constant_initializer(0), trainable=False)
+        with store.device(gs.device):
+            store.get_variable("global/adam_t", [], "int32", constant_initializer(0), trainable=False)
+    elif optimizer != "sgd":
+        raise ValueError(f"unknown optimizer {optimizer!r}")
     with store.device(local_device):
         with store.variable_scope("local"):
             build_mlp_variables(store, spec)

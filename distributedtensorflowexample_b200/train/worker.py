@@ -62,7 +62,11 @@ class Worker:
         self.spec = spec_from_flags(flags.hidden, dtype=flags.dtype if server.backend == "cuda" else "float32")
         # C8: two copies of the net, global on the ps job, local on this worker
         self.model = build_replicated_model(self.spec, job_name, task_index, num_ps=server.num_ps,
-                                            ps_strategy=flags.ps_strategy)
+                                            ps_strategy=flags.ps_strategy,
+                                            optimizer=flags.optimizer if server.backend == "cuda" else "sgd")
+        if server.backend != "cuda" and (flags.sync or flags.optimizer != "sgd"):
+            raise ValueError("--sync and --optimizer adam are implemented on the CUDA path (the gloo "
+                             "configuration reproduces the reference's async SGD only)")
         self.global_step = self.model.global_step
         if server.backend == "gloo":
             self._build_cpu()
@@ -96,10 +100,38 @@ class Worker:
         self.store = store
         self.client = PeerParamClient(store)
         names = [v.name for v in self.model.global_trainable]
-        self.trainer = GpuTrainer(self.spec, self.flags.batch_size, self.flags.learning_rate,
-                                  [store.tensor(n) for n in names], store.tensor(self.global_step.name), dev,
-                                  steps_per_launch=self.flags.steps_per_launch,
-                                  atomic=not self.flags.unlocked_apply, remote=True)
+        f = self.flags
+        self.sync_group = None
+        if f.sync or f.optimizer == "adam":
+            from .gpu_step import LayerwiseStepper
+            tr = GpuTrainer(self.spec, f.batch_size, f.learning_rate, [store.tensor(n) for n in names],
+                            store.tensor(self.global_step.name), dev, engine="layerwise", remote=True)
+            kw = {}
+            if f.sync:
+                if self.server.num_workers > max(1, f.num_gpus):
+                    raise ValueError("--sync needs one worker per GPU (its kernel waits on the other ranks)")
+                from ..parallel.sync import SyncGroup
+                W, me = self.server.num_workers, self.task_index
+
+                def exchange(blob):
+                    import pickle
+                    kv.set(f"sync/{me}", pickle.dumps(blob))
+                    return [pickle.loads(kv.get(f"sync/{r}")) for r in range(W)]
+                # variable on ps shard k is reduced by worker (k mod W)
+                self.sync_group = SyncGroup(store, names, me, W, exchange=exchange)
+                kw["grad_buffers"] = self.sync_group.grad_views({n: tuple(store.tensor(n).shape) for n in names})
+            else:
+                kw["adam"] = dict(slots=[store.tensor(n + "/grad_slot") for n in names],
+                                  m=[store.tensor(n + "/Adam") for n in names],
+                                  v=[store.tensor(n + "/Adam_1") for n in names], apply=self.is_chief)
+            tr.layer = LayerwiseStepper(self.spec, f.batch_size, tr.params, tr.global_step, f.learning_rate, dev,
+                                        atomic=not f.unlocked_apply, **kw)
+            self.trainer = tr
+        else:
+            self.trainer = GpuTrainer(self.spec, f.batch_size, f.learning_rate,
+                                      [store.tensor(n) for n in names], store.tensor(self.global_step.name), dev,
+                                      steps_per_launch=f.steps_per_launch,
+                                      atomic=not f.unlocked_apply, remote=True)
         self.engine = None
 
     def build_summary_op(self) -> None:
@@ -141,7 +173,15 @@ class Worker:
             self._start_time = time.time()
             self._start_step = 0
             run = self._loop_cpu if self.trainer is None else self._loop_cuda
-            last_step = run(sv, dataset)
+            try:
+                last_step = run(sv, dataset)
+            finally:
+                if getattr(self, "sync_group", None) is not None:
+                    # tell the peers' spinning sync kernels that this rank is gone (they skip the update)
+                    try:
+                        self.client.request_stop()
+                    except Exception:
+                        pass
         self.summary_writer.close()
         return last_step
 
@@ -186,10 +226,16 @@ class Worker:
         test_x = torch.as_tensor(dataset.test.images, dtype=torch.float32).to(dev)
         test_y = torch.as_tensor(dataset.test.label_ids, dtype=torch.int32).to(dev)
         eval_fn = lambda: tr.evaluate(test_x, test_y)
-        n = max(1, f.steps_per_launch)
+        n = 1 if self.sync_group is not None else max(1, f.steps_per_launch)   # sync: one update per exchange
         step = 0
         while not sv.should_stop():
             loss_d, acc_d, step_d = tr.train_device_steps(train, n)
+            if self.sync_group is not None:
+                self.sync_group.reduce_scatter_apply(f.learning_rate)
+                step_d = self.store.tensor(self.global_step.name)[:1] - 1      # the aggregated update just applied
+                if self.sync_group.aborted():
+                    print("sync: a peer left, stopping", flush=True)
+                    break
             loss, acc, steps = loss_d.tolist(), acc_d.tolist(), step_d.tolist()   # one sync per launch
             stop = False
             for l, a, s in zip(loss, acc, steps):

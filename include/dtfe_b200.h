@@ -93,11 +93,14 @@ int dtfe_adam_apply_f32(float* param, float* m, float* v, float* slot, size_t n,
                         float beta2, float eps, float grad_scale, void* stream);
 /* Synchronous SGD: every rank reduces the flat-gradient ranges [seg_begin,seg_end) of the variables it
  * owns out of all ranks' gradient buffers in peer memory and applies them in place (seg_param); flag barriers in peer memory on entry and exit.  One rank per
- * GPU (the kernel spins on peers).  No counterpart in the reference (async only); semantic model is
+ * GPU (the kernel spins on peers).  A wait is abandoned - parameters untouched, local_sync[2] != 0 - when
+ * *abort_flag becomes non-zero (a rank is leaving) or after timeout_s seconds, so a lost rank cannot hang
+ * the others' GPUs.  No counterpart in the reference (async only); semantic model is
  * TF1 SyncReplicasOptimizer. */
 int dtfe_sync_rs_apply_f32(const float* const* grads, unsigned* const* flags, int rank, int world, int nseg,
                            float* const* seg_param, const size_t* seg_begin, const size_t* seg_end, float alpha,
-                           unsigned epoch, unsigned* local_sync, int* global_step_or_null, void* stream);
+                           unsigned epoch, unsigned* local_sync, int* global_step_or_null,
+                           const unsigned* abort_flag_or_null, double timeout_s, void* stream);
 int dtfe_sync_max_ranks(void);
 
 /* ---- the whole reference training step in one cooperative kernel ------------------------------- */

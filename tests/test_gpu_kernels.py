@@ -142,4 +142,11 @@ def test_sync_rs_apply_single_rank():
     assert gs.item() == 1
     ops.sync_rs_apply([grads.data_ptr()], [flags.data_ptr()], 0, 1, [(param, 0, n)], -0.1, 2, local_sync, gs)
     torch.testing.assert_close(param.double(), ref - 0.1 * grads.double(), rtol=1e-6, atol=1e-5)
-    assert gs.item() == 2
+    assert gs.item() == 2 and local_sync[2].item() == 0
+    # a peer that never arrives: the wait is abandoned after the timeout instead of hanging the GPU
+    flags2 = torch.zeros_like(flags)
+    before = param.clone()
+    ops.sync_rs_apply([grads.data_ptr(), grads.data_ptr()], [flags2.data_ptr(), flags2.data_ptr()], 0, 2,
+                      [(param, 0, n)], -0.1, 1, torch.zeros(4, device="cuda", dtype=torch.int32), None, timeout_s=0.05)
+    torch.cuda.synchronize()
+    assert torch.equal(param, before)

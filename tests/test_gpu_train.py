@@ -161,3 +161,36 @@ def test_trainer_device_and_host_paths_agree():
         for a, b in zip(outs[0], other):
             np.testing.assert_allclose(a, b, rtol=1e-5, atol=1e-6)
     assert outs[0][-1].item() == 10
+
+
+def test_layerwise_adam_matches_oracle():
+    """Optional Adam (north star): workers push raw gradients into owner-side slots, the owner applies."""
+    from distributedtensorflowexample_b200.parallel.ps import PeerParamStore
+    from distributedtensorflowexample_b200.train.gpu_step import LayerwiseStepper
+    spec = reference_mlp_spec()
+    model = build_replicated_model(spec, num_ps=2, optimizer="adam")
+    store = PeerParamStore(model.global_all, 2, torch.device("cuda:0"))
+    store.allocate()
+    store.initialize(np.random.default_rng(5))
+    names = [v.name for v in model.global_trainable]
+    assert "global/dense/kernel/Adam" in store.layout.entries and "global/dense_1/bias/Adam_1" in store.layout.entries
+    assert store.shard_of("global/dense/kernel/Adam") == store.shard_of("global/dense/kernel")
+    params_np = [store.read(n).astype(np.float64) for n in names]
+    st_ref = oracle.AdamState(params_np)
+    x, y = _data(500)
+    X = torch.tensor(x, device="cuda"); Y = torch.tensor(y, device="cuda")
+    adam = dict(slots=[store.tensor(n + "/grad_slot") for n in names], m=[store.tensor(n + "/Adam") for n in names],
+                v=[store.tensor(n + "/Adam_1") for n in names], apply=True)
+    B, lr = 100, 0.01
+    st = LayerwiseStepper(spec, B, [store.tensor(n) for n in names], store.tensor("global/global_step"), lr, "cuda:0",
+                          adam=adam)
+    for s in range(4):
+        rows = slice(s * B, (s + 1) * B)
+        st.run(X[rows], Y[rows])
+        _, _, grads = oracle.gradients(params_np, x[rows].astype(np.float64), y[rows])
+        st_ref.apply(params_np, grads, lr)
+    for n, p in zip(names, params_np):
+        np.testing.assert_allclose(store.read(n), p, rtol=2e-3, atol=5e-4)
+    assert store.read("global/global_step").item() == 4
+    assert float(np.abs(store.read(names[0] + "/grad_slot")).max()) == 0.0
+    store.close()
