@@ -58,6 +58,8 @@ struct Mlp2Args {
   int train;                // 0: forward/metrics only (no phase C)
   int remote;               // some shard lives on a peer GPU: completion fence must be .sys
   long long* dbg;           // optional [nsteps][G][8] globaltimer stamps (profiling)
+  float *gW1, *gb1, *gW2, *gb2;  // sync mode: raw gradients are stored here instead of being pushed
+  int* cursor;              // optional device-side step cursor: batches start at *cursor (graph replay)
 };
 
 __device__ __forceinline__ void grid_barrier(unsigned* ctr, unsigned& target, unsigned G) {
@@ -85,6 +87,12 @@ __device__ __forceinline__ long long gtime() {
 __device__ __forceinline__ void push1(float* p, float v, int atomic) {
   if (atomic) dtfe::red_add_sys(p, v);
   else *p = dtfe::ld_relaxed_sys(p) + v;
+}
+// Asynchronous mode: push -lr*g into the shard.  Synchronous mode: leave the raw gradient in this
+// rank's exchange buffer for the reduce-scatter kernel.
+__device__ __forceinline__ void emit(float* shard, float* gbuf, long i, float g, float nlr, int atomic) {
+  if (gbuf) __stcg(gbuf + i, g);
+  else push1(shard + i, nlr * g, atomic);
 }
 
 template <int KS>
@@ -126,7 +134,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
       long row = 0;
       if (e < B * KS && st < a.nsteps) {
         int r = e / KS;
-        row = a.batch_idx ? (long)__ldg(a.batch_idx + (long)st * B + r) : (long)st * a.rows_per_step + r;
+        row = a.batch_idx ? (long)__ldg(a.batch_idx + (sbase + st) * B + r) : (sbase + st) * a.rows_per_step + r;
       }
       rownext[i] = row;
     }
@@ -143,6 +151,8 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
       xnext[i] = v;
     }
   };
+  // device-side cursor: this launch processes batches cursor .. cursor+nsteps-1 of batch_idx
+  const long sbase = a.cursor ? (long)*reinterpret_cast<volatile int*>(a.cursor) : 0;
   fetch_rows(0);
   fetch_x(0);
   fetch_rows(1);
@@ -167,7 +177,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
     {
       int r = 2 * g + slot;
       if (r < B) {
-        long row = a.batch_idx ? (long)__ldg(a.batch_idx + (long)s * B + r) : (long)s * a.rows_per_step + r;
+        long row = a.batch_idx ? (long)__ldg(a.batch_idx + (sbase + s) * B + r) : (sbase + s) * a.rows_per_step + r;
         ylab = __ldg(a.labels + row);
       }
     }
@@ -293,7 +303,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
         float se = dtfe::warp_sum(ex);
         int y = ylab;
         if (r0 != 2 * g) {                   // later rounds (B > 2*G): fetch the label now
-          long row = a.batch_idx ? (long)a.batch_idx[(long)s * B + r] : (long)s * a.rows_per_step + r;
+          long row = a.batch_idx ? (long)a.batch_idx[(sbase + s) * B + r] : (sbase + s) * a.rows_per_step + r;
           y = a.labels[row];
         }
         float zy = __shfl_sync(0xffffffffu, zc, y);
@@ -395,8 +405,8 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
         for (int q = 0; q < 4; ++q) {
           int k = k0 + grp * 4 + q;
           if (k < D) {
-            if (v0) push1(a.W1 + (long)k * H + j0, nlr * (acc0[q] + bcc0[q]), a.atomic);
-            if (kParts < 4 && v1) push1(a.W1 + (long)k * H + j1, nlr * (acc1[q] + bcc1[q]), a.atomic);
+            if (v0) emit(a.W1, a.gW1, (long)k * H + j0, acc0[q] + bcc0[q], nlr, a.atomic);
+            if (kParts < 4 && v1) emit(a.W1, a.gW1, (long)k * H + j1, acc1[q] + bcc1[q], nlr, a.atomic);
           }
         }
       }
@@ -426,14 +436,14 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
           for (int c = 0; c < kMaxC; ++c) {
             if (c < C) {
               float v = dtfe::warp_sum(accc[c]);
-              if (lane == 0) push1(a.W2 + (long)tt * C + c, nlr * v, a.atomic);
+              if (lane == 0) emit(a.W2, a.gW2, (long)tt * C + c, v, nlr, a.atomic);
             }
           }
         } else {  // db1[tt] = sum_b dA[b][tt]
           float v = 0.f;
           for (int b = lane; b < B; b += 32) v += dAs[b * HP + tt];
           v = dtfe::warp_sum(v);
-          if (lane == 0) push1(a.b1 + tt, nlr * v, a.atomic);
+          if (lane == 0) emit(a.b1, a.gb1, tt, v, nlr, a.atomic);
         }
       }
       if (g == (int)G - 1 && warp == 7) {  // db2[c] = sum_b dZ[b][c]
@@ -441,7 +451,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
           float v = 0.f;
           for (int b = lane; b < B; b += 32) v += dZs[b * C + c];
           v = dtfe::warp_sum(v);
-          if (lane == 0) push1(a.b2 + c, nlr * v, a.atomic);
+          if (lane == 0) emit(a.b2, a.gb2, c, v, nlr, a.atomic);
         }
       }
       // All of this CTA's pushes are performed before it reports completion: the CTA barrier orders
@@ -454,7 +464,8 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
         unsigned prev = atomicAdd(a.sync + 2, 1u);
         if (prev == G - 1) {
           a.sync[2] = 0;
-          int old = dtfe::atom_add_sys_s32(a.global_step, 1);
+          // sync mode: the aggregated update (and its global_step += 1) belongs to the exchange kernel
+          int old = a.gW1 ? *reinterpret_cast<volatile int*>(a.global_step) : dtfe::atom_add_sys_s32(a.global_step, 1);
           a.step_out[s] = old;
         }
       }
@@ -468,7 +479,11 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
   __syncthreads();
   if (tid == 0) {
     unsigned prev = atomicAdd(a.sync + 1, 1u);
-    if (prev == G - 1) { a.sync[0] = 0; a.sync[1] = 0; __threadfence(); }
+    if (prev == G - 1) {
+      a.sync[0] = 0; a.sync[1] = 0;
+      if (a.cursor) *a.cursor = (int)sbase + a.nsteps;   // every CTA read the cursor before arriving here
+      __threadfence();
+    }
   }
 }
 
@@ -516,6 +531,9 @@ static int mlp2_fill(const Mlp2Launch& L, Mlp2Args& a) {
   a.sync = (unsigned*)w;
   a.loss_out = L.loss_out; a.acc_out = L.acc_out; a.step_out = L.step_out;
   a.lr = L.lr; a.nsteps = L.nsteps; a.atomic = L.atomic; a.train = L.train; a.remote = L.remote; a.dbg = L.dbg;
+  a.gW1 = L.gW1; a.gb1 = L.gb1; a.gW2 = L.gW2; a.gb2 = L.gb2; a.cursor = L.cursor;
+  DTFE_REQUIRE((a.gW1 != nullptr) == (a.gb1 != nullptr) && (a.gW1 != nullptr) == (a.gW2 != nullptr) &&
+               (a.gW1 != nullptr) == (a.gb2 != nullptr), "mlp2_step: pass all four gradient buffers or none");
   return 0;
 }
 

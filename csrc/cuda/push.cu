@@ -131,6 +131,9 @@ __global__ void __launch_bounds__(256) k_sync_rs_apply(SyncArgs a) {
   // local_sync words: [0] go (epoch once all gradients are in, 0xffffffff on abort) [1] done count
   //                   [2] abort status of the last call (0 ok, 1 entry barrier, 2 exit barrier)
   const unsigned long long t0 = gtimer_ns();
+  // epoch 0 = take it from device memory (last completed epoch + 1), so a captured CUDA graph can be
+  // replayed step after step without a host-side argument changing.
+  if (a.epoch == 0) a.epoch = *reinterpret_cast<volatile unsigned*>(a.local_sync + 3) + 1u;
   // (a) arrive: tell every peer "my gradients for this epoch are complete", then wait for all.
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     __threadfence_system();
@@ -151,7 +154,7 @@ __global__ void __launch_bounds__(256) k_sync_rs_apply(SyncArgs a) {
     __syncthreads();
     if (threadIdx.x == 0) {
       unsigned prev = atomicAdd(a.local_sync + 1, 1u);
-      if (prev == gridDim.x - 1) { a.local_sync[1] = 0; a.local_sync[0] = a.epoch; }
+      if (prev == gridDim.x - 1) { a.local_sync[1] = 0; a.local_sync[0] = a.epoch; a.local_sync[3] = a.epoch; }
     }
     return;
   }
@@ -192,6 +195,7 @@ __global__ void __launch_bounds__(256) k_sync_rs_apply(SyncArgs a) {
     unsigned prev = atomicAdd(a.local_sync + 1, 1u);
     if (prev == gridDim.x - 1) {
       a.local_sync[1] = 0;
+      a.local_sync[3] = a.epoch;
       if (a.global_step) dtfe::atom_add_sys_s32(a.global_step, 1);
       __threadfence_system();
       for (int p = 0; p < a.world; ++p)
@@ -201,6 +205,26 @@ __global__ void __launch_bounds__(256) k_sync_rs_apply(SyncArgs a) {
       if (!ok) a.local_sync[2] = 2u;
     }
   }
+}
+
+// Batch gather with a device-side cursor: rows idx[cursor*B .. +B) of the resident dataset -> a dense
+// batch.  The cursor lives in device memory so the launch can sit in a replayed CUDA graph.
+__global__ void __launch_bounds__(256) k_gather_rows(const float* __restrict__ X, long ldx,
+                                                     const int* __restrict__ labels, const int* __restrict__ idx,
+                                                     const int* __restrict__ cursor, int B, int D,
+                                                     float* __restrict__ Xout, int* __restrict__ Yout) {
+  const long base = (long)(*cursor) * B;
+  const int r = blockIdx.x;
+  const long row = idx[base + r];
+  const float* src = X + row * ldx;
+  float* dst = Xout + (long)r * D;
+  if ((D & 3) == 0 && ((ldx & 3) == 0)) {
+    for (int c = threadIdx.x; c < D / 4; c += blockDim.x)
+      reinterpret_cast<float4*>(dst)[c] = __ldg(reinterpret_cast<const float4*>(src) + c);
+  } else {
+    for (int c = threadIdx.x; c < D; c += blockDim.x) dst[c] = __ldg(src + c);
+  }
+  if (threadIdx.x == 0) Yout[r] = labels[row];
 }
 
 inline int grid_for(size_t n, int per_thread) {
@@ -279,3 +303,11 @@ DTFE_API int dtfe_sync_rs_apply_f32(const float* const* grads, unsigned* const* 
 }
 
 DTFE_API int dtfe_sync_max_ranks() { return kMaxRanks; }
+
+// Xout[r,:] = X[idx[cursor*B + r], :], Yout[r] = labels[...]; *cursor is read on the device.
+DTFE_API int dtfe_gather_rows_f32(const float* X, long ldx, const int* labels, const int* idx, const int* cursor,
+                                  int B, int D, float* Xout, int* Yout, void* stream) {
+  k_gather_rows<<<B, 256, 0, (cudaStream_t)stream>>>(X, ldx, labels, idx, cursor, B, D, Xout, Yout);
+  DTFE_LAUNCH_CHECK();
+  return 0;
+}

@@ -130,17 +130,31 @@ def _run_mnist_sync(args, rank, world, dev, ClockSampler, spec, model, store, na
     """Synchronous SGD: layer-wise kernels write gradients to a peer-visible buffer, then ONE kernel per
     rank does barrier + reduce-scatter + apply + barrier over peer memory (parallel/sync.py)."""
     from .parallel.sync import SyncGroup
-    from .train.gpu_step import LayerwiseStepper
+    from .train.gpu_step import FusedMlp2Stepper
     sg = SyncGroup(store, names, rank, world)
     shapes = {n: tuple(store.tensor(n).shape) for n in names}
-    st = LayerwiseStepper(spec, B, [store.tensor(n) for n in names], store.tensor("global/global_step"), lr, dev,
-                          grad_buffers=sg.grad_views(shapes))
-    idx = ds.next_indices(B, K + W).long()
+    st = FusedMlp2Stepper(spec, B, [store.tensor(n) for n in names], store.tensor("global/global_step"), lr, dev,
+                          remote=not store.all_local(), grad_buffers=sg.grad_views(shapes))
+    idx = ds.next_indices(B, K + W + 8)
+    st.cursor = torch.zeros(1, dtype=torch.int32, device=dev)
+
+    def one_step():
+        st.run(ds.images, ds.labels, nsteps=1, batch_idx=idx)   # fwd/bwd in one kernel, gradients -> exchange buffer
+        sg.reduce_scatter_apply(lr)                             # barrier + reduce-scatter + apply + barrier
+
+    # Both launches are captured once and replayed: per-step host work is one cudaGraphLaunch, so a slow
+    # host on one rank cannot stall the others' GPUs at the exchange.
+    side = torch.cuda.Stream(device=dev)
+    with torch.cuda.stream(side):
+        one_step()
+    torch.cuda.current_stream().wait_stream(side)
+    _barrier(world)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        one_step()
 
     def step(i):
-        rows = idx[i * B:(i + 1) * B]
-        st.run(ds.images.index_select(0, rows), ds.labels.index_select(0, rows))
-        sg.reduce_scatter_apply(lr)
+        graph.replay()
 
     for i in range(W):
         step(i)
@@ -161,8 +175,8 @@ def _run_mnist_sync(args, rank, world, dev, ClockSampler, spec, model, store, na
            "vs_baseline": None, "dtype": "fp32", "data": "synthetic", "impl": "ours",
            "config": {"model": "MNIST MLP 784-100-10", "global_batch": B * world, "batch_per_worker": B,
                       "parallelism": f"sync-ps dp{world}: reduce-scatter fused with apply over peer memory",
-                      "engine": "layerwise fp32 + sync_rs_apply"},
-           "gpu_launches": (st.launches_per_call + 1) * K, "clocks": clk,
+                      "engine": "fused step kernel (gradients to the exchange buffer) + sync_rs_apply"},
+           "gpu_launches": 2 * K, "cuda_graph": True, "clocks": clk,
            "global_step_after": int(store.tensor("global/global_step").item())}
     if rank == 0:
         print(json.dumps(out), flush=True)

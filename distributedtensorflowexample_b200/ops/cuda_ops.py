@@ -43,6 +43,7 @@ _SIGS = {
     "dtfe_sync_rs_apply_f32": ([POINTER(_P), POINTER(_P), c_int, c_int, c_int, POINTER(_P), POINTER(c_size_t),
                                 POINTER(c_size_t), c_float, c_uint, _P, _P, _P, ctypes.c_double, _P], c_int),
     "dtfe_sync_max_ranks": ([], c_int),
+    "dtfe_gather_rows_f32": ([_P, c_long, _P, _P, _P, c_int, c_int, _P, _P, _P], c_int),
     "dtfe_mlp2_step_grid": ([c_int, c_int], c_int),
     "dtfe_mlp2_step_workspace_words": ([c_int, c_int, c_int, c_int, c_int], c_size_t),
     "dtfe_mlp2_step": ([_P, _P], c_int),
@@ -268,6 +269,13 @@ def adam_apply(param, m, v, slot, lr_t: float, beta1: float, beta2: float, eps: 
                                     lr_t, beta1, beta2, eps, grad_scale, _stream()), "dtfe_adam_apply_f32")
 
 
+def gather_rows(X, labels, idx, cursor, Xout, Yout):
+    """On-device ``next_batch``: rows ``idx[cursor*B : (cursor+1)*B]`` of the resident dataset (cursor on device)."""
+    B, D = Xout.shape
+    check(lib().dtfe_gather_rows_f32(X.data_ptr(), X.stride(0), labels.data_ptr(), idx.data_ptr(), cursor.data_ptr(),
+                                     B, D, Xout.data_ptr(), Yout.data_ptr(), _stream()), "dtfe_gather_rows_f32")
+
+
 def sync_rs_apply(grad_ptrs: Sequence[int], flag_ptrs: Sequence[int], rank: int, world: int,
                   segments: Sequence, alpha: float, epoch: int, local_sync: torch.Tensor,
                   global_step: Optional[torch.Tensor], abort_flag_ptr: Optional[int] = None, timeout_s: float = 20.0):
@@ -300,6 +308,8 @@ class _Mlp2Launch(ctypes.Structure):
         ("loss_out", _P), ("acc_out", _P), ("step_out", _P),
         ("lr", c_float), ("nsteps", c_int), ("atomic", c_int), ("train", c_int), ("remote", c_int),
         ("dbg", _P),
+        ("gW1", _P), ("gb1", _P), ("gW2", _P), ("gb2", _P),
+        ("cursor", _P),
     ]
 
 
@@ -360,7 +370,7 @@ class Mlp2Step:
 
     def run(self, W1, b1, W2, b2, global_step, X, labels, lr: float, nsteps: int = 1, batch_idx=None,
             rows_per_step: int = 0, atomic: bool = True, train: bool = True, out_offset: int = 0,
-            remote: bool = True, dbg=None):
+            remote: bool = True, dbg=None, grads=None, cursor=None):
         assert nsteps + out_offset <= self.max_steps
         L = _Mlp2Launch()
         L.B, L.D, L.H, L.C, L.ks = self.B, self.D, self.H, self.C, self.ks
@@ -377,4 +387,7 @@ class Mlp2Step:
         L.lr, L.nsteps, L.atomic, L.train = lr, nsteps, int(atomic), int(train)
         L.remote = int(remote)
         L.dbg = _ptr(dbg)
+        if grads is not None:
+            L.gW1, L.gb1, L.gW2, L.gb2 = (g.data_ptr() for g in grads)
+        L.cursor = _ptr(cursor)
         check(lib().dtfe_mlp2_step(ctypes.byref(L), _stream()), "dtfe_mlp2_step")

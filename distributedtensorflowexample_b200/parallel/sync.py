@@ -86,10 +86,12 @@ class SyncGroup:
             out.append(self.gradbuf[b:e].view(*shapes[name]))
         return out
 
-    def reduce_scatter_apply(self, lr: float) -> None:
+    def reduce_scatter_apply(self, lr: float, device_epoch: bool = True) -> None:
+        """``device_epoch``: the kernel numbers the exchanges itself (local_sync[3]), so this call can be
+        captured in a CUDA graph and replayed."""
         self.epoch += 1
         ops.sync_rs_apply(self.grad_ptrs, self.flag_ptrs, self.rank, self.world, self.segments,
-                          -lr / self.world, self.epoch, self.local_sync, self.global_step,
+                          -lr / self.world, 0 if device_epoch else self.epoch, self.local_sync, self.global_step,
                           abort_flag_ptr=self._abort_ptr, timeout_s=self.timeout_s)
 
     def aborted(self) -> int:

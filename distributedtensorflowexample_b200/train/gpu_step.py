@@ -56,7 +56,11 @@ class DeviceDataset:
 class FusedMlp2Stepper:
     def __init__(self, spec: MLPSpec, batch: int, params: Sequence[torch.Tensor], global_step: torch.Tensor,
                  lr: float, device, max_steps_per_launch: int = 1, atomic: bool = True, ks: int = 8,
-                 remote: bool = True):
+                 remote: bool = True, grad_buffers: Optional[Sequence[torch.Tensor]] = None):
+        """``grad_buffers``: synchronous mode - raw gradients go to these 4 buffers (this rank's exchange
+        buffer) instead of being pushed; ``parallel.sync.SyncGroup.reduce_scatter_apply`` finishes the step."""
+        self.grad_buffers = list(grad_buffers) if grad_buffers is not None else None
+        self.cursor = None
         if spec.num_layers != 2 or spec.param_dtype != "float32":
             raise ValueError("FusedMlp2Stepper handles 2-layer float32 models")
         D, H, C = spec.dims
@@ -78,7 +82,8 @@ class FusedMlp2Stepper:
         """Results land in ``self.k.loss/acc/step[out_offset : out_offset+nsteps]`` (device)."""
         self.k.run(self.W1, self.b1, self.W2, self.b2, self.global_step, X, labels, self.lr, nsteps=nsteps,
                    batch_idx=batch_idx, rows_per_step=rows_per_step, atomic=self.atomic, train=train,
-                   out_offset=out_offset, remote=self.remote, dbg=self.dbg)
+                   out_offset=out_offset, remote=self.remote, dbg=self.dbg, grads=self.grad_buffers,
+                   cursor=self.cursor)
 
     @property
     def loss(self): return self.k.loss

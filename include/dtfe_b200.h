@@ -93,7 +93,8 @@ int dtfe_adam_apply_f32(float* param, float* m, float* v, float* slot, size_t n,
                         float beta2, float eps, float grad_scale, void* stream);
 /* Synchronous SGD: every rank reduces the flat-gradient ranges [seg_begin,seg_end) of the variables it
  * owns out of all ranks' gradient buffers in peer memory and applies them in place (seg_param); flag barriers in peer memory on entry and exit.  One rank per
- * GPU (the kernel spins on peers).  A wait is abandoned - parameters untouched, local_sync[2] != 0 - when
+ * GPU (the kernel spins on peers).  epoch = 0 takes the epoch from local_sync[3] (device side), which lets
+ * the launch be replayed from a CUDA graph.  A wait is abandoned - parameters untouched, local_sync[2] != 0 - when
  * *abort_flag becomes non-zero (a rank is leaving) or after timeout_s seconds, so a lost rank cannot hang
  * the others' GPUs.  No counterpart in the reference (async only); semantic model is
  * TF1 SyncReplicasOptimizer. */
@@ -102,6 +103,10 @@ int dtfe_sync_rs_apply_f32(const float* const* grads, unsigned* const* flags, in
                            unsigned epoch, unsigned* local_sync, int* global_step_or_null,
                            const unsigned* abort_flag_or_null, double timeout_s, void* stream);
 int dtfe_sync_max_ranks(void);
+/* On-device batch sampling (TF1 DataSet.next_batch on resident data): gathers the rows
+ * idx[*cursor * B .. +B) of X/labels into a dense batch; the cursor is device memory. */
+int dtfe_gather_rows_f32(const float* X, long ldx, const int* labels, const int* idx, const int* cursor, int B,
+                         int D, float* Xout, int* Yout, void* stream);
 
 /* ---- the whole reference training step in one cooperative kernel ------------------------------- */
 /* pull -> fwd -> xent/accuracy -> bwd -> push+apply -> global_step for nsteps consecutive steps
@@ -118,6 +123,10 @@ typedef struct dtfe_mlp2_launch {
   float* loss_out; float* acc_out; int* step_out;   /* [nsteps] each */
   float lr; int nsteps; int atomic; int train; int remote;
   long long* dbg;                     /* NULL, or [nsteps][grid][8] globaltimer stamps */
+  float *gW1, *gb1, *gW2, *gb2;       /* all NULL (async: push), or sync mode: raw gradients stored here, no push,
+                                         no global_step increment (dtfe_sync_rs_apply_f32 does both) */
+  int* cursor;                        /* NULL, or device int: batches start at batch_idx[*cursor * B]; advanced by
+                                         nsteps at kernel end (lets a captured graph walk through the data) */
 } dtfe_mlp2_launch;
 int dtfe_mlp2_step_grid(int D, int ks);
 size_t dtfe_mlp2_step_workspace_words(int B, int D, int H, int C, int ks);

@@ -49,6 +49,23 @@ def main():
         np.testing.assert_allclose(store.read(n), r, rtol=1e-3, atol=2e-4, err_msg=f"sync {n}")
     assert store.read("global/global_step").item() == nsteps, store.read("global/global_step")
     dist.barrier()
+    # same thing with the fused step kernel writing into the exchange buffer (what bench --mode sync runs)
+    fs = FusedMlp2Stepper(spec, B, [store.tensor(n) for n in names], store.tensor("global/global_step"), lr, dev,
+                          remote=True, grad_buffers=sg.grad_views(shapes))
+    fs.cursor = torch.zeros(1, dtype=torch.int32, device=dev)
+    order = torch.arange(4000, device=dev, dtype=torch.int32).view(-1, world, B)[:, rank, :].contiguous().view(-1)
+    fs.cursor.fill_(nsteps)
+    for s in range(nsteps, 2 * nsteps):
+        fs.run(X, Y, nsteps=1, batch_idx=order)
+        sg.reduce_scatter_apply(lr)
+    torch.cuda.synchronize(); dist.barrier()
+    for s in range(nsteps, 2 * nsteps):
+        rows = slice(s * world * B, (s + 1) * world * B)
+        oracle.sgd_step(ref, x[rows].astype(np.float64), y[rows].astype(np.int64), lr)
+    for n, r in zip(names, ref):
+        np.testing.assert_allclose(store.read(n), r, rtol=1e-3, atol=3e-4, err_msg=f"sync fused {n}")
+    assert store.read("global/global_step").item() == 2 * nsteps and fs.cursor.item() == 2 * nsteps
+    dist.barrier()
     sg.close(); store.close()
 
     # ---------------- async: conservation of pushed deltas with exact arithmetic ---------------
