@@ -124,6 +124,8 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
   // ---- software prefetch state -------------------------------------------------------------------
   // Batch rows are data dependent (index -> row), i.e. two chained global loads.  Indices are fetched
   // two steps ahead and the X slice one step ahead, so neither latency is ever on the critical path.
+  // device-side cursor: this launch processes batches cursor .. cursor+nsteps-1 of batch_idx
+  const long sbase = a.cursor ? (long)*reinterpret_cast<volatile int*>(a.cursor) : 0;
   constexpr int kXPer = (kMaxB * KS + kThreads - 1) / kThreads;
   float xnext[kXPer];
   long rownext[kXPer];
@@ -151,8 +153,6 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
       xnext[i] = v;
     }
   };
-  // device-side cursor: this launch processes batches cursor .. cursor+nsteps-1 of batch_idx
-  const long sbase = a.cursor ? (long)*reinterpret_cast<volatile int*>(a.cursor) : 0;
   fetch_rows(0);
   fetch_x(0);
   fetch_rows(1);
