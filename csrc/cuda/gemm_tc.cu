@@ -49,6 +49,8 @@ struct GemmTcArgs {
   float alpha;                     // EPI_PUSH scale (-lr)
   int act;                         // 0 none, 1 sigmoid
   float* G; long ldg;              // optional fp32 raw gradient copy (EPI_PUSH), may be null
+  int nparts; int rows_per_part;   // EPI_PUSH into a row-partitioned variable: row m lives in Dparts[m / rows_per_part]
+  void* Dparts[8];
 };
 
 // ---------------------------------------------------------------- PTX wrappers
@@ -186,9 +188,17 @@ __device__ __forceinline__ void epilogue_chunk(const GemmTcArgs& g, int m, int n
 #pragma unroll
       for (int j = 0; j < 32; ++j) if (j < nvalid) gp[j] = v[j];
     }
-    if (g.D == nullptr) return;
+    // Row-partitioned variable: each block of rows is owned by a different ps shard (usually a different GPU)
+    void* dbase = g.D;
+    int mrow = m;
+    if (g.nparts) {
+      int part = m / g.rows_per_part;
+      dbase = g.Dparts[part];
+      mrow = m - part * g.rows_per_part;
+    }
+    if (dbase == nullptr) return;
     if (g.out_dtype == OUT_F32) {
-      float* w = (float*)g.D + (long)m * g.ldd + n0;
+      float* w = (float*)dbase + (long)mrow * g.ldd + n0;
       if (nvalid == 32 && ((reinterpret_cast<uintptr_t>(w) & 15) == 0)) {
 #pragma unroll
         for (int q = 0; q < 8; ++q)
@@ -199,7 +209,7 @@ __device__ __forceinline__ void epilogue_chunk(const GemmTcArgs& g, int m, int n
         for (int j = 0; j < 32; ++j) if (j < nvalid) dtfe::red_add_sys(w + j, g.alpha * v[j]);
       }
     } else {
-      __nv_bfloat16* w = (__nv_bfloat16*)g.D + (long)m * g.ldd + n0;
+      __nv_bfloat16* w = (__nv_bfloat16*)dbase + (long)mrow * g.ldd + n0;
       if (nvalid == 32 && ((reinterpret_cast<uintptr_t>(w) & 15) == 0)) {
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
@@ -690,6 +700,13 @@ DTFE_API int dtfe_gemm_tc_bf16(const dtfe_gemm_tc* p, void* stream) {
   g.bias = p->bias; g.bias_dtype = p->bias_bf16 ? OUT_BF16 : OUT_F32;
   g.H = (const __nv_bfloat16*)p->H; g.ldh = p->ldh;
   g.alpha = p->alpha; g.act = p->act; g.G = p->G; g.ldg = p->ldg;
+  DTFE_REQUIRE(p->nparts >= 0 && p->nparts <= 8, "gemm_tc: nparts must be in [0,8]");
+  if (p->nparts) {
+    DTFE_REQUIRE(p->epilogue == EPI_PUSH && p->rows_per_part > 0 && (long)p->rows_per_part * p->nparts >= p->M,
+                 "gemm_tc: D_parts is for the push epilogue and must cover M rows");
+    g.nparts = p->nparts; g.rows_per_part = p->rows_per_part;
+    for (int i = 0; i < p->nparts; ++i) g.Dparts[i] = p->D_parts[i];
+  }
   if (p->epilogue == EPI_ACTGRAD) DTFE_REQUIRE(p->H != nullptr, "gemm_tc: EPI_ACTGRAD needs H");
   if (p->epilogue != EPI_PUSH) DTFE_REQUIRE(p->D != nullptr, "gemm_tc: D is null");
   if (two_cta) return launch_epi2(p->epilogue, p->a_mn_major, p->b_mn_major, ta, tb, g, (cudaStream_t)stream);

@@ -459,11 +459,15 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
       DBG_STAMP(5);
       __syncthreads();
       if (tid == 0) {
-        if (a.remote) __threadfence_system(); else __threadfence();
+        // gpu-scope fence + gpu-scope counter chain the CTAs together; only the CTA that finishes last
+        // pays the system-scope fence that orders all of this step's (possibly remote) pushes before the
+        // global_step increment other GPUs can observe.
+        __threadfence();
         DBG_STAMP(6);
         unsigned prev = atomicAdd(a.sync + 2, 1u);
         if (prev == G - 1) {
           a.sync[2] = 0;
+          if (a.remote) __threadfence_system();
           // sync mode: the aggregated update (and its global_step += 1) belongs to the exchange kernel
           int old = a.gW1 ? *reinterpret_cast<volatile int*>(a.global_step) : dtfe::atom_add_sys_s32(a.global_step, 1);
           a.step_out[s] = old;

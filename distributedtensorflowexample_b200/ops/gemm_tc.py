@@ -28,6 +28,8 @@ class _GemmTc(ctypes.Structure):
         ("H", c_void_p), ("ldh", c_long),
         ("alpha", c_float), ("G", c_void_p), ("ldg", c_long),
         ("tile_n", c_int),
+        ("nparts", c_int), ("rows_per_part", c_int),
+        ("D_parts", c_void_p * 8),
     ]
 
 
@@ -43,7 +45,7 @@ def _bf16(t: torch.Tensor, name: str) -> torch.Tensor:
 def gemm_tc(A: torch.Tensor, B: torch.Tensor, M: int, N: int, K: int, a_mn_major: bool, b_mn_major: bool,
             D: Optional[torch.Tensor], epilogue: int = EPI_STORE, bias: Optional[torch.Tensor] = None, act: int = 0,
             H: Optional[torch.Tensor] = None, alpha: float = 0.0, G: Optional[torch.Tensor] = None,
-            tile_n: int = 0) -> None:
+            tile_n: int = 0, D_parts=None) -> None:
     _bf16(A, "A"); _bf16(B, "B")
     p = _GemmTc()
     p.M, p.N, p.K = M, N, K
@@ -64,6 +66,11 @@ def gemm_tc(A: torch.Tensor, B: torch.Tensor, M: int, N: int, K: int, a_mn_major
     if G is not None:
         p.G, p.ldg = G.data_ptr(), G.stride(0)
     p.tile_n = tile_n
+    if D_parts is not None:
+        p.nparts, p.rows_per_part = len(D_parts), D_parts[0].shape[0]
+        p.ldd, p.out_bf16 = D_parts[0].stride(0), int(D_parts[0].dtype == torch.bfloat16)
+        for i, t in enumerate(D_parts):
+            p.D_parts[i] = t.data_ptr()
     check(cuda_ops.lib().dtfe_gemm_tc_bf16(ctypes.byref(p), torch.cuda.current_stream().cuda_stream),
           "dtfe_gemm_tc_bf16")
 
@@ -85,10 +92,14 @@ def dense_bwd_dx_tc(dY, W, Hprev, out, tile_n: int = 0):
 
 
 def dense_bwd_dw_push_tc(X, dY, W, alpha: float, grad_out=None, tile_n: int = 0):
-    """W += alpha * X^T @ dY, pushed from the GEMM epilogue with red.add (W may be peer memory)."""
+    """W += alpha * X^T @ dY, pushed from the GEMM epilogue with red.add (W may be peer memory, or a list of
+    row blocks of a partitioned variable, each in a different shard)."""
     Mb, K = X.shape
     N = dY.shape[1]
-    gemm_tc(X, dY, K, N, Mb, True, True, W, EPI_PUSH, alpha=alpha, G=grad_out, tile_n=tile_n)
+    if isinstance(W, (list, tuple)):
+        gemm_tc(X, dY, K, N, Mb, True, True, None, EPI_PUSH, alpha=alpha, G=grad_out, tile_n=tile_n, D_parts=list(W))
+    else:
+        gemm_tc(X, dY, K, N, Mb, True, True, W, EPI_PUSH, alpha=alpha, G=grad_out, tile_n=tile_n)
 
 
 def smoke() -> None:

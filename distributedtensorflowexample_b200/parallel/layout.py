@@ -32,6 +32,7 @@ class Entry:
     nbytes: int        # bytes reserved in the shard (rows * pitch * itemsize for 2-D tensors)
     trainable: bool
     pitch: int = 0     # row pitch in elements of 2-D tensors (0 = dense)
+    parts: tuple = ()  # row-partitioned variable: ((shard, offset), ...) - part p holds rows [p*R/P, (p+1)*R/P)
 
 
 def _align(n: int, a: int = ALIGN) -> int:
@@ -39,10 +40,14 @@ def _align(n: int, a: int = ALIGN) -> int:
 
 
 class ShardLayout:
-    def __init__(self, variables: Sequence[VariableDef], num_shards: int):
+    def __init__(self, variables: Sequence[VariableDef], num_shards: int, partition_min_bytes: int = 0):
+        """``partition_min_bytes`` > 0: 2-D variables at least this large are split by rows into one part per
+        shard (TF1's partitioned variables / ``min_max_variable_partitioner`` idea), so that no single ps task
+        serves - or ingests the pushes for - a whole big matrix."""
         if num_shards < 1:
             raise ValueError("num_shards must be >= 1")
         self.num_shards = num_shards
+        self.partition_min_bytes = partition_min_bytes
         self.entries: Dict[str, Entry] = {}
         self.order: List[str] = []
         cursor = [HEADER_BYTES] * num_shards
@@ -52,6 +57,20 @@ class ShardLayout:
             k = v.device.task
             if not 0 <= k < num_shards:
                 raise ValueError(f"variable {v.name} placed on ps task {k} but there are {num_shards} shards")
+            if (partition_min_bytes and num_shards > 1 and len(v.shape) == 2 and v.nbytes >= partition_min_bytes
+                    and v.shape[0] % num_shards == 0):
+                item = 2 if v.dtype == "bfloat16" else 4
+                pitch = (v.shape[1] + 7) // 8 * 8 if v.dtype == "bfloat16" else v.shape[1]
+                part_bytes = (v.shape[0] // num_shards) * pitch * item
+                parts = []
+                for pk in range(num_shards):
+                    o = _align(cursor[pk])
+                    parts.append((pk, o))
+                    cursor[pk] = o + part_bytes
+                self.entries[v.name] = Entry(v.name, -1, -1, tuple(v.shape), v.dtype, part_bytes * num_shards,
+                                             v.trainable, pitch if pitch != v.shape[1] else 0, tuple(parts))
+                self.order.append(v.name)
+                continue
             off = _align(cursor[k])
             nbytes, pitch = v.nbytes, 0
             if len(v.shape) == 2 and v.dtype == "bfloat16" and v.shape[1] % 8:
@@ -71,7 +90,8 @@ class ShardLayout:
         return list(self.order)
 
     def shard_entries(self, k: int) -> List[Entry]:
-        return [self.entries[n] for n in self.order if self.entries[n].shard == k]
+        return [self.entries[n] for n in self.order
+                if self.entries[n].shard == k or any(pk == k for pk, _ in self.entries[n].parts)]
 
     def describe(self) -> str:
         lines = []

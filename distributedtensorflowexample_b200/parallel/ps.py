@@ -27,12 +27,13 @@ _TORCH_DTYPES = {"float32": torch.float32, "int32": torch.int32, "bfloat16": tor
 
 
 class PeerParamStore:
-    def __init__(self, variables: Sequence[VariableDef], num_shards: int, device: torch.device):
+    def __init__(self, variables: Sequence[VariableDef], num_shards: int, device: torch.device,
+                 partition_min_bytes: int = 0):
         from ..ops import cuda_ops
         self._ops = cuda_ops
         self.device = torch.device(device)
         self.variables = list(variables)
-        self.layout = ShardLayout(self.variables, num_shards)
+        self.layout = ShardLayout(self.variables, num_shards, partition_min_bytes)
         self.num_shards = num_shards
         self._base: List[Optional[int]] = [None] * num_shards     # device pointers (local or peer-mapped)
         self._owned: List[bool] = [False] * num_shards
@@ -103,10 +104,37 @@ class PeerParamStore:
                                                          self.device, owner=self)
         return self._headers[k]
 
+    def is_partitioned(self, name: str) -> bool:
+        return bool(self.layout[name].parts)
+
+    def parts(self, name: str) -> List[torch.Tensor]:
+        """Row blocks of a partitioned variable, one per shard (block p lives in shard p's HBM)."""
+        key = name + "//parts"
+        ts = self._views.get(key)
+        if ts is None:
+            e = self.layout[name]
+            if not e.parts:
+                raise KeyError(f"{name} is not partitioned")
+            rp = e.shape[0] // len(e.parts)
+            pitch = e.pitch or e.shape[1]
+            ts = []
+            for shard, off in e.parts:
+                full = self._ops.tensor_from_ptr(self.base_ptr(shard) + off, (rp, pitch), _TORCH_DTYPES[e.dtype],
+                                                 self.device, owner=self)
+                ts.append(full[:, :e.shape[1]])
+            self._views[key] = ts
+        return ts
+
+    def param_handle(self, name: str):
+        """What a step engine binds to: a tensor, or the list of row blocks of a partitioned variable."""
+        return self.parts(name) if self.is_partitioned(name) else self.tensor(name)
+
     def tensor(self, name: str) -> torch.Tensor:
         t = self._views.get(name)
         if t is None:
             e = self.layout[name]
+            if e.parts:
+                raise KeyError(f"{name} is row-partitioned over {len(e.parts)} shards; use parts()/param_handle()")
             if e.pitch:
                 full = self._ops.tensor_from_ptr(self.base_ptr(e.shard) + e.offset, (e.shape[0], e.pitch),
                                                  _TORCH_DTYPES[e.dtype], self.device, owner=self)
@@ -118,26 +146,37 @@ class PeerParamStore:
         return t
 
     def shard_of(self, name: str) -> int:
+        """Owning shard (-1 for a row-partitioned variable, which every shard owns a block of)."""
         return self.layout[name].shard
 
     # ---- chief duties -------------------------------------------------------------------
     def initialize(self, rng: np.random.Generator, only_owned: bool = False) -> None:
         """Run every variable's initializer (reference ``global_init_op``, worker.py:98-99)."""
         for v in self.variables:
-            if only_owned and not self._owned[self.layout[v.name].shard]:
+            if only_owned and self.layout[v.name].shard >= 0 and not self._owned[self.layout[v.name].shard]:
                 continue
             val = v.initializer(v.shape, v.dtype, rng)
             self.assign(v.name, val)
         torch.cuda.synchronize(self.device)
 
     def assign(self, name: str, value) -> None:
+        if self.is_partitioned(name):
+            parts = self.parts(name)
+            src = torch.as_tensor(np.asarray(value)).to(device=self.device, dtype=parts[0].dtype)
+            rp = parts[0].shape[0]
+            for p, t in enumerate(parts):
+                t.copy_(src[p * rp:(p + 1) * rp])
+            return
         t = self.tensor(name)
         src = torch.as_tensor(np.asarray(value)).to(device=self.device, dtype=t.dtype)
         t.copy_(src.reshape(t.shape))
 
     def read(self, name: str) -> np.ndarray:
         e = self.layout[name]
-        t = self.tensor(name).detach()
+        if e.parts:
+            t = torch.cat([p.detach() for p in self.parts(name)], dim=0)
+        else:
+            t = self.tensor(name).detach()
         arr = t.float().cpu().numpy() if t.dtype == torch.bfloat16 else t.cpu().numpy()
         return arr.reshape(e.shape)
 

@@ -18,10 +18,10 @@ from .ps import PeerParamStore
 
 
 def build_spmd_store(spec: MLPSpec, rank: int, world: int, device: torch.device, seed: Optional[int] = 0,
-                     num_ps: Optional[int] = None, ps_strategy: str = "round_robin"):
+                     num_ps: Optional[int] = None, ps_strategy: str = "round_robin", partition_min_bytes: int = 0):
     num_ps = world if num_ps is None else num_ps
     model = build_replicated_model(spec, "worker", rank, num_ps=num_ps, ps_strategy=ps_strategy)
-    store = PeerParamStore(model.global_all, num_ps, device)
+    store = PeerParamStore(model.global_all, num_ps, device, partition_min_bytes=partition_min_bytes)
     mine = [k for k in range(num_ps) if k % world == rank]
     store.allocate(mine)
     if world > 1:

@@ -209,12 +209,20 @@ class TcStepper:
         from ..ops import gemm_tc
         self.G = gemm_tc
         self.spec, self.batch, self.lr, self.tile_n = spec, batch, lr, tile_n
-        self.params = list(params)
+        self.params = list(params)      # tensors, or lists of row blocks for partitioned variables
         self.global_step = global_step
         dev = torch.device(device)
         dims = spec.dims
         pad8 = lambda n: (n + 7) // 8 * 8
         bf = dict(device=dev, dtype=torch.bfloat16)
+        # A partitioned weight is read many times per step by the GEMMs (once per M tile), and peer reads
+        # bypass the local L2, so its blocks are pulled ONCE per step into a local replica (the reference's
+        # sync_op, worker.py:81-85, as one L1-bypassing vector copy per block) and the GEMMs read that.
+        self.replicas = {}
+        for i, p in enumerate(self.params):
+            if isinstance(p, (list, tuple)):
+                rows = sum(b.shape[0] for b in p)
+                self.replicas[i] = torch.empty(rows, p[0].stride(0), **bf)[:, :p[0].shape[1]]
         self.acts = [torch.empty(batch, pad8(d), **bf)[:, :d] for d in dims[1:-1]]
         C = dims[-1]
         self.logits = torch.empty(batch, pad8(C), device=dev, dtype=torch.float32)[:, :C]
@@ -229,13 +237,27 @@ class TcStepper:
         L = spec.num_layers
         self.launches_per_call = L + 2 + (L - 1) + 2 * L + 1
 
+    def pull_partitioned(self) -> None:
+        for i, rep in self.replicas.items():
+            rp = self.params[i][0].shape[0]
+            for k, blk in enumerate(self.params[i]):
+                dst = rep[k * rp:(k + 1) * rp]
+                # blocks and replica rows share the pitch, so each block is one contiguous byte range
+                n = rp * blk.stride(0)
+                ops.pull(torch.as_strided(dst, (n,), (1,)).view(torch.float32),
+                         torch.as_strided(blk, (n,), (1,)).view(torch.float32))
+
+    def _w(self, i):
+        return self.replicas[i] if i in self.replicas else self.params[i]
+
     def forward(self, X: torch.Tensor, acts=None, logits=None) -> torch.Tensor:
         acts = self.acts if acts is None else acts
         logits = self.logits if logits is None else logits
         h = X
         L = self.spec.num_layers
+        self.pull_partitioned()
         for l in range(L):
-            W, b = self.params[2 * l], self.params[2 * l + 1]
+            W, b = self._w(2 * l), self.params[2 * l + 1]
             last = l == L - 1
             out = logits if last else acts[l]
             self.G.dense_fwd_tc(h, W, b, ops.ACT_NONE if last else ops.ACT_SIGMOID, out, tile_n=self.tile_n)
@@ -257,7 +279,7 @@ class TcStepper:
             h_in = X if l == 0 else self.acts[l - 1]
             d_prev = None
             if l > 0:   # against the pre-update weights, so before this layer's push
-                d_prev = self.G.dense_bwd_dx_tc(d, W, h_in, self.dacts[l - 1], tile_n=self.tile_n)
+                d_prev = self.G.dense_bwd_dx_tc(d, self._w(2 * l), h_in, self.dacts[l - 1], tile_n=self.tile_n)
             self.G.dense_bwd_dw_push_tc(h_in, d, W, alpha, tile_n=self.tile_n)
             ops.bias_grad_push_bf16(d, b, alpha)
             d = d_prev

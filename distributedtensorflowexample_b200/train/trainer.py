@@ -163,4 +163,5 @@ class GpuTrainer:
         return float(correct.item()) / float(total)
 
     def snapshot_params(self) -> List[np.ndarray]:
-        return [p.detach().float().cpu().numpy() for p in self.params]
+        return [(torch.cat(list(p), 0) if isinstance(p, (list, tuple)) else p).detach().float().cpu().numpy()
+                for p in self.params]

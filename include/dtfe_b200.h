@@ -180,6 +180,8 @@ typedef struct dtfe_gemm_tc {
   const void* H; long ldh;
   float alpha; float* G; long ldg;
   int tile_n;
+  int nparts; int rows_per_part;      /* push epilogue into a row-partitioned variable: row m of the result goes to */
+  void* D_parts[8];                   /* D_parts[m / rows_per_part] (one block per ps shard); D is then ignored        */
 } dtfe_gemm_tc;
 int dtfe_gemm_tc_bf16(const dtfe_gemm_tc* p, void* stream);
 

@@ -10,14 +10,15 @@ from distributedtensorflowexample_b200.models.mlp import MLPSpec
 from distributedtensorflowexample_b200.train.replica import build_replicated_model
 
 
+@pytest.mark.parametrize("partition", [0, 1])
 @pytest.mark.parametrize("dims,B", [((784, 256, 128, 10), 128), ((784, 512, 10), 200)])
-def test_tc_step_matches_oracle(dims, B):
+def test_tc_step_matches_oracle(dims, B, partition):
     from distributedtensorflowexample_b200.parallel.ps import PeerParamStore
     from distributedtensorflowexample_b200.train.gpu_step import TcStepper
     from distributedtensorflowexample_b200.data import synthetic_arrays
     spec = MLPSpec(dims, param_dtype="bfloat16")
     model = build_replicated_model(spec, num_ps=2)
-    store = PeerParamStore(model.global_all, 2, torch.device("cuda:0"))
+    store = PeerParamStore(model.global_all, 2, torch.device("cuda:0"), partition_min_bytes=(64 << 10) if partition else 0)
     store.allocate()
     rng = np.random.default_rng(0)
     names = [v.name for v in model.global_trainable]
@@ -25,13 +26,17 @@ def test_tc_step_matches_oracle(dims, B):
         store.assign(v.name, (rng.normal(size=v.shape) * 0.05).astype(np.float32))
     W_last = store.tensor(names[-2])
     assert W_last.shape == (dims[-2], 10) and W_last.stride(0) == 16          # padded pitch inside the shard
+    assert store.is_partitioned(names[0]) == bool(partition)                   # W1 (>= 64 KB) is split by rows
+    if partition:
+        blocks = store.parts(names[0])
+        assert len(blocks) == 2 and blocks[0].shape == (392, dims[1]) and store.shard_of(names[0]) == -1
     params_np = [store.read(n).astype(np.float64) for n in names]              # bf16-rounded values
     x, y = synthetic_arrays(B, seed=3)
     xb = torch.tensor(x, device="cuda").bfloat16()
     X = xb
     Y = torch.tensor(y.astype(np.int32), device="cuda")
     lr = 0.5
-    st = TcStepper(spec, B, [store.tensor(n) for n in names], store.tensor("global/global_step"), lr, "cuda:0")
+    st = TcStepper(spec, B, [store.param_handle(n) for n in names], store.tensor("global/global_step"), lr, "cuda:0")
     st.run(X, Y)
     torch.cuda.synchronize()
     loss, acc, grads = oracle.gradients(params_np, xb.float().cpu().numpy().astype(np.float64), y.astype(np.int64))
