@@ -28,6 +28,8 @@
 // per-row loss/correct flags and three sync words.
 #include "common.cuh"
 #include <math.h>
+#include <stdlib.h>
+#include <time.h>
 
 namespace {
 
@@ -621,8 +623,10 @@ struct HostFeed {
   int B, D, dev;
   float* xs[2];
   int* ys[2];
-  cudaStream_t copy;
-  cudaEvent_t copied[2], consumed[2];
+  float* out[2];                       // per-slot {loss, acc} + int step written by the kernel
+  int* step[2];
+  cudaStream_t copy, back;             // H2D and D2H side streams
+  cudaEvent_t copied[2], done[2], readback[2];
 };
 }  // namespace
 
@@ -634,10 +638,14 @@ DTFE_API int dtfe_hostfeed_create(int B, int D, void** out) {
   for (int i = 0; i < 2; ++i) {
     DTFE_CUDA_CHECK(cudaMalloc(&h->xs[i], (size_t)B * D * sizeof(float)));
     DTFE_CUDA_CHECK(cudaMalloc(&h->ys[i], (size_t)B * sizeof(int)));
+    DTFE_CUDA_CHECK(cudaMalloc(&h->out[i], 4 * sizeof(float)));
+    h->step[i] = reinterpret_cast<int*>(h->out[i] + 2);
     DTFE_CUDA_CHECK(cudaEventCreateWithFlags(&h->copied[i], cudaEventDisableTiming));
-    DTFE_CUDA_CHECK(cudaEventCreateWithFlags(&h->consumed[i], cudaEventDisableTiming));
+    DTFE_CUDA_CHECK(cudaEventCreateWithFlags(&h->done[i], cudaEventDisableTiming));
+    DTFE_CUDA_CHECK(cudaEventCreateWithFlags(&h->readback[i], cudaEventDisableTiming));
   }
   DTFE_CUDA_CHECK(cudaStreamCreateWithFlags(&h->copy, cudaStreamNonBlocking));
+  DTFE_CUDA_CHECK(cudaStreamCreateWithFlags(&h->back, cudaStreamNonBlocking));
   *out = h;
   return 0;
 }
@@ -646,17 +654,20 @@ DTFE_API int dtfe_hostfeed_destroy(void* handle) {
   HostFeed* h = static_cast<HostFeed*>(handle);
   if (!h) return 0;
   for (int i = 0; i < 2; ++i) {
-    cudaFree(h->xs[i]); cudaFree(h->ys[i]);
-    cudaEventDestroy(h->copied[i]); cudaEventDestroy(h->consumed[i]);
+    cudaFree(h->xs[i]); cudaFree(h->ys[i]); cudaFree(h->out[i]);
+    cudaEventDestroy(h->copied[i]); cudaEventDestroy(h->done[i]); cudaEventDestroy(h->readback[i]);
   }
   cudaStreamDestroy(h->copy);
+  cudaStreamDestroy(h->back);
   delete h;
   return 0;
 }
 
 // launch: B/D/H/C/ks, parameter pointers, workspace, lr, atomic, train, remote are used; X/labels/
 // batch_idx/nsteps are supplied per step from the host batches.  loss_host (pinned, [nsteps]) receives
-// one float per step; launch->acc_out / step_out keep the last step's values on the device.
+// one float per step.  Three streams keep everything off the kernels' critical path: H2D copies of
+// batch i+1 run under step i, and the D2H read of step i's loss runs under step i+1; on return the
+// caller's stream waits for the last read-back, so synchronising it makes every loss_host[i] valid.
 DTFE_API int dtfe_mlp2_train_host(void* handle, const dtfe_mlp2_launch* launch, const float* const* x_host,
                                   const int* const* y_host, int nsteps, float* loss_host, void* stream) {
   HostFeed* h = static_cast<HostFeed*>(handle);
@@ -668,17 +679,32 @@ DTFE_API int dtfe_mlp2_train_host(void* handle, const dtfe_mlp2_launch* launch, 
   Mlp2Args a{};
   for (int i = 0; i < nsteps; ++i) {
     const int s = i & 1;
-    DTFE_CUDA_CHECK(cudaStreamWaitEvent(h->copy, h->consumed[s], 0));
+    // H2D: the staging slot is free once the step that last read it has finished
+    DTFE_CUDA_CHECK(cudaStreamWaitEvent(h->copy, h->done[s], 0));
     DTFE_CUDA_CHECK(cudaMemcpyAsync(h->xs[s], x_host[i], (size_t)h->B * h->D * sizeof(float), cudaMemcpyHostToDevice, h->copy));
     DTFE_CUDA_CHECK(cudaMemcpyAsync(h->ys[s], y_host[i], (size_t)h->B * sizeof(int), cudaMemcpyHostToDevice, h->copy));
     DTFE_CUDA_CHECK(cudaEventRecord(h->copied[s], h->copy));
+    // step: needs its batch, and its output slot must have been read back
     DTFE_CUDA_CHECK(cudaStreamWaitEvent(st, h->copied[s], 0));
+    DTFE_CUDA_CHECK(cudaStreamWaitEvent(st, h->readback[s], 0));
     L.X = h->xs[s]; L.labels = h->ys[s];
+    L.loss_out = h->out[s]; L.acc_out = h->out[s] + 1; L.step_out = h->step[s];
     if (int rc = mlp2_fill(L, a)) return rc;
     int rc = L.ks == 8 ? mlp2_launch<8>(a, st) : mlp2_launch<16>(a, st);
     if (rc) return rc;
-    DTFE_CUDA_CHECK(cudaEventRecord(h->consumed[s], st));
-    DTFE_CUDA_CHECK(cudaMemcpyAsync(loss_host + i, L.loss_out, sizeof(float), cudaMemcpyDeviceToHost, st));
+    DTFE_CUDA_CHECK(cudaEventRecord(h->done[s], st));
+    // D2H of this step's loss on the read-back stream
+    DTFE_CUDA_CHECK(cudaStreamWaitEvent(h->back, h->done[s], 0));
+    DTFE_CUDA_CHECK(cudaMemcpyAsync(loss_host + i, h->out[s], sizeof(float), cudaMemcpyDeviceToHost, h->back));
+    DTFE_CUDA_CHECK(cudaEventRecord(h->readback[s], h->back));
+  }
+  if (nsteps > 0) {
+    DTFE_CUDA_CHECK(cudaStreamWaitEvent(st, h->readback[(nsteps - 1) & 1], 0));
+    if (nsteps > 1) DTFE_CUDA_CHECK(cudaStreamWaitEvent(st, h->readback[nsteps & 1], 0));
+    // keep the caller-visible output views (launch->loss_out etc.) in step with the last step
+    DTFE_CUDA_CHECK(cudaMemcpyAsync(launch->loss_out, h->out[(nsteps - 1) & 1], sizeof(float), cudaMemcpyDeviceToDevice, st));
+    DTFE_CUDA_CHECK(cudaMemcpyAsync(launch->acc_out, h->out[(nsteps - 1) & 1] + 1, sizeof(float), cudaMemcpyDeviceToDevice, st));
+    DTFE_CUDA_CHECK(cudaMemcpyAsync(launch->step_out, h->step[(nsteps - 1) & 1], sizeof(int), cudaMemcpyDeviceToDevice, st));
   }
   return 0;
 }

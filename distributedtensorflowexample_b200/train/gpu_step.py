@@ -219,6 +219,8 @@ class TcStepper:
         # bypass the local L2, so its blocks are pulled ONCE per step into a local replica (the reference's
         # sync_op, worker.py:81-85, as one L1-bypassing vector copy per block) and the GEMMs read that.
         self.replicas = {}
+        self._pull_stream = None
+        self._pending = set()
         for i, p in enumerate(self.params):
             if isinstance(p, (list, tuple)):
                 rows = sum(b.shape[0] for b in p)
@@ -238,17 +240,34 @@ class TcStepper:
         self.launches_per_call = L + 2 + (L - 1) + 2 * L + 1
 
     def pull_partitioned(self) -> None:
-        for i, rep in self.replicas.items():
-            rp = self.params[i][0].shape[0]
-            for k, blk in enumerate(self.params[i]):
-                dst = rep[k * rp:(k + 1) * rp]
-                # blocks and replica rows share the pitch, so each block is one contiguous byte range
-                n = rp * blk.stride(0)
-                ops.pull(torch.as_strided(dst, (n,), (1,)).view(torch.float32),
-                         torch.as_strided(blk, (n,), (1,)).view(torch.float32))
+        """Issue this step's pulls on a side stream, one event per variable: the copy of layer l+1's
+        weights over NVLink runs under layer l's GEMM; ``_w`` makes the consumer wait for its own event."""
+        if not self.replicas:
+            return
+        if self._pull_stream is None:
+            self._pull_stream = torch.cuda.Stream(device=self.loss.device)
+            self._pull_events = {i: torch.cuda.Event() for i in self.replicas}
+        main = torch.cuda.current_stream()
+        self._pull_stream.wait_stream(main)        # previous step's readers of the replicas are done
+        with torch.cuda.stream(self._pull_stream):
+            for i, rep in self.replicas.items():
+                rp = self.params[i][0].shape[0]
+                for k, blk in enumerate(self.params[i]):
+                    dst = rep[k * rp:(k + 1) * rp]
+                    # blocks and replica rows share the pitch, so each block is one contiguous byte range
+                    n = rp * blk.stride(0)
+                    ops.pull(torch.as_strided(dst, (n,), (1,)).view(torch.float32),
+                             torch.as_strided(blk, (n,), (1,)).view(torch.float32))
+                self._pull_events[i].record(self._pull_stream)
+        self._pending = set(self.replicas)
 
     def _w(self, i):
-        return self.replicas[i] if i in self.replicas else self.params[i]
+        if i in self.replicas:
+            if i in self._pending:
+                torch.cuda.current_stream().wait_event(self._pull_events[i])
+                self._pending.discard(i)
+            return self.replicas[i]
+        return self.params[i]
 
     def forward(self, X: torch.Tensor, acts=None, logits=None) -> torch.Tensor:
         acts = self.acts if acts is None else acts
