@@ -42,9 +42,3 @@ def build_spmd_store(spec: MLPSpec, rank: int, world: int, device: torch.device,
         dist.barrier()
     assert store.is_ready()
     return model, store
-
-
-def exchange_buffer_ptrs(t: torch.Tensor, rank: int, world: int, keep: list) -> List[int]:
-    """Make a cudaMalloc'd buffer of every rank addressable from every rank; returns device pointers
-    indexed by rank.  ``t`` must have been created with ``cuda_ops.shard_alloc`` (IPC needs the base)."""
-    raise NotImplementedError

@@ -153,3 +153,25 @@ def test_shell_launchers_keep_reference_knobs():
     out = subprocess.run(["bash", os.path.join(root, "run_single_gpu.sh")], capture_output=True, text=True,
                          env={**os.environ, "MODE": "print"}, timeout=60).stdout
     assert out.count("new-window") == 2 and "--num_workers 2 --num_gpus 1" in out
+
+
+def test_shard_layout_offsets_pitch_and_partitioning():
+    from distributedtensorflowexample_b200.models.mlp import MLPSpec, reference_mlp_spec
+    from distributedtensorflowexample_b200.parallel.layout import ShardLayout, HEADER_BYTES
+    from distributedtensorflowexample_b200.train.replica import build_replicated_model
+    m = build_replicated_model(reference_mlp_spec(), num_ps=1)
+    lay = ShardLayout(m.global_all, 1)
+    offs = [lay[n].offset for n in lay.names()]
+    assert offs[0] == HEADER_BYTES and all(o % 256 == 0 for o in offs) and offs == sorted(offs)
+    assert lay["global/dense/kernel"].nbytes == 313600 and lay["global/global_step"].nbytes == 4
+    assert lay.shard_bytes[0] >= offs[-1] + 4
+    # bf16 matrices with a width that is not a multiple of 8 get a padded pitch (TMA needs 16-byte rows)
+    wide = build_replicated_model(MLPSpec((784, 64, 10), param_dtype="bfloat16"), num_ps=4)
+    lay = ShardLayout(wide.global_all, 4, partition_min_bytes=64 << 10)
+    e = lay["global/dense_1/kernel"]
+    assert e.pitch == 16 and e.nbytes == 64 * 16 * 2 and not e.parts
+    w1 = lay["global/dense/kernel"]                      # 784x64 bf16 = 100352 B >= 64 KB, 784 % 4 == 0
+    assert w1.shard == -1 and [p[0] for p in w1.parts] == [0, 1, 2, 3] and w1.nbytes == 784 * 64 * 2
+    assert all(any(x.name == "global/dense/kernel" for x in lay.shard_entries(k)) for k in range(4))
+    with pytest.raises(ValueError):
+        ShardLayout(wide.local_all, 4)                   # local/* variables are not on the ps job
