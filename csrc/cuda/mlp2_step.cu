@@ -59,7 +59,7 @@ struct Mlp2Args {
   int atomic;
   int train;                // 0: forward/metrics only (no phase C)
   int remote;               // some shard lives on a peer GPU: completion fence must be .sys
-  long long* dbg;           // optional [nsteps][G][8] globaltimer stamps (profiling)
+  long long* dbg;           // optional [nsteps][G][16] globaltimer stamps (profiling)
   float *gW1, *gb1, *gW2, *gb2;  // sync mode: raw gradients are stored here instead of being pushed
   int* cursor;              // optional device-side step cursor: batches start at *cursor (graph replay)
 };
@@ -84,7 +84,7 @@ __device__ __forceinline__ long long gtime() {
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
   return t;
 }
-#define DBG_STAMP(i) do { if (a.dbg && tid == 0) a.dbg[((long)s * G + g) * 8 + (i)] = gtime(); } while (0)
+#define DBG_STAMP(i) do { if (a.dbg && tid == 0) a.dbg[((long)s * G + g) * 16 + (i)] = gtime(); } while (0)
 
 __device__ __forceinline__ void push1(float* p, float v, int atomic) {
   if (atomic) dtfe::red_add_sys(p, v);
@@ -114,6 +114,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
   float* red = dzs + 2 * kMaxC;           // [256]
   float* dZs = red + kThreads;            // [B][C]
   float* dAs = dZs + kMaxB * kMaxC;       // [B][H]  (phase C)
+  float* red_part = dAs;                  // [2][8][kMaxH] phase-B scratch, aliases dAs (never live together)
   (void)red;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -130,15 +131,16 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
   const long sbase = a.cursor ? (long)*reinterpret_cast<volatile int*>(a.cursor) : 0;
   constexpr int kXPer = (kMaxB * KS + kThreads - 1) / kThreads;
   float xnext[kXPer];
-  long rownext[kXPer];
+  int rownext[kXPer];       // kept as loaded (int): converting would make the warp wait for the load right here
+  int ylab_row = 0;         // dataset row of the first batch row this thread's slot handles in phase B
   auto fetch_rows = [&](int st) {
 #pragma unroll
     for (int i = 0; i < kXPer; ++i) {
       int e = tid + i * kThreads;
-      long row = 0;
+      int row = 0;
       if (e < B * KS && st < a.nsteps) {
         int r = e / KS;
-        row = a.batch_idx ? (long)__ldg(a.batch_idx + (sbase + st) * B + r) : (sbase + st) * a.rows_per_step + r;
+        row = a.batch_idx ? __ldg(a.batch_idx + (sbase + st) * B + r) : (int)((sbase + st) * a.rows_per_step + r);
       }
       rownext[i] = row;
     }
@@ -150,7 +152,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
       float v = 0.f;
       if (e < B * KS && st < a.nsteps) {
         int k = k0 + e % KS;
-        if (k < D) v = __ldg(a.X + rownext[i] * a.ldx + k);
+        if (k < D) v = __ldg(a.X + (long)rownext[i] * a.ldx + k);
       }
       xnext[i] = v;
     }
@@ -160,6 +162,12 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
   fetch_rows(1);
 
   const int slot = tid >> 7, t = tid & 127, wq = warp & 3;   // phase B roles: 2 rows per CTA, 4 warps each
+  auto fetch_label_row = [&](int st) {
+    int r = 2 * g + slot;
+    if (r < B && st < a.nsteps)
+      ylab_row = a.batch_idx ? __ldg(a.batch_idx + (sbase + st) * B + r) : (int)((sbase + st) * a.rows_per_step + r);
+  };
+  fetch_label_row(0);
 
   for (int s = 0; s < a.nsteps; ++s) {
     // ------------------------------ phase A ------------------------------------
@@ -176,13 +184,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
     }
     // label of the first row this thread's slot handles in phase B (latency hidden behind phase A)
     int ylab = 0;
-    {
-      int r = 2 * g + slot;
-      if (r < B) {
-        long row = a.batch_idx ? (long)__ldg(a.batch_idx + (sbase + s) * B + r) : (sbase + s) * a.rows_per_step + r;
-        ylab = __ldg(a.labels + row);
-      }
-    }
+    if (2 * g + slot < B) ylab = __ldg(a.labels + ylab_row);   // row index arrived a step ago
     __syncthreads();
     {
       // W slice in registers once; X rows as broadcast float4 loads: KS/4 + 0 shared loads per 4*KS FMAs
@@ -220,6 +222,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
     // Next step's X slice and the rows after that: issued now, consumed a whole step later.
     fetch_x(s + 1);
     fetch_rows(s + 2);
+    fetch_label_row(s + 1);
     // Small parameters are read after the barrier so that every CTA sees the pushes all CTAs made in
     // the previous step's phase C.  They go to registers first; the reduction loads below are issued
     // before anything waits, so all of it shares one L2 round trip.
@@ -237,35 +240,39 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
       const int r = r0 + slot;
       const bool rv = r < B;
       float z = 0.f;
-      if (rv && t < H) {
+      const bool vec_reduce = (H & 3) == 0;
+      if (vec_reduce) {
+        // Cooperative float4 reduction of the G split-K partials of row r: thread = (column quad, partial
+        // group); every thread sums ~G/nqg float4 loads in registers, the nqg group sums meet in smem.
+        const int nq4 = H >> 2;                     // float4 columns per row (25)
+        const int nqg = 128 / nq4;                  // partial groups per row slot (5)
+        const int c4 = t % nq4, qg = t / nq4;
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (rv && qg < nqg) {
+          const float4* P4 = reinterpret_cast<const float4*>(a.part + (long)r * H) + c4;
+          const long gs4 = ((long)B * H) >> 2;
+          for (unsigned q0 = qg; q0 < G; q0 += 10 * nqg) {     // up to 10 loads in flight per thread
+            float4 v[10];
+#pragma unroll
+            for (int u = 0; u < 10; ++u) {
+              unsigned q = q0 + u * nqg;
+              v[u] = (q < G) ? __ldcg(P4 + (long)q * gs4) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+#pragma unroll
+            for (int u = 0; u < 10; ++u) { acc.x += v[u].x; acc.y += v[u].y; acc.z += v[u].z; acc.w += v[u].w; }
+          }
+          reinterpret_cast<float4*>(red_part + (slot * 8 + qg) * kMaxH)[c4] = acc;
+        }
+      } else if (rv && t < H) {
         const float* P = a.part + (long)r * H + t;
         const long gs = (long)B * H;
-        // G independent loads: two batches of 16 in flight so the L2 latency is paid about once
-        float z0 = 0.f, z1 = 0.f, z2 = 0.f, z3 = 0.f;
+        float z0 = 0.f, z1 = 0.f;
         unsigned q = 0;
-        float cur[16];
-        const unsigned nb = G / 16;
-        if (nb > 0) {
-#pragma unroll
-          for (int u = 0; u < 16; ++u) cur[u] = __ldcg(P + (long)u * gs);
-          for (unsigned bi = 1; bi <= nb; ++bi) {
-            float nxt[16];
-            if (bi < nb) {
-#pragma unroll
-              for (int u = 0; u < 16; ++u) nxt[u] = __ldcg(P + (long)(bi * 16 + u) * gs);
-            }
-#pragma unroll
-            for (int u = 0; u < 16; u += 4) { z0 += cur[u]; z1 += cur[u + 1]; z2 += cur[u + 2]; z3 += cur[u + 3]; }
-            if (bi < nb) {
-#pragma unroll
-              for (int u = 0; u < 16; ++u) cur[u] = nxt[u];
-            }
-          }
-          q = nb * 16;
-        }
-        for (; q < G; ++q) z0 += __ldcg(P + (long)q * gs);
-        z = (z0 + z1) + (z2 + z3);
+        for (; q + 2 <= G; q += 2) { z0 += __ldcg(P + (long)q * gs); z1 += __ldcg(P + (long)(q + 1) * gs); }
+        if (q < G) z0 += __ldcg(P + (long)q * gs);
+        z = z0 + z1;
       }
+      DBG_STAMP(8);
       if (!params_in_smem) {
 #pragma unroll
         for (int i = 0; i < kW2Per; ++i) {
@@ -280,20 +287,38 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
       if (r0 >= B) break;                    // CTA without rows: parameters staged, nothing else to do
       float h = 0.f;
       if (rv && t < H) {
+        if (vec_reduce) {
+          const int nqg = 128 / (H >> 2);
+          for (int qg = 0; qg < nqg; ++qg) z += red_part[(slot * 8 + qg) * kMaxH + t];
+        }
         h = dtfe::sigmoidf_fast(z + b1s[t]);
         hs[slot * kMaxH + t] = h;
         __stcg(a.Hbuf + (long)r * H + t, h);
       }
       __syncthreads();
-      for (int c = wq; c < C; c += 4) {
-        float p = 0.f;
-        for (int u = lane; u < H; u += 32) p = fmaf(hs[slot * kMaxH + u], W2s[u * C + c], p);
-        p = dtfe::warp_sum(p);
-        if (lane == 0) zs[slot * kMaxC + c] = p + b2s[c];
-      }
-      __syncthreads();
+      DBG_STAMP(9);
+      DBG_STAMP(10);
       if (wq == 0 && rv) {
-        float zc = (lane < C) ? zs[slot * kMaxC + lane] : -INFINITY;
+        // One warp per row: lane = class + C*group; each group covers a third (32/C groups) of the hidden
+        // units, partial logits are folded with shuffles, then the same lanes do the softmax.
+        const int ngrp = 32 / C;                      // C <= 16 -> at least 2 groups
+        const int cls = lane % C, grp = lane / C;
+        float p0 = 0.f, p1 = 0.f;
+        if (grp < ngrp) {
+          const float* hrow = hs + slot * kMaxH;
+          int u = grp;
+          for (; u + ngrp < H; u += 2 * ngrp) {
+            p0 = fmaf(hrow[u], W2s[u * C + cls], p0);
+            p1 = fmaf(hrow[u + ngrp], W2s[(u + ngrp) * C + cls], p1);
+          }
+          if (u < H) p0 = fmaf(hrow[u], W2s[u * C + cls], p0);
+        }
+        float p = p0 + p1;
+        for (int gsh = 1; gsh < ngrp; ++gsh) {        // fold group gsh into group 0
+          float other = __shfl_down_sync(0xffffffffu, p, gsh * C);
+          if (grp == 0) p += (lane + gsh * C < ngrp * C) ? other : 0.f;
+        }
+        float zc = (lane < C) ? p + b2s[lane] : -INFINITY;
         float mx = zc; int am = (lane < C) ? lane : 0x7fffffff;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
@@ -320,6 +345,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
         }
       }
       __syncthreads();
+      DBG_STAMP(11);
       if (rv && t < H) {
         float dh = 0.f;
         for (int c = 0; c < C; ++c) dh = fmaf(dzs[slot * kMaxC + c], W2s[t * C + c], dh);
@@ -364,6 +390,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
       for (int e = (B * H) / 4 * 4 + tid; e < B * H; e += kThreads) dAs[e] = __ldcg(a.dA + e);
       for (int e = tid; e < B * C; e += kThreads) dZs[e] = __ldcg(a.dZ + e);
       __syncthreads();
+      DBG_STAMP(12);
       {
         // dW1 rows [k0, k0+KS): a warp owns 4 consecutive rows (one broadcast float4 of X per batch row)
         // and a contiguous block of columns, so each dA value fetched from shared memory feeds 4 FMAs.
@@ -412,6 +439,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
           }
         }
       }
+      DBG_STAMP(13);
       // small gradients
       for (int tt = t_first; tt < H; tt += 4 * (int)G) {
         if ((warp & 1) == 0) {  // dW2[tt][:] = sum_b H[b][tt] * dZ[b][:]
@@ -434,13 +462,16 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
                 if (c < C) accc[c] = fmaf(hcol[i], dZs[b * C + c], accc[c]);
             }
           }
+          // every lane ends up with all C sums; lane c keeps the c-th and the row is pushed in one request
+          float mine = 0.f;
 #pragma unroll
           for (int c = 0; c < kMaxC; ++c) {
             if (c < C) {
               float v = dtfe::warp_sum(accc[c]);
-              if (lane == 0) emit(a.W2, a.gW2, (long)tt * C + c, v, nlr, a.atomic);
+              if (lane == c) mine = v;
             }
           }
+          if (lane < C) emit(a.W2, a.gW2, (long)tt * C + lane, mine, nlr, a.atomic);
         } else {  // db1[tt] = sum_b dA[b][tt]
           float v = 0.f;
           for (int b = lane; b < B; b += 32) v += dAs[b * HP + tt];
@@ -449,12 +480,14 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
         }
       }
       if (g == (int)G - 1 && warp == 7) {  // db2[c] = sum_b dZ[b][c]
+        float mine = 0.f;
         for (int c = 0; c < C; ++c) {
           float v = 0.f;
           for (int b = lane; b < B; b += 32) v += dZs[b * C + c];
           v = dtfe::warp_sum(v);
-          if (lane == 0) emit(a.b2, a.gb2, c, v, nlr, a.atomic);
+          if (lane == c) mine = v;
         }
+        if (lane < C) emit(a.b2, a.gb2, lane, mine, nlr, a.atomic);
       }
       // All of this CTA's pushes are performed before it reports completion: the CTA barrier orders
       // every thread's reds before thread 0's fence, and fences are cumulative.

@@ -122,7 +122,7 @@ typedef struct dtfe_mlp2_launch {
   float* workspace;                   /* dtfe_mlp2_step_workspace_words() 4-byte words, zeroed once */
   float* loss_out; float* acc_out; int* step_out;   /* [nsteps] each */
   float lr; int nsteps; int atomic; int train; int remote;
-  long long* dbg;                     /* NULL, or [nsteps][grid][8] globaltimer stamps */
+  long long* dbg;                     /* NULL, or [nsteps][grid][16] globaltimer stamps */
   float *gW1, *gb1, *gW2, *gb2;       /* all NULL (async: push), or sync mode: raw gradients stored here, no push,
                                          no global_step increment (dtfe_sync_rs_apply_f32 does both) */
   int* cursor;                        /* NULL, or device int: batches start at batch_idx[*cursor * B]; advanced by

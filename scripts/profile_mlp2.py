@@ -30,16 +30,30 @@ for i in range(launches):
 
 if "--stamps" in sys.argv:
     G = tr.fused.k.grid
-    dbg = torch.zeros(nsteps * G * 8, dtype=torch.int64, device=dev)
+    dbg = torch.zeros(nsteps * G * 16, dtype=torch.int64, device=dev)
     tr.fused.dbg = dbg
     idx = ds.next_indices(100, nsteps)
     tr.run_indices(ds, idx, nsteps)
     torch.cuda.synchronize()
-    t = dbg.view(nsteps, G, 8).double().cpu().numpy()
-    names = ["A:load+compute+store", "barrier1", "B:reduce..dA", "barrier2", "C:dW1+push", "fence", "done-atomic"]
-    s0 = t[2:]                       # skip first steps
-    for i, n in enumerate(names):
-        d = (s0[:, :, i + 1] - s0[:, :, i]) / 1e3
-        print(f"{n:24s} mean {d.mean():6.2f} us  max-over-CTAs {d.max(axis=1).mean():6.2f} us  min {d.min(axis=1).mean():6.2f}")
-    step = (s0[1:, :, 0] - s0[:-1, :, 0]) / 1e3
+    t = dbg.view(nsteps, G, 16).double().cpu().numpy()[2:]      # skip the first steps
+    def seg(name, a, b, rows=slice(None)):
+        d = (t[:, rows, b] - t[:, rows, a]) / 1e3
+        print(f"{name:34s} mean {d.mean():6.2f} us  max-over-CTAs {d.max(axis=1).mean():6.2f}  min {d.min(axis=1).mean():6.2f}")
+    act = slice(0, 50)                                          # CTAs that own batch rows in phase B
+    seg("A: load+compute+store", 0, 1)
+    seg("barrier1", 1, 2)
+    seg("B total", 2, 3)
+    seg("  B (row CTAs) loads+reduce", 2, 8, act)
+    seg("  B (row CTAs) stage+sigmoid", 8, 9, act)
+    seg("  B (row CTAs) logits", 9, 10, act)
+    seg("  B (row CTAs) softmax/xent", 10, 11, act)
+    seg("  B (row CTAs) dA+store", 11, 3, act)
+    seg("barrier2", 3, 4)
+    seg("C total", 4, 5)
+    seg("  C load dA/dZ to smem", 4, 12)
+    seg("  C dW1 + push", 12, 13)
+    seg("  C small grads + push", 13, 5)
+    seg("fence", 5, 6)
+    seg("done-atomic", 6, 7)
+    step = (t[1:, :, 0] - t[:-1, :, 0]) / 1e3
     print(f"step period             {step.mean():6.2f} us")
