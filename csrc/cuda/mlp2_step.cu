@@ -162,6 +162,25 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
   fetch_rows(1);
 
   const int slot = tid >> 7, t = tid & 127, wq = warp & 3;   // phase B roles: 2 rows per CTA, 4 warps each
+
+  // Ownership of the W1 slice inside the CTA (used by the phase-C dW1 tiling AND by the pull): a warp owns
+  // 4 consecutive rows and a contiguous block of columns; a lane owns up to two columns of those rows.
+  constexpr int kGroups = KS / 4, kParts = 8 / kGroups;
+  const int wgrp = warp % kGroups, wpart = warp / kGroups;
+  const int wcq = (H + kParts - 1) / kParts;            // columns per part (<= 64)
+  const int wj0 = wpart * wcq + lane, wj1 = wj0 + 32;
+  const bool wv0 = lane < wcq && wj0 < H, wv1 = lane + 32 < wcq && wj1 < H;
+  float wnext0[4], wnext1[4];
+  auto fetch_w1 = [&]() {                               // the pull: this thread's elements of the W1 slice
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      int k = k0 + wgrp * 4 + q;
+      wnext0[q] = (wv0 && k < D) ? dtfe::ld_relaxed_sys(a.W1 + (long)k * H + wj0) : 0.f;
+      wnext1[q] = (wv1 && k < D) ? dtfe::ld_relaxed_sys(a.W1 + (long)k * H + wj1) : 0.f;
+    }
+  };
+  fetch_w1();
+  int pending_step = 0;                                 // CTA 0 / thread 0: global step observed for the previous step
   auto fetch_label_row = [&](int st) {
     int r = 2 * g + slot;
     if (r < B && st < a.nsteps)
@@ -177,10 +196,12 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
       int e = tid + i * kThreads;
       if (e < B * KS) Xs[e] = xnext[i];
     }
-    for (int e = tid; e < KS * H; e += kThreads) {
-      int kk = e / H, j = e % H;
-      int k = k0 + kk;
-      Ws[kk * HP + j] = (k < D) ? dtfe::ld_relaxed_sys(a.W1 + (long)k * H + j) : 0.f;
+    // W1 slice: every thread re-read, right after its own pushes in the previous step's phase C (same
+    // thread, same addresses: program order guarantees it sees them), exactly the elements it owns.
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      if (wv0) Ws[(wgrp * 4 + q) * HP + wj0] = wnext0[q];
+      if (wv1) Ws[(wgrp * 4 + q) * HP + wj1] = wnext1[q];
     }
     // label of the first row this thread's slot handles in phase B (latency hidden behind phase A)
     int ylab = 0;
@@ -223,6 +244,11 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
     fetch_x(s + 1);
     fetch_rows(s + 2);
     fetch_label_row(s + 1);
+    // Every CTA has passed barrier 1, so every push of step s-1 has been issued and fenced: count that update
+    // now.  The atomic's result (the global step the previous step observed, what the reference fetches next
+    // to train_op) is not consumed until the end of phase B, so its round trip costs nothing.
+    if (g == 0 && tid == 0 && s > 0 && a.train)
+      pending_step = a.gW1 ? *reinterpret_cast<volatile int*>(a.global_step) : dtfe::atom_add_sys_s32(a.global_step, 1);
     // Small parameters are read after the barrier so that every CTA sees the pushes all CTAs made in
     // the previous step's phase C.  They go to registers first; the reduction loads below are issued
     // before anything waits, so all of it shares one L2 round trip.
@@ -353,6 +379,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
       }
       __syncthreads();
     }
+    if (g == 0 && tid == 0 && s > 0 && a.train) a.step_out[s - 1] = pending_step;
     DBG_STAMP(3);
     grid_barrier(a.sync, bar_target, G);
     DBG_STAMP(4);
@@ -372,18 +399,16 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
     }
     if (a.train) {
       const float nlr = -a.lr;
-      // Small-gradient duty of this warp: hidden unit t = g + G*(warp/2) (+ 4G per extra round);
-      // even warps produce the dW2 row, odd warps db1.  The H column an even warp needs is requested
-      // now, so its L2 latency hides behind the dA load and the dW1 loop.
-      const int pair = warp >> 1;
-      const int t_first = g + (int)G * pair;
-      float hcol[4] = {0.f, 0.f, 0.f, 0.f};
-      if ((warp & 1) == 0 && t_first < H) {
+      // Small gradients: hidden unit t0 = g (and t1 = g + G on the first CTAs when H > G).  Every warp
+      // takes one or two classes of the dW2 row, so the H column is requested by all warps now and its L2
+      // latency hides behind the dA load and the dW1 loop.
+      const int t0 = g, t1 = g + (int)G;
+      float hcol0[4] = {0.f, 0.f, 0.f, 0.f}, hcol1[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          int b = lane + 32 * i;
-          if (b < B) hcol[i] = __ldcg(a.Hbuf + (long)b * H + t_first);
-        }
+      for (int i = 0; i < 4; ++i) {
+        int b = lane + 32 * i;
+        if (b < B && t0 < H) hcol0[i] = __ldcg(a.Hbuf + (long)b * H + t0);
+        if (b < B && t1 < H) hcol1[i] = __ldcg(a.Hbuf + (long)b * H + t1);
       }
       for (int e = tid; e < (B * H) / 4; e += kThreads)
         reinterpret_cast<float4*>(dAs)[e] = __ldcg(reinterpret_cast<const float4*>(a.dA) + e);
@@ -394,25 +419,20 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
       {
         // dW1 rows [k0, k0+KS): a warp owns 4 consecutive rows (one broadcast float4 of X per batch row)
         // and a contiguous block of columns, so each dA value fetched from shared memory feeds 4 FMAs.
-        constexpr int kGroups = KS / 4, kParts = 8 / kGroups;
-        const int grp = warp % kGroups, part = warp / kGroups;
-        const int cq = (H + kParts - 1) / kParts;          // columns per part (<= 64)
-        const int j0 = part * cq + lane, j1 = j0 + 32;
-        const bool v0 = lane < cq && j0 < H, v1 = lane + 32 < cq && j1 < H;
         float acc0[4] = {0.f, 0.f, 0.f, 0.f}, acc1[4] = {0.f, 0.f, 0.f, 0.f};
         float bcc0[4] = {0.f, 0.f, 0.f, 0.f}, bcc1[4] = {0.f, 0.f, 0.f, 0.f};
-        const float* xp = Xs + grp * 4;
+        const float* xp = Xs + wgrp * 4;
         int b = 0;
         for (; b + 2 <= B; b += 2) {          // two independent chains
           float4 xa = *reinterpret_cast<const float4*>(xp + b * KS);
           float4 xb = *reinterpret_cast<const float4*>(xp + (b + 1) * KS);
-          float da0 = v0 ? dAs[b * HP + j0] : 0.f, db0 = v0 ? dAs[(b + 1) * HP + j0] : 0.f;
+          float da0 = wv0 ? dAs[b * HP + wj0] : 0.f, db0 = wv0 ? dAs[(b + 1) * HP + wj0] : 0.f;
           acc0[0] = fmaf(xa.x, da0, acc0[0]); acc0[1] = fmaf(xa.y, da0, acc0[1]);
           acc0[2] = fmaf(xa.z, da0, acc0[2]); acc0[3] = fmaf(xa.w, da0, acc0[3]);
           bcc0[0] = fmaf(xb.x, db0, bcc0[0]); bcc0[1] = fmaf(xb.y, db0, bcc0[1]);
           bcc0[2] = fmaf(xb.z, db0, bcc0[2]); bcc0[3] = fmaf(xb.w, db0, bcc0[3]);
           if (kParts < 4) {                   // wide parts (KS = 16): a second column per lane
-            float da1 = v1 ? dAs[b * HP + j1] : 0.f, db1 = v1 ? dAs[(b + 1) * HP + j1] : 0.f;
+            float da1 = wv1 ? dAs[b * HP + wj1] : 0.f, db1 = wv1 ? dAs[(b + 1) * HP + wj1] : 0.f;
             acc1[0] = fmaf(xa.x, da1, acc1[0]); acc1[1] = fmaf(xa.y, da1, acc1[1]);
             acc1[2] = fmaf(xa.z, da1, acc1[2]); acc1[3] = fmaf(xa.w, da1, acc1[3]);
             bcc1[0] = fmaf(xb.x, db1, bcc1[0]); bcc1[1] = fmaf(xb.y, db1, bcc1[1]);
@@ -421,105 +441,85 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
         }
         for (; b < B; ++b) {
           float4 xa = *reinterpret_cast<const float4*>(xp + b * KS);
-          float da0 = v0 ? dAs[b * HP + j0] : 0.f;
+          float da0 = wv0 ? dAs[b * HP + wj0] : 0.f;
           acc0[0] = fmaf(xa.x, da0, acc0[0]); acc0[1] = fmaf(xa.y, da0, acc0[1]);
           acc0[2] = fmaf(xa.z, da0, acc0[2]); acc0[3] = fmaf(xa.w, da0, acc0[3]);
           if (kParts < 4) {
-            float da1 = v1 ? dAs[b * HP + j1] : 0.f;
+            float da1 = wv1 ? dAs[b * HP + wj1] : 0.f;
             acc1[0] = fmaf(xa.x, da1, acc1[0]); acc1[1] = fmaf(xa.y, da1, acc1[1]);
             acc1[2] = fmaf(xa.z, da1, acc1[2]); acc1[3] = fmaf(xa.w, da1, acc1[3]);
           }
         }
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-          int k = k0 + grp * 4 + q;
+          int k = k0 + wgrp * 4 + q;
           if (k < D) {
-            if (v0) emit(a.W1, a.gW1, (long)k * H + j0, acc0[q] + bcc0[q], nlr, a.atomic);
-            if (kParts < 4 && v1) emit(a.W1, a.gW1, (long)k * H + j1, acc1[q] + bcc1[q], nlr, a.atomic);
+            if (wv0) emit(a.W1, a.gW1, (long)k * H + wj0, acc0[q] + bcc0[q], nlr, a.atomic);
+            if (kParts < 4 && wv1) emit(a.W1, a.gW1, (long)k * H + wj1, acc1[q] + bcc1[q], nlr, a.atomic);
           }
         }
       }
+      // pull for the next step: the same thread reads back exactly the elements it just pushed
+      fetch_w1();
       DBG_STAMP(13);
-      // small gradients
-      for (int tt = t_first; tt < H; tt += 4 * (int)G) {
-        if ((warp & 1) == 0) {  // dW2[tt][:] = sum_b H[b][tt] * dZ[b][:]
-          if (tt != t_first) {
+      // small gradients, one or two classes per warp
+      for (int tt = t0, rnd = 0; tt < H; tt += (int)G, ++rnd) {
+        float hc[4];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              int b = lane + 32 * i;
-              hcol[i] = (b < B) ? __ldcg(a.Hbuf + (long)b * H + tt) : 0.f;
-            }
-          }
-          float accc[kMaxC];
-#pragma unroll
-          for (int c = 0; c < kMaxC; ++c) accc[c] = 0.f;
+        for (int i = 0; i < 4; ++i) {
+          int b = lane + 32 * i;
+          hc[i] = rnd == 0 ? hcol0[i] : rnd == 1 ? hcol1[i] : (b < B ? __ldcg(a.Hbuf + (long)b * H + tt) : 0.f);
+        }
+        for (int c = warp; c < C; c += 8) {       // dW2[tt][c] = sum_b H[b][tt] * dZ[b][c]
+          float v = 0.f;
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
             int b = lane + 32 * i;
-            if (b < B) {
-#pragma unroll
-              for (int c = 0; c < kMaxC; ++c)
-                if (c < C) accc[c] = fmaf(hcol[i], dZs[b * C + c], accc[c]);
-            }
+            if (b < B) v = fmaf(hc[i], dZs[b * C + c], v);
           }
-          // every lane ends up with all C sums; lane c keeps the c-th and the row is pushed in one request
-          float mine = 0.f;
-#pragma unroll
-          for (int c = 0; c < kMaxC; ++c) {
-            if (c < C) {
-              float v = dtfe::warp_sum(accc[c]);
-              if (lane == c) mine = v;
-            }
-          }
-          if (lane < C) emit(a.W2, a.gW2, (long)tt * C + lane, mine, nlr, a.atomic);
-        } else {  // db1[tt] = sum_b dA[b][tt]
+          v = dtfe::warp_sum(v);
+          if (lane == 0) emit(a.W2, a.gW2, (long)tt * C + c, v, nlr, a.atomic);
+        }
+        if (warp == 5) {                          // db1[tt] = sum_b dA[b][tt]
           float v = 0.f;
           for (int b = lane; b < B; b += 32) v += dAs[b * HP + tt];
           v = dtfe::warp_sum(v);
           if (lane == 0) emit(a.b1, a.gb1, tt, v, nlr, a.atomic);
         }
       }
-      if (g == (int)G - 1 && warp == 7) {  // db2[c] = sum_b dZ[b][c]
-        float mine = 0.f;
-        for (int c = 0; c < C; ++c) {
+      if (g == (int)G - 1) {                      // db2[c] = sum_b dZ[b][c], spread over the warps
+        for (int c = warp; c < C; c += 8) {
           float v = 0.f;
           for (int b = lane; b < B; b += 32) v += dZs[b * C + c];
           v = dtfe::warp_sum(v);
-          if (lane == c) mine = v;
+          if (lane == 0) emit(a.b2, a.gb2, c, v, nlr, a.atomic);
         }
-        if (lane < C) emit(a.b2, a.gb2, lane, mine, nlr, a.atomic);
       }
-      // All of this CTA's pushes are performed before it reports completion: the CTA barrier orders
-      // every thread's reds before thread 0's fence, and fences are cumulative.
       DBG_STAMP(5);
-      __syncthreads();
-      if (tid == 0) {
-        // gpu-scope fence + gpu-scope counter chain the CTAs together; only the CTA that finishes last
-        // pays the system-scope fence that orders all of this step's (possibly remote) pushes before the
-        // global_step increment other GPUs can observe.
-        __threadfence();
-        DBG_STAMP(6);
-        unsigned prev = atomicAdd(a.sync + 2, 1u);
-        if (prev == G - 1) {
-          a.sync[2] = 0;
-          if (a.remote) __threadfence_system();
-          // sync mode: the aggregated update (and its global_step += 1) belongs to the exchange kernel
-          int old = a.gW1 ? *reinterpret_cast<volatile int*>(a.global_step) : dtfe::atom_add_sys_s32(a.global_step, 1);
-          a.step_out[s] = old;
-        }
-      }
+      // No per-step completion handshake: the next grid barrier (or the exit handshake below) orders all
+      // of this step's pushes before the global_step increment that counts them.
+      __syncthreads();                            // dAs / Xs are rewritten by the next step
       DBG_STAMP(7);
-    } else if (g == 0 && tid == 0) {
-      a.step_out[s] = *reinterpret_cast<volatile int*>(a.global_step);
+    } else {
+      fetch_w1();
+      if (g == 0 && tid == 0) a.step_out[s] = *reinterpret_cast<volatile int*>(a.global_step);
+      __syncthreads();
     }
   }
 
-  // leave the sync words zeroed for the next launch
+  // Exit handshake: the last CTA to get here leaves the sync words zeroed for the next launch and counts
+  // the final step (every CTA fenced its pushes before arriving).
   __syncthreads();
   if (tid == 0) {
+    __threadfence();
     unsigned prev = atomicAdd(a.sync + 1, 1u);
     if (prev == G - 1) {
       a.sync[0] = 0; a.sync[1] = 0;
+      if (a.train && a.nsteps > 0) {
+        if (a.remote) __threadfence_system();
+        int old = a.gW1 ? *reinterpret_cast<volatile int*>(a.global_step) : dtfe::atom_add_sys_s32(a.global_step, 1);
+        a.step_out[a.nsteps - 1] = old;
+      }
       if (a.cursor) *a.cursor = (int)sbase + a.nsteps;   // every CTA read the cursor before arriving here
       __threadfence();
     }

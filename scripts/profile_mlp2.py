@@ -53,7 +53,6 @@ if "--stamps" in sys.argv:
     seg("  C load dA/dZ to smem", 4, 12)
     seg("  C dW1 + push", 12, 13)
     seg("  C small grads + push", 13, 5)
-    seg("fence", 5, 6)
-    seg("done-atomic", 6, 7)
+    seg("  C closing __syncthreads", 5, 7)
     step = (t[1:, :, 0] - t[:-1, :, 0]) / 1e3
     print(f"step period             {step.mean():6.2f} us")
