@@ -329,16 +329,23 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
         // units, partial logits are folded with shuffles, then the same lanes do the softmax.
         const int ngrp = 32 / C;                      // C <= 16 -> at least 2 groups
         const int cls = lane % C, grp = lane / C;
-        float p0 = 0.f, p1 = 0.f;
+        float p0 = 0.f, p1 = 0.f, p2 = 0.f, p3 = 0.f;
         if (grp < ngrp) {
           const float* hrow = hs + slot * kMaxH;
+          const float* wcol = W2s + cls;
           int u = grp;
-          for (; u + ngrp < H; u += 2 * ngrp) {
-            p0 = fmaf(hrow[u], W2s[u * C + cls], p0);
-            p1 = fmaf(hrow[u + ngrp], W2s[(u + ngrp) * C + cls], p1);
+          const int st = ngrp;
+#pragma unroll 2
+          for (; u + 3 * st < H; u += 4 * st) {
+            p0 = fmaf(hrow[u], wcol[u * C], p0);
+            p1 = fmaf(hrow[u + st], wcol[(u + st) * C], p1);
+            p2 = fmaf(hrow[u + 2 * st], wcol[(u + 2 * st) * C], p2);
+            p3 = fmaf(hrow[u + 3 * st], wcol[(u + 3 * st) * C], p3);
           }
-          if (u < H) p0 = fmaf(hrow[u], W2s[u * C + cls], p0);
+          for (; u < H; u += st) p0 = fmaf(hrow[u], wcol[u * C], p0);
         }
+        p0 = (p0 + p1) + (p2 + p3);
+        p1 = 0.f;
         float p = p0 + p1;
         for (int gsh = 1; gsh < ngrp; ++gsh) {        // fold group gsh into group 0
           float other = __shfl_down_sync(0xffffffffu, p, gsh * C);
@@ -347,13 +354,15 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
         float zc = (lane < C) ? p + b2s[lane] : -INFINITY;
         float mx = zc; int am = (lane < C) ? lane : 0x7fffffff;
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
+        for (int o = 8; o > 0; o >>= 1) {          // C <= 16: the classes live in lanes 0..15
           float om = __shfl_xor_sync(0xffffffffu, mx, o);
           int oa = __shfl_xor_sync(0xffffffffu, am, o);
           if (om > mx || (om == mx && oa < am)) { mx = om; am = oa; }
         }
         float ex = (lane < C) ? __expf(zc - mx) : 0.f;
-        float se = dtfe::warp_sum(ex);
+        float se = ex;
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) se += __shfl_xor_sync(0xffffffffu, se, o);
         int y = ylab;
         if (r0 != 2 * g) {                   // later rounds (B > 2*G): fetch the label now
           long row = a.batch_idx ? (long)a.batch_idx[(sbase + s) * B + r] : (sbase + s) * a.rows_per_step + r;
