@@ -110,7 +110,8 @@ class ClockSampler:
 def _reference_unavailable():
     why = ("TensorFlow 1.x is not installable here: /root/reference ships no setup.py/wheels (pip install of the "
            "source tree fails), no network, Python 3.12 (TF1 needs <=3.7), and TF 1.x predates CUDA 12.8/sm_100")
-    print(json.dumps({"impl": "reference", "unavailable": why}))
+    if int(os.environ.get("RANK", "0")) == 0:       # one line per job, also when launched under torchrun
+        print(json.dumps({"impl": "reference", "unavailable": why}), flush=True)
 
 
 def main():

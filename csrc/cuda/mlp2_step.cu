@@ -661,27 +661,28 @@ DTFE_API int dtfe_mlp2_step_noalloc(const dtfe_mlp2_launch* launch, void* stream
 // compute stream.  Doing the loop here instead of in Python keeps the per-step host cost at a few
 // microseconds of driver calls.
 namespace {
+constexpr int kFeedMaxSteps = 16;
 struct HostFeed {
-  int B, D, dev;
-  float* xs[2];
+  int B, D, S, dev;                    // S = training steps (host batches) fused into one kernel launch
+  float* xs[2];                        // staging: S batches per slot
   int* ys[2];
-  float* out[2];                       // per-slot {loss, acc} + int step written by the kernel
-  int* step[2];
+  float* out[2];                       // per slot: loss[S] | acc[S] | step[S] (int)
   cudaStream_t copy, back;             // H2D and D2H side streams
   cudaEvent_t copied[2], done[2], readback[2];
 };
 }  // namespace
 
-DTFE_API int dtfe_hostfeed_create(int B, int D, void** out) {
+DTFE_API int dtfe_hostfeed_create(int B, int D, int steps_per_launch, void** out) {
   DTFE_REQUIRE(B >= 1 && D >= 1, "dtfe_hostfeed_create: bad shape");
+  DTFE_REQUIRE(steps_per_launch >= 1 && steps_per_launch <= kFeedMaxSteps,
+               "dtfe_hostfeed_create: steps_per_launch must be in [1,%d]", kFeedMaxSteps);
   HostFeed* h = new HostFeed();
-  h->B = B; h->D = D;
+  h->B = B; h->D = D; h->S = steps_per_launch;
   DTFE_CUDA_CHECK(cudaGetDevice(&h->dev));
   for (int i = 0; i < 2; ++i) {
-    DTFE_CUDA_CHECK(cudaMalloc(&h->xs[i], (size_t)B * D * sizeof(float)));
-    DTFE_CUDA_CHECK(cudaMalloc(&h->ys[i], (size_t)B * sizeof(int)));
-    DTFE_CUDA_CHECK(cudaMalloc(&h->out[i], 4 * sizeof(float)));
-    h->step[i] = reinterpret_cast<int*>(h->out[i] + 2);
+    DTFE_CUDA_CHECK(cudaMalloc(&h->xs[i], (size_t)h->S * B * D * sizeof(float)));
+    DTFE_CUDA_CHECK(cudaMalloc(&h->ys[i], (size_t)h->S * B * sizeof(int)));
+    DTFE_CUDA_CHECK(cudaMalloc(&h->out[i], 3 * kFeedMaxSteps * sizeof(float)));
     DTFE_CUDA_CHECK(cudaEventCreateWithFlags(&h->copied[i], cudaEventDisableTiming));
     DTFE_CUDA_CHECK(cudaEventCreateWithFlags(&h->done[i], cudaEventDisableTiming));
     DTFE_CUDA_CHECK(cudaEventCreateWithFlags(&h->readback[i], cudaEventDisableTiming));
@@ -706,9 +707,11 @@ DTFE_API int dtfe_hostfeed_destroy(void* handle) {
 }
 
 // launch: B/D/H/C/ks, parameter pointers, workspace, lr, atomic, train, remote are used; X/labels/
-// batch_idx/nsteps are supplied per step from the host batches.  loss_host (pinned, [nsteps]) receives
-// one float per step.  Three streams keep everything off the kernels' critical path: H2D copies of
-// batch i+1 run under step i, and the D2H read of step i's loss runs under step i+1; on return the
+// batch_idx/nsteps are supplied from the host batches.  Every step's batch is copied H2D from its own
+// pinned buffer (x_host[i], y_host[i]) and every step's loss is copied back D2H into loss_host[i]
+// (pinned); up to `steps_per_launch` consecutive steps share one kernel launch.  Three streams keep the
+// copies off the kernels' critical path: the H2D copies of the next group run under the current group's
+// kernel, and the D2H read of a group's losses runs under the next group's kernel.  On return the
 // caller's stream waits for the last read-back, so synchronising it makes every loss_host[i] valid.
 DTFE_API int dtfe_mlp2_train_host(void* handle, const dtfe_mlp2_launch* launch, const float* const* x_host,
                                   const int* const* y_host, int nsteps, float* loss_host, void* stream) {
@@ -717,36 +720,44 @@ DTFE_API int dtfe_mlp2_train_host(void* handle, const dtfe_mlp2_launch* launch, 
   DTFE_REQUIRE(launch->B == h->B && launch->D == h->D, "dtfe_mlp2_train_host: feed was created for B=%d D=%d", h->B, h->D);
   cudaStream_t st = (cudaStream_t)stream;
   Mlp2Launch L = *launch;
-  L.nsteps = 1; L.batch_idx = nullptr; L.rows_per_step = 0; L.ldx = h->D; L.dbg = nullptr;
+  L.batch_idx = nullptr; L.rows_per_step = h->B; L.ldx = h->D; L.dbg = nullptr; L.cursor = nullptr;
   Mlp2Args a{};
-  for (int i = 0; i < nsteps; ++i) {
-    const int s = i & 1;
-    // H2D: the staging slot is free once the step that last read it has finished
+  const size_t xbytes = (size_t)h->B * h->D * sizeof(float), ybytes = (size_t)h->B * sizeof(int);
+  int group = 0, last_slot = 0, last_n = 0;
+  for (int i = 0; i < nsteps; i += h->S, ++group) {
+    const int s = group & 1;
+    const int n = nsteps - i < h->S ? nsteps - i : h->S;
+    // H2D: the staging slot is free once the launch that last read it has finished
     DTFE_CUDA_CHECK(cudaStreamWaitEvent(h->copy, h->done[s], 0));
-    DTFE_CUDA_CHECK(cudaMemcpyAsync(h->xs[s], x_host[i], (size_t)h->B * h->D * sizeof(float), cudaMemcpyHostToDevice, h->copy));
-    DTFE_CUDA_CHECK(cudaMemcpyAsync(h->ys[s], y_host[i], (size_t)h->B * sizeof(int), cudaMemcpyHostToDevice, h->copy));
+    for (int j = 0; j < n; ++j) {
+      DTFE_CUDA_CHECK(cudaMemcpyAsync(h->xs[s] + (size_t)j * h->B * h->D, x_host[i + j], xbytes, cudaMemcpyHostToDevice, h->copy));
+      DTFE_CUDA_CHECK(cudaMemcpyAsync(h->ys[s] + (size_t)j * h->B, y_host[i + j], ybytes, cudaMemcpyHostToDevice, h->copy));
+    }
     DTFE_CUDA_CHECK(cudaEventRecord(h->copied[s], h->copy));
-    // step: needs its batch, and its output slot must have been read back
+    // steps: need their batches, and the slot's outputs must have been read back
     DTFE_CUDA_CHECK(cudaStreamWaitEvent(st, h->copied[s], 0));
     DTFE_CUDA_CHECK(cudaStreamWaitEvent(st, h->readback[s], 0));
-    L.X = h->xs[s]; L.labels = h->ys[s];
-    L.loss_out = h->out[s]; L.acc_out = h->out[s] + 1; L.step_out = h->step[s];
+    L.X = h->xs[s]; L.labels = h->ys[s]; L.nsteps = n;
+    L.loss_out = h->out[s]; L.acc_out = h->out[s] + kFeedMaxSteps;
+    L.step_out = reinterpret_cast<int*>(h->out[s] + 2 * kFeedMaxSteps);
     if (int rc = mlp2_fill(L, a)) return rc;
     int rc = L.ks == 8 ? mlp2_launch<8>(a, st) : mlp2_launch<16>(a, st);
     if (rc) return rc;
     DTFE_CUDA_CHECK(cudaEventRecord(h->done[s], st));
-    // D2H of this step's loss on the read-back stream
+    // D2H of these steps' losses on the read-back stream
     DTFE_CUDA_CHECK(cudaStreamWaitEvent(h->back, h->done[s], 0));
-    DTFE_CUDA_CHECK(cudaMemcpyAsync(loss_host + i, h->out[s], sizeof(float), cudaMemcpyDeviceToHost, h->back));
+    DTFE_CUDA_CHECK(cudaMemcpyAsync(loss_host + i, h->out[s], (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, h->back));
     DTFE_CUDA_CHECK(cudaEventRecord(h->readback[s], h->back));
+    last_slot = s; last_n = n;
   }
   if (nsteps > 0) {
-    DTFE_CUDA_CHECK(cudaStreamWaitEvent(st, h->readback[(nsteps - 1) & 1], 0));
-    if (nsteps > 1) DTFE_CUDA_CHECK(cudaStreamWaitEvent(st, h->readback[nsteps & 1], 0));
+    DTFE_CUDA_CHECK(cudaStreamWaitEvent(st, h->readback[0], 0));
+    DTFE_CUDA_CHECK(cudaStreamWaitEvent(st, h->readback[1], 0));
     // keep the caller-visible output views (launch->loss_out etc.) in step with the last step
-    DTFE_CUDA_CHECK(cudaMemcpyAsync(launch->loss_out, h->out[(nsteps - 1) & 1], sizeof(float), cudaMemcpyDeviceToDevice, st));
-    DTFE_CUDA_CHECK(cudaMemcpyAsync(launch->acc_out, h->out[(nsteps - 1) & 1] + 1, sizeof(float), cudaMemcpyDeviceToDevice, st));
-    DTFE_CUDA_CHECK(cudaMemcpyAsync(launch->step_out, h->step[(nsteps - 1) & 1], sizeof(int), cudaMemcpyDeviceToDevice, st));
+    const float* o = h->out[last_slot];
+    DTFE_CUDA_CHECK(cudaMemcpyAsync(launch->loss_out, o + last_n - 1, sizeof(float), cudaMemcpyDeviceToDevice, st));
+    DTFE_CUDA_CHECK(cudaMemcpyAsync(launch->acc_out, o + kFeedMaxSteps + last_n - 1, sizeof(float), cudaMemcpyDeviceToDevice, st));
+    DTFE_CUDA_CHECK(cudaMemcpyAsync(launch->step_out, o + 2 * kFeedMaxSteps + last_n - 1, sizeof(int), cudaMemcpyDeviceToDevice, st));
   }
   return 0;
 }

@@ -99,7 +99,7 @@ def run_mnist(args, rank: int, world: int, dev, ClockSampler) -> int:
         assert np.isfinite(loss_host[:Ke].numpy()).all()
         e2e = {"value": world * B * Ke / sec, "unit": "examples/sec", "steps": Ke,
                "h2d_bytes_per_step": tr.h2d_bytes_per_step(), "d2h_bytes_per_step": tr.d2h_bytes_per_step(),
-               "timing": "host wall clock around GpuTrainer.train_host_batches (per step: H2D of the batch from pinned memory, one step, D2H of the loss), max over ranks"}
+               "steps_per_launch": 4, "timing": "host wall clock around GpuTrainer.train_host_batches (every step: H2D copy of its batch from pinned memory and D2H read of its loss; 4 consecutive steps share a kernel launch), max over ranks"}
         _barrier(world)
 
     final_step = int(gs.item())

@@ -47,7 +47,7 @@ _SIGS = {
     "dtfe_mlp2_step_grid": ([c_int, c_int], c_int),
     "dtfe_mlp2_step_workspace_words": ([c_int, c_int, c_int, c_int, c_int], c_size_t),
     "dtfe_mlp2_step": ([_P, _P], c_int),
-    "dtfe_hostfeed_create": ([c_int, c_int, POINTER(_P)], c_int),
+    "dtfe_hostfeed_create": ([c_int, c_int, c_int, POINTER(_P)], c_int),
     "dtfe_hostfeed_destroy": ([_P], c_int),
     "dtfe_mlp2_train_host": ([_P, _P, POINTER(_P), POINTER(_P), c_int, _P, _P], c_int),
 }
@@ -340,14 +340,17 @@ class Mlp2Step:
         return L
 
     def train_host(self, W1, b1, W2, b2, global_step, x_host, y_host, loss_host, lr: float, atomic: bool = True,
-                   remote: bool = True):
+                   remote: bool = True, steps_per_launch: int = 1):
         """Native host-fed loop: ``x_host``/``y_host`` are lists of pinned CPU tensors (one batch per step),
         ``loss_host`` a pinned float32 tensor with one slot per step."""
-        if getattr(self, "_feed", None) is None:
+        if getattr(self, "_feed", None) is None or self._feed_spl != steps_per_launch:
+            if getattr(self, "_feed", None) is not None:
+                torch.cuda.synchronize(self.device)
+                lib().dtfe_hostfeed_destroy(self._feed)
             h = _P()
             with torch.cuda.device(self.device):
-                check(lib().dtfe_hostfeed_create(self.B, self.D, ctypes.byref(h)), "dtfe_hostfeed_create")
-            self._feed = h
+                check(lib().dtfe_hostfeed_create(self.B, self.D, steps_per_launch, ctypes.byref(h)), "dtfe_hostfeed_create")
+            self._feed, self._feed_spl = h, steps_per_launch
         n = len(x_host)
         for x, y in zip(x_host, y_host):
             if not (x.is_pinned() and y.is_pinned() and x.dtype == torch.float32 and y.dtype == torch.int32

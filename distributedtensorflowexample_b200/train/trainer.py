@@ -128,16 +128,18 @@ class GpuTrainer:
         row[0:1].copy_(loss_t[0:1], non_blocking=True)
         return row
 
-    def train_host_batches(self, x_list, y_list, loss_host: torch.Tensor) -> torch.Tensor:
+    def train_host_batches(self, x_list, y_list, loss_host: torch.Tensor, steps_per_launch: int = 4) -> torch.Tensor:
         """Feed ``len(x_list)`` batches from pinned host memory, one training step each (the reference's
         ``sess.run(train_op, feed_dict=...)`` loop, worker.py:133-137), with the loop itself in native code
         when the fused engine is active.  ``loss_host[i]`` (pinned) holds step i's loss once the stream has
-        drained."""
+        drained.  Each batch gets its own H2D copy and each loss its own slot in the D2H read-back;
+        ``steps_per_launch`` consecutive steps share one kernel launch."""
         if self.fused is not None:
             W1, b1, W2, b2 = self.params
+            spl = max(1, min(16, steps_per_launch))
             self.fused.k.train_host(W1, b1, W2, b2, self.global_step, x_list, y_list, loss_host, self.lr,
-                                    atomic=self.fused.atomic, remote=self.fused.remote)
-            self.launch_count += len(x_list)
+                                    atomic=self.fused.atomic, remote=self.fused.remote, steps_per_launch=spl)
+            self.launch_count += (len(x_list) + spl - 1) // spl
         else:
             for i, (x, y) in enumerate(zip(x_list, y_list)):
                 row = self.train_host_batch(x, y, out_index=i)

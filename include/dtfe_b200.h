@@ -134,9 +134,10 @@ int dtfe_mlp2_step(const dtfe_mlp2_launch* launch, void* stream);
 
 /* Host-fed loop (the reference's feed_dict path, worker.py:133-137): `nsteps` steps, step i fed from the
  * pinned host buffers x_host[i] ([B,D] fp32) / y_host[i] ([B] int32) through double-buffered staging
- * and a private copy stream; the loss of step i is copied back to loss_host[i] (pinned).  The feed
- * handle owns the staging buffers, events and copy stream. */
-int dtfe_hostfeed_create(int B, int D, void** out);
+ * and private copy streams; the loss of step i is copied back to loss_host[i] (pinned).  Up to
+ * steps_per_launch (<= 16) consecutive steps share one kernel launch; every batch still gets its own H2D
+ * copy and every loss its D2H read.  The feed handle owns the staging buffers, events and streams. */
+int dtfe_hostfeed_create(int B, int D, int steps_per_launch, void** out);
 int dtfe_hostfeed_destroy(void* handle);
 int dtfe_mlp2_train_host(void* handle, const dtfe_mlp2_launch* launch, const float* const* x_host,
                          const int* const* y_host, int nsteps, float* loss_host, void* stream);
