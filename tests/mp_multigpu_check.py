@@ -107,6 +107,39 @@ def main():
     assert (np.diff(steps_seen) > 0).all()                                   # strictly increasing observations
     dist.barrier()
     store.close()
+    # ---------------- pull fused with the forward GEMM: TMA reads a PEER shard straight into tcgen05 tiles ----
+    from distributedtensorflowexample_b200.models.mlp import MLPSpec
+    from distributedtensorflowexample_b200.train.gpu_step import TcStepper
+    bspec = MLPSpec((784, 104, 10), param_dtype="bfloat16")
+    bmodel, bstore = build_spmd_store(bspec, rank, world, dev, seed=9)
+    bnames = [v.name for v in bmodel.global_trainable]
+    if rank == 0:
+        g = np.random.default_rng(2)
+        for v in bmodel.global_trainable:
+            bstore.assign(v.name, (g.normal(size=v.shape) * 0.05).astype(np.float32))
+    dist.barrier()
+    # with round-robin placement over 2 shards W1 lives on GPU 0 and b1 on GPU 1: each rank reads one of them remotely
+    assert {bstore.shard_of(bnames[0]), bstore.shard_of(bnames[1])} == {0, 1}
+    tc = TcStepper(bspec, B, [bstore.tensor(n) for n in bnames], bstore.tensor("global/global_step"), 0.0, dev)
+    Xb = X[:B].bfloat16()
+    tc.run(Xb, Y[:B], train=False)
+    torch.cuda.synchronize()
+    pn = [bstore.read(n).astype(np.float64) for n in bnames]
+    logits_ref, _ = oracle.forward(pn, Xb.float().cpu().numpy().astype(np.float64))
+    np.testing.assert_allclose(tc.logits.cpu().numpy(), logits_ref, rtol=3e-2, atol=3e-2)
+    # and the push epilogue into the (possibly remote) bf16 shard: both ranks push the same update once
+    before = [bstore.read(n) for n in bnames]
+    dist.barrier()
+    tc.lr = 0.5
+    tc.run(Xb, Y[:B], train=True)
+    torch.cuda.synchronize(); dist.barrier()
+    _, _, grads = oracle.gradients(pn, Xb.float().cpu().numpy().astype(np.float64), y[:B].astype(np.int64))
+    for n, b0, gr in zip(bnames, before, grads):
+        want = b0 - world * 0.5 * gr
+        np.testing.assert_allclose(bstore.read(n), want, rtol=0, atol=2 ** -6 * (np.abs(want).max() + 1e-3) + 0.1 * np.abs(gr).max())
+    assert bstore.read("global/global_step").item() == world
+    dist.barrier()
+    bstore.close()
     if rank == 0:
         print("MULTIGPU_OK")
     dist.destroy_process_group()
