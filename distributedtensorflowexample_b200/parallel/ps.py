@@ -40,6 +40,7 @@ class PeerParamStore:
         self._opened: List[bool] = [False] * num_shards
         self._views: Dict[str, torch.Tensor] = {}
         self._headers: List[Optional[torch.Tensor]] = [None] * num_shards
+        self._snap_stream = None
 
     # ---- allocation / mapping ---------------------------------------------------------
     def allocate(self, shards: Optional[Sequence[int]] = None) -> None:
@@ -182,8 +183,13 @@ class PeerParamStore:
 
     def snapshot(self, names: Optional[Sequence[str]] = None) -> Dict[str, np.ndarray]:
         """Fuzzy snapshot of the shards for the checkpoint thread (reference 3.5: not coordinated
-        with training, tensors may be from slightly different global steps)."""
-        return {n: self.read(n) for n in (names or self.layout.names())}
+        with training, tensors may be from slightly different global steps).  The D2H copies run on a
+        side stream so that a save never waits for - or stalls - the training stream."""
+        if self._snap_stream is None:
+            self._snap_stream = torch.cuda.Stream(device=self.device)
+        with torch.cuda.stream(self._snap_stream):
+            out = {n: self.read(n) for n in (names or self.layout.names())}
+        return out
 
     def mark_ready(self) -> None:
         torch.cuda.synchronize(self.device)

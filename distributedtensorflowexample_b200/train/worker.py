@@ -47,6 +47,8 @@ def _parse_fault(text: str):
             out[name] = (int(task), int(step))
         elif name == "delay_push":
             out[name] = float(arg)
+        elif name == "kill_ps":
+            out[name] = float(arg)          # handled by the ps process (main.py)
         else:
             raise ValueError(f"unknown fault {part!r}")
     return out

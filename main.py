@@ -51,8 +51,15 @@ def main() -> int:
         server = Server(cluster, job_name="ps", task_index=FLAGS.task_index,
                         config=ServerConfig(backend=backend))
         print(f"ps:{FLAGS.task_index} serving at {server.target} (data source: {mnist.source})", flush=True)
+        die_after = None                  # test-only fault injection: --fault kill_ps:<seconds>
+        for part in (FLAGS.fault or "").split(","):
+            if part.startswith("kill_ps:"):
+                die_after = time.time() + float(part.split(":", 1)[1])
         while True:                       # not server.join(): signals must stay deliverable
             time.sleep(0.5)
+            if die_after is not None and time.time() >= die_after:
+                print("fault injection: ps dies", flush=True)
+                os._exit(19)
             if server.error is not None:
                 raise server.error
             if backend == "gloo" and not server.serving():
