@@ -203,6 +203,8 @@ def define_framework_flags(flag_values: FlagValues = FLAGS) -> FlagValues:
     DEFINE_integer("eval_every", 10000, "Test-set accuracy when global step %% this == 0 (reference: 10000)", flag_values)
     DEFINE_integer("steps_per_launch", 1, "Training steps fused into one persistent kernel launch", flag_values)
     DEFINE_string("ps_strategy", "round_robin", "round_robin | greedy_bytes variable placement", flag_values)
+    DEFINE_boolean("log_device_placement", False, "Print where every variable was placed (TF1 ConfigProto option; "
+                   "the reference sets it to False)", flag_values)
     DEFINE_integer("base_port", 12222, "First port of the cluster spec (reference: 12222)", flag_values)
     DEFINE_string("gpu_ids", "", "Comma-separated physical GPU ids (the launchers' GPU_ID array)", flag_values)
     DEFINE_boolean("unlocked_apply", False, "Apply pushes as unlocked read-modify-write like TF1 use_locking=False "

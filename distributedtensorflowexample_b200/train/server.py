@@ -32,6 +32,7 @@ class ServerConfig:
     device_index: int = 0                          # "gpu:0" = the one GPU this process sees (worker.py:17-22)
     store_timeout_s: float = 600.0
     allow_soft_placement: bool = True              # reference worker.py:120: fall back to CPU when no GPU
+    log_device_placement: bool = False             # reference worker.py:121 turns it off explicitly; here a flag
 
 
 def resolve_backend(name: str) -> str:

@@ -70,6 +70,9 @@ class Worker:
             raise ValueError("--sync and --optimizer adam are implemented on the CUDA path (the gloo "
                              "configuration reproduces the reference's async SGD only)")
         self.global_step = self.model.global_step
+        if flags.log_device_placement:
+            for v in self.model.store.all_variables():
+                print(f"{v.name}: ({'VariableV2'}) {v.device}", flush=True)
         if server.backend == "gloo":
             self._build_cpu()
         else:
