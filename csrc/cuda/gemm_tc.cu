@@ -31,13 +31,15 @@
 #include <cuda.h>
 #include <cuda_bf16.h>
 #include <mutex>
+#include <algorithm>
+#include <stdlib.h>
 
 namespace {
 
 constexpr int BM = 128, BK = 64, UMMA_K = 16;
 constexpr int kThreads = 192;
 
-enum { EPI_STORE = 0, EPI_BIAS_ACT = 1, EPI_ACTGRAD = 2, EPI_PUSH = 3 };
+enum { EPI_STORE = 0, EPI_BIAS_ACT = 1, EPI_ACTGRAD = 2, EPI_PUSH = 3, EPI_PUSH_TMA = 4 };
 enum { OUT_F32 = 0, OUT_BF16 = 1 };
 
 struct GemmTcArgs {
@@ -377,6 +379,20 @@ constexpr int BN2 = 256;
 constexpr int kStages2 = 6;
 constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;   // clears the CTA-rank bit of a shared::cluster address
 
+// TMA reduce-store: one bulk tensor op adds a whole shared-memory box into global (possibly peer) memory.
+__device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* map, const void* smem_src, int c0, int c1) {
+  asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];"
+               :: "l"(map), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" :: "r"(id), "r"(nthreads) : "memory");
+}
+
+struct DMaps { CUtensorMap m[8]; };   // one tensor map per row block of a partitioned push target
+
 __device__ __forceinline__ uint32_t cluster_ctarank() {
   uint32_t r;
   asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
@@ -421,17 +437,23 @@ __device__ __forceinline__ void tmem_dealloc_2sm(uint32_t taddr, uint32_t ncols)
 
 template <int A_MN, int B_MN, int EPI>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
-k_gemm_tc2(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, GemmTcArgs g) {
+k_gemm_tc2(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+           const __grid_constant__ DMaps dmaps, GemmTcArgs g) {
+  // EPI_PUSH_TMA: the epilogue stages the scaled bf16 tile in shared memory (4 swizzled 128x64 boxes) and
+  // pushes it with TMA reduce-adds - 16 KB per operation instead of 16 B per red instruction, which is what
+  // makes a push into a PEER shard run at NVLink speed.  It trades two pipeline stages for the staging tile.
+  constexpr int kStages = EPI == EPI_PUSH_TMA ? 4 : kStages2;
   constexpr uint32_t A_BYTES = BM * BK * 2;            // this CTA's 128 rows of A
   constexpr uint32_t B_BYTES = (BN2 / 2) * BK * 2;     // this CTA's half of B
   constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;  // 32 KB
+  constexpr uint32_t STAGING_BOX = BM * 128;           // 128 rows x 64 bf16
   constexpr uint32_t BOX_BYTES = 64 * BK * 2;
   constexpr uint32_t TMEM_COLS = 2 * BN2;              // two accumulator stages
 
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  __shared__ __align__(8) uint64_t full_bar[kStages2];
-  __shared__ __align__(8) uint64_t empty_bar[kStages2];
+  __shared__ __align__(8) uint64_t full_bar[kStages];
+  __shared__ __align__(8) uint64_t empty_bar[kStages];
   __shared__ __align__(8) uint64_t tmem_full_bar[2];
   __shared__ __align__(8) uint64_t tmem_empty_bar[2];
   __shared__ uint32_t tmem_base_holder;
@@ -448,7 +470,7 @@ k_gemm_tc2(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ C
     tma_prefetch_desc(&tmap_a);
     tma_prefetch_desc(&tmap_b);
 #pragma unroll
-    for (int s = 0; s < kStages2; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    for (int s = 0; s < kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
 #pragma unroll
     for (int s = 0; s < 2; ++s) { mbar_init(&tmem_full_bar[s], 1); mbar_init(&tmem_empty_bar[s], 8); }
     fence_barrier_init();
@@ -485,7 +507,7 @@ k_gemm_tc2(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ C
           } else {
             tma_load_2d_2sm(sb, &tmap_b, &full_bar[stage], k0, n0);
           }
-          if (++stage == kStages2) { stage = 0; phase ^= 1; }
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
       }
     }
@@ -513,7 +535,7 @@ k_gemm_tc2(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ C
             umma_bf16_2sm(tmem_d, adesc, bdesc, idesc, (kb | k) != 0);
           }
           umma_commit_2sm(&empty_bar[stage]);            // frees the stage in both CTAs
-          if (++stage == kStages2) { stage = 0; phase ^= 1; }
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
         umma_commit_2sm(&tmem_full_bar[as]);             // accumulator ready, both CTAs' epilogues
         if (++as == 2) { as = 0; aphase ^= 1; }
@@ -529,12 +551,48 @@ k_gemm_tc2(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ C
       mbar_wait(&tmem_full_bar[as], aphase);
       tc_fence_after();
       const int m = m0 + q * 32 + lane;
+      if (EPI == EPI_PUSH_TMA) {
+        uint8_t* staging = smem + (size_t)kStages * STAGE_BYTES;
+        const int row = q * 32 + lane;
+        // the previous tile's reduce-adds must have finished reading the staging tile
+        if (warp == 2 && lane == 0) tma_store_wait_read();
+        named_bar_sync(1, 128);
 #pragma unroll 1
-      for (int c = 0; c < BN2; c += 32) {
-        uint32_t r[32];
-        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN2 + c), r);
-        tmem_ld_wait();
-        if (m < g.M && n0 + c < g.N) epilogue_chunk<EPI>(g, m, n0 + c, r);
+        for (int c = 0; c < BN2; c += 32) {
+          uint32_t r[32];
+          tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN2 + c), r);
+          tmem_ld_wait();
+          // 32 columns = 4 chunks of 16 B inside the 128-byte row of box c/64, XOR-swizzled like the tensor map
+          uint8_t* rowp = staging + (size_t)(c >> 6) * STAGING_BOX + (size_t)row * 128;
+          const int chunk0 = (c & 32) ? 4 : 0;
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            uint4 pk;
+            pk.x = dtfe::pack_bf16x2(g.alpha * __uint_as_float(r[8 * u + 0]), g.alpha * __uint_as_float(r[8 * u + 1]));
+            pk.y = dtfe::pack_bf16x2(g.alpha * __uint_as_float(r[8 * u + 2]), g.alpha * __uint_as_float(r[8 * u + 3]));
+            pk.z = dtfe::pack_bf16x2(g.alpha * __uint_as_float(r[8 * u + 4]), g.alpha * __uint_as_float(r[8 * u + 5]));
+            pk.w = dtfe::pack_bf16x2(g.alpha * __uint_as_float(r[8 * u + 6]), g.alpha * __uint_as_float(r[8 * u + 7]));
+            *reinterpret_cast<uint4*>(rowp + (((chunk0 + u) ^ (row & 7)) << 4)) = pk;
+          }
+        }
+        fence_proxy_async();               // make the generic-proxy writes visible to the TMA engine
+        named_bar_sync(1, 128);
+        if (warp == 2 && lane == 0) {
+          int part = 0, mloc = m0;
+          if (g.nparts) { part = m0 / g.rows_per_part; mloc = m0 - part * g.rows_per_part; }
+#pragma unroll
+          for (int jb = 0; jb < BN2 / 64; ++jb)
+            if (n0 + jb * 64 < g.N) tma_reduce_add_2d(&dmaps.m[part], staging + (size_t)jb * STAGING_BOX, n0 + jb * 64, mloc);
+          tma_store_commit();
+        }
+      } else {
+#pragma unroll 1
+        for (int c = 0; c < BN2; c += 32) {
+          uint32_t r[32];
+          tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN2 + c), r);
+          tmem_ld_wait();
+          if (m < g.M && n0 + c < g.N) epilogue_chunk<EPI == EPI_PUSH_TMA ? EPI_PUSH : EPI>(g, m, n0 + c, r);
+        }
       }
       tc_fence_before();
       __syncwarp();
@@ -543,6 +601,7 @@ k_gemm_tc2(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ C
     }
   }
 
+  if (EPI == EPI_PUSH_TMA && warp == 2 && lane == 0) tma_store_wait_all();   // pushes complete before exit
   tc_fence_before();
   __syncthreads();
   cluster_sync_all();            // nobody exits (or frees TMEM) while its peer may still signal it
@@ -609,8 +668,10 @@ int launch_cfg(const CUtensorMap& ta, const CUtensorMap& tb, const GemmTcArgs& g
 }
 
 template <int A_MN, int B_MN, int EPI>
-int launch_cfg2(const CUtensorMap& ta, const CUtensorMap& tb, const GemmTcArgs& g, cudaStream_t stream) {
-  constexpr size_t smem = (size_t)kStages2 * (BM * BK * 2 + (BN2 / 2) * BK * 2) + 1024;
+int launch_cfg2(const CUtensorMap& ta, const CUtensorMap& tb, const DMaps& dm, const GemmTcArgs& g, cudaStream_t stream) {
+  constexpr size_t smem = EPI == EPI_PUSH_TMA
+      ? (size_t)4 * (BM * BK * 2 + (BN2 / 2) * BK * 2) + (size_t)(BN2 / 64) * BM * 128 + 1024
+      : (size_t)kStages2 * (BM * BK * 2 + (BN2 / 2) * BK * 2) + 1024;
   auto kern = k_gemm_tc2<A_MN, B_MN, EPI>;
   static bool configured[64] = {};
   static int sm_count[64] = {};
@@ -624,27 +685,28 @@ int launch_cfg2(const CUtensorMap& ta, const CUtensorMap& tb, const GemmTcArgs& 
   int tiles = ((g.M + 2 * BM - 1) / (2 * BM)) * ((g.N + BN2 - 1) / BN2);
   int clusters = (dev < 64 ? sm_count[dev] : 148) / 2;
   if (clusters > tiles) clusters = tiles;
-  kern<<<dim3(2 * clusters), kThreads, smem, stream>>>(ta, tb, g);
+  kern<<<dim3(2 * clusters), kThreads, smem, stream>>>(ta, tb, dm, g);
   DTFE_LAUNCH_CHECK();
   return 0;
 }
 
 template <int EPI>
-int launch_major2(int a_mn, int b_mn, const CUtensorMap& ta, const CUtensorMap& tb, const GemmTcArgs& g,
-                  cudaStream_t s) {
-  if (!a_mn && b_mn) return launch_cfg2<0, 1, EPI>(ta, tb, g, s);
-  if (!a_mn && !b_mn) return launch_cfg2<0, 0, EPI>(ta, tb, g, s);
-  if (a_mn && b_mn) return launch_cfg2<1, 1, EPI>(ta, tb, g, s);
-  return launch_cfg2<1, 0, EPI>(ta, tb, g, s);
+int launch_major2(int a_mn, int b_mn, const CUtensorMap& ta, const CUtensorMap& tb, const DMaps& dm,
+                  const GemmTcArgs& g, cudaStream_t s) {
+  if (!a_mn && b_mn) return launch_cfg2<0, 1, EPI>(ta, tb, dm, g, s);
+  if (!a_mn && !b_mn) return launch_cfg2<0, 0, EPI>(ta, tb, dm, g, s);
+  if (a_mn && b_mn) return launch_cfg2<1, 1, EPI>(ta, tb, dm, g, s);
+  return launch_cfg2<1, 0, EPI>(ta, tb, dm, g, s);
 }
 
-int launch_epi2(int epi, int a_mn, int b_mn, const CUtensorMap& ta, const CUtensorMap& tb, const GemmTcArgs& g,
-                cudaStream_t s) {
+int launch_epi2(int epi, int a_mn, int b_mn, const CUtensorMap& ta, const CUtensorMap& tb, const DMaps& dm,
+                const GemmTcArgs& g, cudaStream_t s) {
   switch (epi) {
-    case EPI_STORE: return launch_major2<EPI_STORE>(a_mn, b_mn, ta, tb, g, s);
-    case EPI_BIAS_ACT: return launch_major2<EPI_BIAS_ACT>(a_mn, b_mn, ta, tb, g, s);
-    case EPI_ACTGRAD: return launch_major2<EPI_ACTGRAD>(a_mn, b_mn, ta, tb, g, s);
-    case EPI_PUSH: return launch_major2<EPI_PUSH>(a_mn, b_mn, ta, tb, g, s);
+    case EPI_STORE: return launch_major2<EPI_STORE>(a_mn, b_mn, ta, tb, dm, g, s);
+    case EPI_BIAS_ACT: return launch_major2<EPI_BIAS_ACT>(a_mn, b_mn, ta, tb, dm, g, s);
+    case EPI_ACTGRAD: return launch_major2<EPI_ACTGRAD>(a_mn, b_mn, ta, tb, dm, g, s);
+    case EPI_PUSH: return launch_major2<EPI_PUSH>(a_mn, b_mn, ta, tb, dm, g, s);
+    case EPI_PUSH_TMA: return launch_major2<EPI_PUSH_TMA>(a_mn, b_mn, ta, tb, dm, g, s);
   }
   dtfe_set_error("gemm_tc: unknown epilogue %d", epi);
   return -1;
@@ -709,7 +771,26 @@ DTFE_API int dtfe_gemm_tc_bf16(const dtfe_gemm_tc* p, void* stream) {
   }
   if (p->epilogue == EPI_ACTGRAD) DTFE_REQUIRE(p->H != nullptr, "gemm_tc: EPI_ACTGRAD needs H");
   if (p->epilogue != EPI_PUSH) DTFE_REQUIRE(p->D != nullptr, "gemm_tc: D is null");
-  if (two_cta) return launch_epi2(p->epilogue, p->a_mn_major, p->b_mn_major, ta, tb, g, (cudaStream_t)stream);
+  if (two_cta) {
+    // Push through TMA reduce-adds when the target is a bf16 matrix whose row blocks line up with the tiles
+    static DMaps dm;   // zero-initialised; only read by the EPI_PUSH_TMA instantiation
+    DMaps local{};
+    int epi = p->epilogue;
+    const bool tma_ok = epi == EPI_PUSH && p->out_bf16 && p->G == nullptr && getenv("DTFE_NO_TMA_PUSH") == nullptr &&
+                        (p->ldd * 2) % 16 == 0 && (p->nparts == 0 ? p->D != nullptr : p->rows_per_part % BM == 0);
+    if (tma_ok) {
+      const int np = p->nparts ? p->nparts : 1;
+      bool ok = true;
+      for (int i = 0; i < np && ok; ++i) {
+        void* base = p->nparts ? p->D_parts[i] : p->D;
+        long rows = p->nparts ? std::min<long>(p->rows_per_part, (long)p->M - (long)i * p->rows_per_part) : p->M;
+        ok = base != nullptr && ((uintptr_t)base % 16) == 0 && rows > 0 &&
+             make_tmap(&local.m[i], base, (uint64_t)p->N, (uint64_t)rows, (uint64_t)p->ldd, 64, BM) == 0;
+      }
+      if (ok) epi = EPI_PUSH_TMA;
+    }
+    return launch_epi2(epi, p->a_mn_major, p->b_mn_major, ta, tb, epi == EPI_PUSH_TMA ? local : dm, g, (cudaStream_t)stream);
+  }
   return bn == 256 ? launch_epi<256>(p->epilogue, p->a_mn_major, p->b_mn_major, ta, tb, g, (cudaStream_t)stream)
                    : launch_epi<128>(p->epilogue, p->a_mn_major, p->b_mn_major, ta, tb, g, (cudaStream_t)stream);
 }

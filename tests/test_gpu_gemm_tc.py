@@ -66,3 +66,37 @@ def test_dense_layer_ops_tc(B_, din, dout):
     G.dense_bwd_dw_push_tc(x, dY, Wb, -0.01)
     want = W.float() - 0.01 * ref_g
     assert (Wb.float() - want).abs().max().item() < 2e-2 * want.abs().max().item() + 1e-3
+
+
+@pytest.mark.parametrize("parts", [0, 2, 4])
+@pytest.mark.parametrize("M,N,K", [(1024, 512, 256), (2048, 1536, 1024), (1000, 520, 300)])
+def test_push_epilogue_through_tma_reduce(M, N, K, parts):
+    """dW push of the 2-CTA kernel: bf16 target, whole tiles added with cp.reduce.async.bulk.tensor; must
+    agree with the per-thread red.add path and with fp32 math, also when the target is row-partitioned."""
+    import os
+    from distributedtensorflowexample_b200.ops import gemm_tc as G
+    if parts and M % (parts * 128):
+        pytest.skip("row blocks must be multiples of 128 rows for the TMA path (others fall back)")
+    X = _mk((K, M), 11, 0.5)        # A is [K][M] (M contiguous), B is [K][N]
+    dY = _mk((K, N), 12, 0.5)
+    W0 = _mk((M, N), 13, 1.0)
+    ref = W0.float() - 0.01 * (X.float().T @ dY.float())
+    outs = []
+    for no_tma in ("", "1"):
+        if no_tma:
+            os.environ["DTFE_NO_TMA_PUSH"] = "1"
+        else:
+            os.environ.pop("DTFE_NO_TMA_PUSH", None)
+        W = W0.clone()
+        if parts:
+            rp = M // parts
+            blocks = [W[i * rp:(i + 1) * rp] for i in range(parts)]
+            G.gemm_tc(X, dY, M, N, K, True, True, None, G.EPI_PUSH, alpha=-0.01, tile_n=512, D_parts=blocks)
+        else:
+            G.gemm_tc(X, dY, M, N, K, True, True, W, G.EPI_PUSH, alpha=-0.01, tile_n=512)
+        torch.cuda.synchronize()
+        outs.append(W.float())
+    os.environ.pop("DTFE_NO_TMA_PUSH", None)
+    tol = 2 ** -7 * ref.abs().max().item() + 1e-3
+    assert (outs[0] - ref).abs().max().item() <= tol
+    assert (outs[1] - ref).abs().max().item() <= tol
