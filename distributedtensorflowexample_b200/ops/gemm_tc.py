@@ -30,6 +30,7 @@ class _GemmTc(ctypes.Structure):
         ("tile_n", c_int),
         ("nparts", c_int), ("rows_per_part", c_int),
         ("D_parts", c_void_p * 8),
+        ("tma_push", c_int),
     ]
 
 
@@ -45,7 +46,7 @@ def _bf16(t: torch.Tensor, name: str) -> torch.Tensor:
 def gemm_tc(A: torch.Tensor, B: torch.Tensor, M: int, N: int, K: int, a_mn_major: bool, b_mn_major: bool,
             D: Optional[torch.Tensor], epilogue: int = EPI_STORE, bias: Optional[torch.Tensor] = None, act: int = 0,
             H: Optional[torch.Tensor] = None, alpha: float = 0.0, G: Optional[torch.Tensor] = None,
-            tile_n: int = 0, D_parts=None) -> None:
+            tile_n: int = 0, D_parts=None, tma_push: bool = False) -> None:
     _bf16(A, "A"); _bf16(B, "B")
     p = _GemmTc()
     p.M, p.N, p.K = M, N, K
@@ -66,6 +67,7 @@ def gemm_tc(A: torch.Tensor, B: torch.Tensor, M: int, N: int, K: int, a_mn_major
     if G is not None:
         p.G, p.ldg = G.data_ptr(), G.stride(0)
     p.tile_n = tile_n
+    p.tma_push = int(tma_push)
     if D_parts is not None:
         p.nparts, p.rows_per_part = len(D_parts), D_parts[0].shape[0]
         p.ldd, p.out_bf16 = D_parts[0].stride(0), int(D_parts[0].dtype == torch.bfloat16)
@@ -91,15 +93,16 @@ def dense_bwd_dx_tc(dY, W, Hprev, out, tile_n: int = 0):
     return out
 
 
-def dense_bwd_dw_push_tc(X, dY, W, alpha: float, grad_out=None, tile_n: int = 0):
+def dense_bwd_dw_push_tc(X, dY, W, alpha: float, grad_out=None, tile_n: int = 0, tma_push: bool = False):
     """W += alpha * X^T @ dY, pushed from the GEMM epilogue with red.add (W may be peer memory, or a list of
     row blocks of a partitioned variable, each in a different shard)."""
     Mb, K = X.shape
     N = dY.shape[1]
     if isinstance(W, (list, tuple)):
-        gemm_tc(X, dY, K, N, Mb, True, True, None, EPI_PUSH, alpha=alpha, G=grad_out, tile_n=tile_n, D_parts=list(W))
+        gemm_tc(X, dY, K, N, Mb, True, True, None, EPI_PUSH, alpha=alpha, G=grad_out, tile_n=tile_n, D_parts=list(W),
+                tma_push=tma_push)
     else:
-        gemm_tc(X, dY, K, N, Mb, True, True, W, EPI_PUSH, alpha=alpha, G=grad_out, tile_n=tile_n)
+        gemm_tc(X, dY, K, N, Mb, True, True, W, EPI_PUSH, alpha=alpha, G=grad_out, tile_n=tile_n, tma_push=tma_push)
 
 
 def smoke() -> None:

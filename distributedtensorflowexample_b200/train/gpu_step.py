@@ -205,7 +205,10 @@ class TcStepper:
     Matrices whose width is not a multiple of 8 (the 10 logits) are kept with a padded row pitch."""
 
     def __init__(self, spec: MLPSpec, batch: int, params: Sequence[torch.Tensor], global_step: torch.Tensor,
-                 lr: float, device, tile_n: int = 0):
+                 lr: float, device, tile_n: int = 0, stage_all: bool = False):
+        """``stage_all``: some shard is on a peer GPU - pull EVERY parameter (also biases and small matrices)
+        into a local replica once per step.  Peer reads bypass the local L2, and a GEMM epilogue that reads a
+        remote bias for each of its tiles was measured at +100 us per layer."""
         from ..ops import gemm_tc
         self.G = gemm_tc
         self.spec, self.batch, self.lr, self.tile_n = spec, batch, lr, tile_n
@@ -218,6 +221,7 @@ class TcStepper:
         # A partitioned weight is read many times per step by the GEMMs (once per M tile), and peer reads
         # bypass the local L2, so its blocks are pulled ONCE per step into a local replica (the reference's
         # sync_op, worker.py:81-85, as one L1-bypassing vector copy per block) and the GEMMs read that.
+        self.stage_all = stage_all
         self.replicas = {}
         self._pull_stream = None
         self._pending = set()
@@ -225,6 +229,11 @@ class TcStepper:
             if isinstance(p, (list, tuple)):
                 rows = sum(b.shape[0] for b in p)
                 self.replicas[i] = torch.empty(rows, p[0].stride(0), **bf)[:, :p[0].shape[1]]
+            elif stage_all:
+                if p.dim() == 2:
+                    self.replicas[i] = torch.empty(p.shape[0], p.stride(0), **bf)[:, :p.shape[1]]
+                else:
+                    self.replicas[i] = torch.empty(pad8(p.numel()), **bf)[:p.numel()]
         self.acts = [torch.empty(batch, pad8(d), **bf)[:, :d] for d in dims[1:-1]]
         C = dims[-1]
         self.logits = torch.empty(batch, pad8(C), device=dev, dtype=torch.float32)[:, :C]
@@ -250,16 +259,28 @@ class TcStepper:
         main = torch.cuda.current_stream()
         self._pull_stream.wait_stream(main)        # previous step's readers of the replicas are done
         with torch.cuda.stream(self._pull_stream):
-            for i, rep in self.replicas.items():
-                rp = self.params[i][0].shape[0]
-                for k, blk in enumerate(self.params[i]):
-                    dst = rep[k * rp:(k + 1) * rp]
-                    # blocks and replica rows share the pitch, so each block is one contiguous byte range
-                    n = rp * blk.stride(0)
+            # small things first (biases, thin matrices), then the big matrices in layer order
+            order = sorted(self.replicas, key=lambda i: (self._nbytes(i) > (1 << 20), i))
+            for i in order:
+                rep = self.replicas[i]
+                blocks = self.params[i] if isinstance(self.params[i], (list, tuple)) else [self.params[i]]
+                rp = blocks[0].shape[0]
+                for k, blk in enumerate(blocks):
+                    if blk.dim() == 2:
+                        dst = rep[k * rp:(k + 1) * rp]
+                        # blocks and replica rows share the pitch, so each block is one contiguous byte range
+                        n = rp * blk.stride(0)
+                    else:
+                        dst, n = rep, (blk.numel() + 1) // 2 * 2
                     ops.pull(torch.as_strided(dst, (n,), (1,)).view(torch.float32),
                              torch.as_strided(blk, (n,), (1,)).view(torch.float32))
                 self._pull_events[i].record(self._pull_stream)
         self._pending = set(self.replicas)
+
+    def _nbytes(self, i) -> int:
+        p = self.params[i]
+        blocks = p if isinstance(p, (list, tuple)) else [p]
+        return sum(b.numel() for b in blocks) * 2
 
     def _w(self, i):
         if i in self.replicas:
@@ -276,7 +297,7 @@ class TcStepper:
         L = self.spec.num_layers
         self.pull_partitioned()
         for l in range(L):
-            W, b = self._w(2 * l), self.params[2 * l + 1]
+            W, b = self._w(2 * l), self._w(2 * l + 1)
             last = l == L - 1
             out = logits if last else acts[l]
             self.G.dense_fwd_tc(h, W, b, ops.ACT_NONE if last else ops.ACT_SIGMOID, out, tile_n=self.tile_n)
@@ -299,7 +320,7 @@ class TcStepper:
             d_prev = None
             if l > 0:   # against the pre-update weights, so before this layer's push
                 d_prev = self.G.dense_bwd_dx_tc(d, self._w(2 * l), h_in, self.dacts[l - 1], tile_n=self.tile_n)
-            self.G.dense_bwd_dw_push_tc(h_in, d, W, alpha, tile_n=self.tile_n)
+            self.G.dense_bwd_dw_push_tc(h_in, d, W, alpha, tile_n=self.tile_n, tma_push=self.stage_all)
             ops.bias_grad_push_bf16(d, b, alpha)
             d = d_prev
         ops.global_step_add(self.global_step, 1, self.step)

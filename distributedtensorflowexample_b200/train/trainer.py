@@ -44,7 +44,7 @@ class GpuTrainer:
             self.layer = LayerwiseStepper(spec, batch, self.params, global_step, lr, self.device, atomic=atomic)
         elif engine == "tc":
             self.fused = None
-            self.layer = TcStepper(spec, batch, self.params, global_step, lr, self.device)
+            self.layer = TcStepper(spec, batch, self.params, global_step, lr, self.device, stage_all=remote)
         else:
             raise ValueError(engine)
         self.input_dtype = torch.bfloat16 if engine == "tc" else torch.float32

@@ -183,6 +183,8 @@ typedef struct dtfe_gemm_tc {
   int tile_n;
   int nparts; int rows_per_part;      /* push epilogue into a row-partitioned variable: row m of the result goes to */
   void* D_parts[8];                   /* D_parts[m / rows_per_part] (one block per ps shard); D is then ignored        */
+  int tma_push;                       /* push epilogue of the 2-CTA kernel through TMA reduce-adds (bf16 targets whose   */
+                                      /* row blocks are multiples of 128 rows): 16 KB bulk adds, meant for peer shards   */
 } dtfe_gemm_tc;
 int dtfe_gemm_tc_bf16(const dtfe_gemm_tc* p, void* stream);
 

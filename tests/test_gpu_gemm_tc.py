@@ -83,20 +83,16 @@ def test_push_epilogue_through_tma_reduce(M, N, K, parts):
     ref = W0.float() - 0.01 * (X.float().T @ dY.float())
     outs = []
     for no_tma in ("", "1"):
-        if no_tma:
-            os.environ["DTFE_NO_TMA_PUSH"] = "1"
-        else:
-            os.environ.pop("DTFE_NO_TMA_PUSH", None)
+        use_tma = not no_tma
         W = W0.clone()
         if parts:
             rp = M // parts
             blocks = [W[i * rp:(i + 1) * rp] for i in range(parts)]
-            G.gemm_tc(X, dY, M, N, K, True, True, None, G.EPI_PUSH, alpha=-0.01, tile_n=512, D_parts=blocks)
+            G.gemm_tc(X, dY, M, N, K, True, True, None, G.EPI_PUSH, alpha=-0.01, tile_n=512, D_parts=blocks, tma_push=use_tma)
         else:
-            G.gemm_tc(X, dY, M, N, K, True, True, W, G.EPI_PUSH, alpha=-0.01, tile_n=512)
+            G.gemm_tc(X, dY, M, N, K, True, True, W, G.EPI_PUSH, alpha=-0.01, tile_n=512, tma_push=use_tma)
         torch.cuda.synchronize()
         outs.append(W.float())
-    os.environ.pop("DTFE_NO_TMA_PUSH", None)
     tol = 2 ** -7 * ref.abs().max().item() + 1e-3
     assert (outs[0] - ref).abs().max().item() <= tol
     assert (outs[1] - ref).abs().max().item() <= tol
