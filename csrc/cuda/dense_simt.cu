@@ -174,15 +174,18 @@ __global__ void __launch_bounds__(256) k_colsum_push_bf16(const __nv_bfloat16* _
     float t0 = 0.f, t1 = 0.f;
 #pragma unroll
     for (int w = 0; w < 8; ++w) { t0 += red[w][lane * 2]; t1 += red[w][lane * 2 + 1]; }
-#pragma unroll
-    for (int e = 0; e < 2; ++e) {
-      int c = n + e;
-      float t = e ? t1 : t0;
-      if (c >= N) continue;
-      if (gout) atomicAdd(gout + c, t);
-      if (b) {
-        if (b_bf16) atomicAdd((__nv_bfloat16*)b + c, __float2bfloat16(alpha * t));
-        else dtfe::red_add_sys((float*)b + c, alpha * t);
+    if (gout) {
+      if (n < N) atomicAdd(gout + n, t0);
+      if (n + 1 < N) atomicAdd(gout + n + 1, t1);
+    }
+    if (b) {
+      if (b_bf16) {
+        __nv_bfloat16* bb = (__nv_bfloat16*)b;
+        if (n + 1 < N) dtfe::red_add_sys_bf16x2(bb + n, dtfe::pack_bf16x2(alpha * t0, alpha * t1));   // one packed red per lane
+        else if (n < N) atomicAdd(bb + n, __float2bfloat16(alpha * t0));
+      } else {
+        if (n < N) dtfe::red_add_sys((float*)b + n, alpha * t0);
+        if (n + 1 < N) dtfe::red_add_sys((float*)b + n + 1, alpha * t1);
       }
     }
   }
