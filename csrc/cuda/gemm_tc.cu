@@ -36,7 +36,17 @@
 
 namespace {
 
-constexpr int BM = 128, BK = 64, UMMA_K = 16;
+constexpr int BM = 128;
+// Element traits.  Everything in shared memory is laid out in 128-byte rows, and one UMMA consumes 32 bytes
+// of K per row, so bf16 (kind::f16) and fp32-as-tf32 (kind::tf32) differ only in these element counts.
+enum { DT_BF16 = 0, DT_TF32 = 1 };
+template <int DT> struct Elem {
+  static constexpr int ES = DT == DT_BF16 ? 2 : 4;       // bytes per operand element
+  static constexpr int BKE = 128 / ES;                    // K elements per pipeline stage (64 / 32)
+  static constexpr int UKE = 32 / ES;                     // K elements per tcgen05.mma (16 / 8)
+  static constexpr int MNB = 128 / ES;                    // MN elements per MN-major TMA box (64 / 32)
+  static constexpr uint32_t FMT = DT == DT_BF16 ? 1u : 2u;  // instruction-descriptor operand format
+};
 constexpr int kThreads = 192;
 
 enum { EPI_STORE = 0, EPI_BIAS_ACT = 1, EPI_ACTGRAD = 2, EPI_PUSH = 3, EPI_PUSH_TMA = 4 };
@@ -47,7 +57,7 @@ struct GemmTcArgs {
   void* D; long ldd;               // output (or pushed-into shard) matrix, row-major [M][ldd]
   int out_dtype;                   // OUT_F32 | OUT_BF16
   const void* bias; int bias_dtype;  // [N]  (EPI_BIAS_ACT)
-  const __nv_bfloat16* H; long ldh;  // [M][ldh] activation output being differentiated (EPI_ACTGRAD)
+  const void* H; long ldh; int h_f32;  // [M][ldh] activation output being differentiated (EPI_ACTGRAD), bf16 or fp32
   float alpha;                     // EPI_PUSH scale (-lr)
   int act;                         // 0 none, 1 sigmoid
   float* G; long ldg;              // optional fp32 raw gradient copy (EPI_PUSH), may be null
@@ -100,13 +110,23 @@ __device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
-__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
-  asm volatile(
-      "{\n\t"
-      ".reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
-      "}" :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum) : "memory");
+template <int DT>
+__device__ __forceinline__ void umma_1sm(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
+  if (DT == DT_BF16) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+        "}" :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum) : "memory");
+  } else {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+        "}" :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum) : "memory");
+  }
 }
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
@@ -136,9 +156,9 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_
   return d;
 }
 
-// kind::f16 instruction descriptor: bf16 x bf16 -> f32
-__host__ __device__ constexpr uint32_t make_idesc(int M, int N, int a_mn_major, int b_mn_major) {
-  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn_major << 15) | ((uint32_t)b_mn_major << 16) |
+// instruction descriptor: (bf16 x bf16 | tf32 x tf32) -> f32
+__host__ __device__ constexpr uint32_t make_idesc(int M, int N, int a_mn_major, int b_mn_major, uint32_t fmt) {
+  return (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)a_mn_major << 15) | ((uint32_t)b_mn_major << 16) |
          ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
@@ -164,7 +184,13 @@ __device__ __forceinline__ void epilogue_chunk(const GemmTcArgs& g, int m, int n
       }
     }
   } else if (EPI == EPI_ACTGRAD) {
-    const __nv_bfloat16* h = g.H + (long)m * g.ldh + n0;
+    if (g.h_f32) {
+      const float* hf = (const float*)g.H + (long)m * g.ldh + n0;
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (j < nvalid) { float hv = __ldg(hf + j); v[j] *= hv * (1.f - hv); }
+    } else {
+    const __nv_bfloat16* h = (const __nv_bfloat16*)g.H + (long)m * g.ldh + n0;
     if (nvalid == 32 && ((reinterpret_cast<uintptr_t>(h) & 15) == 0)) {
       const uint4* h4 = reinterpret_cast<const uint4*>(h);
 #pragma unroll
@@ -182,6 +208,7 @@ __device__ __forceinline__ void epilogue_chunk(const GemmTcArgs& g, int m, int n
 #pragma unroll
       for (int j = 0; j < 32; ++j)
         if (j < nvalid) { float hf = __bfloat162float(h[j]); v[j] *= hf * (1.f - hf); }
+    }
     }
   }
   if (EPI == EPI_PUSH) {
@@ -262,13 +289,15 @@ __device__ __forceinline__ void epilogue_chunk(const GemmTcArgs& g, int m, int n
 
 // ---------------------------------------------------------------- the kernel
 // BN: tile width (128 or 256); A_MN/B_MN: operand majors; STAGES: smem ring depth.
-template <int BN, int A_MN, int B_MN, int EPI, int STAGES>
+template <int DT, int BN, int A_MN, int B_MN, int EPI, int STAGES>
 __global__ void __launch_bounds__(kThreads, BN == 128 ? 2 : 1)
 k_gemm_tc(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, GemmTcArgs g) {
-  constexpr uint32_t A_BYTES = BM * BK * 2;   // 16 KB
-  constexpr uint32_t B_BYTES = BN * BK * 2;   // 16 / 32 KB
+  using E = Elem<DT>;
+  constexpr int BK = E::BKE;
+  constexpr uint32_t A_BYTES = BM * 128;      // 16 KB (128-byte rows)
+  constexpr uint32_t B_BYTES = BN * 128;      // 16 / 32 KB
   constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
-  constexpr uint32_t BOX_BYTES = 64 * BK * 2;  // one MN-major box: 64 mn x 64 k
+  constexpr uint32_t BOX_BYTES = 128 * BK;     // one MN-major box: 128 bytes of mn x BK k-rows
   constexpr uint32_t TMEM_COLS = BN;           // fp32 accumulator columns (power of two >= 32)
 
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -308,13 +337,13 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CU
         const int k0 = kb * BK;
         if (A_MN) {
 #pragma unroll
-          for (int b = 0; b < BM / 64; ++b) tma_load_2d(sa + b * BOX_BYTES, &tmap_a, &full_bar[stage], m0 + b * 64, k0);
+          for (int b = 0; b < BM / E::MNB; ++b) tma_load_2d(sa + b * BOX_BYTES, &tmap_a, &full_bar[stage], m0 + b * E::MNB, k0);
         } else {
           tma_load_2d(sa, &tmap_a, &full_bar[stage], k0, m0);
         }
         if (B_MN) {
 #pragma unroll
-          for (int b = 0; b < BN / 64; ++b) tma_load_2d(sb + b * BOX_BYTES, &tmap_b, &full_bar[stage], n0 + b * 64, k0);
+          for (int b = 0; b < BN / E::MNB; ++b) tma_load_2d(sb + b * BOX_BYTES, &tmap_b, &full_bar[stage], n0 + b * E::MNB, k0);
         } else {
           tma_load_2d(sb, &tmap_b, &full_bar[stage], k0, n0);
         }
@@ -324,7 +353,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CU
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
     if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc(BM, BN, A_MN, B_MN);
+      constexpr uint32_t idesc = make_idesc(BM, BN, A_MN, B_MN, E::FMT);
       int stage = 0; uint32_t phase = 0;
       for (int kb = 0; kb < num_kb; ++kb) {
         mbar_wait(&full_bar[stage], phase);
@@ -332,12 +361,12 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CU
         const uint32_t sa = smem_u32(smem + (size_t)stage * STAGE_BYTES);
         const uint32_t sb = sa + A_BYTES;
 #pragma unroll
-        for (int k = 0; k < BK / UMMA_K; ++k) {
-          const uint64_t adesc = A_MN ? make_smem_desc(sa + k * (UMMA_K * 128), BOX_BYTES, 1024)
-                                      : make_smem_desc(sa + k * (UMMA_K * 2), 16, 1024);
-          const uint64_t bdesc = B_MN ? make_smem_desc(sb + k * (UMMA_K * 128), BOX_BYTES, 1024)
-                                      : make_smem_desc(sb + k * (UMMA_K * 2), 16, 1024);
-          umma_bf16(tmem_base, adesc, bdesc, idesc, (kb | k) != 0);
+        for (int k = 0; k < 4; ++k) {   // 128-byte rows / 32 bytes of K per MMA
+          const uint64_t adesc = A_MN ? make_smem_desc(sa + k * (E::UKE * 128), BOX_BYTES, 1024)
+                                      : make_smem_desc(sa + k * 32, 16, 1024);
+          const uint64_t bdesc = B_MN ? make_smem_desc(sb + k * (E::UKE * 128), BOX_BYTES, 1024)
+                                      : make_smem_desc(sb + k * 32, 16, 1024);
+          umma_1sm<DT>(tmem_base, adesc, bdesc, idesc, (kb | k) != 0);
         }
         umma_commit(&empty_bar[stage]);   // frees this smem stage once the MMAs above have read it
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -408,13 +437,23 @@ __device__ __forceinline__ void tma_load_2d_2sm(void* smem_dst, const CUtensorMa
       "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
       :: "r"(smem_u32(smem_dst)), "l"(map), "r"(smem_u32(bar) & kPeerBitMask), "r"(c0), "r"(c1) : "memory");
 }
-__device__ __forceinline__ void umma_bf16_2sm(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
-  asm volatile(
-      "{\n\t"
-      ".reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t"
-      "}" :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum) : "memory");
+template <int DT>
+__device__ __forceinline__ void umma_2sm(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
+  if (DT == DT_BF16) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t"
+        "}" :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum) : "memory");
+  } else {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+        "}" :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum) : "memory");
+  }
 }
 __device__ __forceinline__ void umma_commit_2sm(uint64_t* bar) {
   // arrives on the barrier at this offset in BOTH CTAs of the pair
@@ -435,7 +474,7 @@ __device__ __forceinline__ void tmem_dealloc_2sm(uint32_t taddr, uint32_t ncols)
   asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" :: "r"(taddr), "r"(ncols) : "memory");
 }
 
-template <int A_MN, int B_MN, int EPI>
+template <int DT, int A_MN, int B_MN, int EPI>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 k_gemm_tc2(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
            const __grid_constant__ DMaps dmaps, GemmTcArgs g) {
@@ -443,11 +482,13 @@ k_gemm_tc2(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ C
   // pushes it with TMA reduce-adds - 16 KB per operation instead of 16 B per red instruction, which is what
   // makes a push into a PEER shard run at NVLink speed.  It trades two pipeline stages for the staging tile.
   constexpr int kStages = EPI == EPI_PUSH_TMA ? 4 : kStages2;
-  constexpr uint32_t A_BYTES = BM * BK * 2;            // this CTA's 128 rows of A
-  constexpr uint32_t B_BYTES = (BN2 / 2) * BK * 2;     // this CTA's half of B
+  using E = Elem<DT>;
+  constexpr int BK = E::BKE;
+  constexpr uint32_t A_BYTES = BM * 128;               // this CTA's 128 rows of A
+  constexpr uint32_t B_BYTES = (BN2 / 2) * 128;        // this CTA's half of B
   constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;  // 32 KB
   constexpr uint32_t STAGING_BOX = BM * 128;           // 128 rows x 64 bf16
-  constexpr uint32_t BOX_BYTES = 64 * BK * 2;
+  constexpr uint32_t BOX_BYTES = 128 * BK;
   constexpr uint32_t TMEM_COLS = 2 * BN2;              // two accumulator stages
 
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -497,13 +538,13 @@ k_gemm_tc2(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ C
           const int k0 = kb * BK;
           if (A_MN) {
 #pragma unroll
-            for (int b = 0; b < BM / 64; ++b) tma_load_2d_2sm(sa + b * BOX_BYTES, &tmap_a, &full_bar[stage], m0 + b * 64, k0);
+            for (int b = 0; b < BM / E::MNB; ++b) tma_load_2d_2sm(sa + b * BOX_BYTES, &tmap_a, &full_bar[stage], m0 + b * E::MNB, k0);
           } else {
             tma_load_2d_2sm(sa, &tmap_a, &full_bar[stage], k0, m0);
           }
           if (B_MN) {
 #pragma unroll
-            for (int b = 0; b < (BN2 / 2) / 64; ++b) tma_load_2d_2sm(sb + b * BOX_BYTES, &tmap_b, &full_bar[stage], n0 + b * 64, k0);
+            for (int b = 0; b < (BN2 / 2) / E::MNB; ++b) tma_load_2d_2sm(sb + b * BOX_BYTES, &tmap_b, &full_bar[stage], n0 + b * E::MNB, k0);
           } else {
             tma_load_2d_2sm(sb, &tmap_b, &full_bar[stage], k0, n0);
           }
@@ -514,7 +555,7 @@ k_gemm_tc2(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ C
   } else if (warp == 1) {
     // ===================== MMA issuer (leader CTA only) =====================
     if (leader && lane == 0) {
-      constexpr uint32_t idesc = make_idesc(2 * BM, BN2, A_MN, B_MN);
+      constexpr uint32_t idesc = make_idesc(2 * BM, BN2, A_MN, B_MN, E::FMT);
       int stage = 0; uint32_t phase = 0;
       int as = 0; uint32_t aphase = 0;
       for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
@@ -527,12 +568,12 @@ k_gemm_tc2(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ C
           const uint32_t sa = smem_u32(smem + (size_t)stage * STAGE_BYTES);
           const uint32_t sb = sa + A_BYTES;
 #pragma unroll
-          for (int k = 0; k < BK / UMMA_K; ++k) {
-            const uint64_t adesc = A_MN ? make_smem_desc(sa + k * (UMMA_K * 128), BOX_BYTES, 1024)
-                                        : make_smem_desc(sa + k * (UMMA_K * 2), 16, 1024);
-            const uint64_t bdesc = B_MN ? make_smem_desc(sb + k * (UMMA_K * 128), BOX_BYTES, 1024)
-                                        : make_smem_desc(sb + k * (UMMA_K * 2), 16, 1024);
-            umma_bf16_2sm(tmem_d, adesc, bdesc, idesc, (kb | k) != 0);
+          for (int k = 0; k < 4; ++k) {
+            const uint64_t adesc = A_MN ? make_smem_desc(sa + k * (E::UKE * 128), BOX_BYTES, 1024)
+                                        : make_smem_desc(sa + k * 32, 16, 1024);
+            const uint64_t bdesc = B_MN ? make_smem_desc(sb + k * (E::UKE * 128), BOX_BYTES, 1024)
+                                        : make_smem_desc(sb + k * 32, 16, 1024);
+            umma_2sm<DT>(tmem_d, adesc, bdesc, idesc, (kb | k) != 0);
           }
           umma_commit_2sm(&empty_bar[stage]);            // frees the stage in both CTAs
           if (++stage == kStages) { stage = 0; phase ^= 1; }
@@ -630,30 +671,30 @@ PFN_encodeTiled get_encode() {
   return fn;
 }
 
-// bf16 2-D tensor map over a row-major [rows][ld] matrix: inner dim = contiguous columns.
+// 2-D tensor map (bf16 or fp32 elements) over a row-major [rows][ld] matrix: inner dim = contiguous columns.
 int make_tmap(CUtensorMap* map, const void* base, uint64_t inner, uint64_t rows, uint64_t ld_elems,
-              uint32_t box_inner, uint32_t box_rows) {
+              uint32_t box_inner, uint32_t box_rows, int es = 2) {
   PFN_encodeTiled enc = get_encode();
   DTFE_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled is not available from this driver");
   DTFE_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "gemm_tc: operand base must be 16-byte aligned");
-  DTFE_REQUIRE((ld_elems * 2) % 16 == 0, "gemm_tc: row pitch (%llu elements) must be a multiple of 8 for TMA",
-               (unsigned long long)ld_elems);
+  DTFE_REQUIRE((ld_elems * es) % 16 == 0, "gemm_tc: row pitch (%llu elements of %d bytes) must be a multiple of 16 bytes for TMA",
+               (unsigned long long)ld_elems, es);
   cuuint64_t dims[2] = {inner, rows};
-  cuuint64_t strides[1] = {ld_elems * 2};
+  cuuint64_t strides[1] = {ld_elems * (uint64_t)es};
   cuuint32_t box[2] = {box_inner, box_rows};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+  CUresult r = enc(map, es == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), dims, strides, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   DTFE_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
   return 0;
 }
 
-template <int BN, int A_MN, int B_MN, int EPI>
+template <int DT, int BN, int A_MN, int B_MN, int EPI>
 int launch_cfg(const CUtensorMap& ta, const CUtensorMap& tb, const GemmTcArgs& g, cudaStream_t stream) {
   constexpr int STAGES = BN == 128 ? 3 : 4;   // 128: 97 KB -> two CTAs per SM; 256: 193 KB -> one
-  constexpr size_t smem = (size_t)STAGES * (BM * BK * 2 + BN * BK * 2) + 1024;
-  auto kern = k_gemm_tc<BN, A_MN, B_MN, EPI, STAGES>;
+  constexpr size_t smem = (size_t)STAGES * (BM * 128 + BN * 128) + 1024;
+  auto kern = k_gemm_tc<DT, BN, A_MN, B_MN, EPI, STAGES>;
   static bool configured[64] = {};
   int dev;
   DTFE_CUDA_CHECK(cudaGetDevice(&dev));
@@ -667,12 +708,12 @@ int launch_cfg(const CUtensorMap& ta, const CUtensorMap& tb, const GemmTcArgs& g
   return 0;
 }
 
-template <int A_MN, int B_MN, int EPI>
+template <int DT, int A_MN, int B_MN, int EPI>
 int launch_cfg2(const CUtensorMap& ta, const CUtensorMap& tb, const DMaps& dm, const GemmTcArgs& g, cudaStream_t stream) {
   constexpr size_t smem = EPI == EPI_PUSH_TMA
-      ? (size_t)4 * (BM * BK * 2 + (BN2 / 2) * BK * 2) + (size_t)(BN2 / 64) * BM * 128 + 1024
-      : (size_t)kStages2 * (BM * BK * 2 + (BN2 / 2) * BK * 2) + 1024;
-  auto kern = k_gemm_tc2<A_MN, B_MN, EPI>;
+      ? (size_t)4 * (BM * 128 + (BN2 / 2) * 128) + (size_t)(BN2 / 64) * BM * 128 + 1024
+      : (size_t)kStages2 * (BM * 128 + (BN2 / 2) * 128) + 1024;
+  auto kern = k_gemm_tc2<DT, A_MN, B_MN, EPI>;
   static bool configured[64] = {};
   static int sm_count[64] = {};
   int dev;
@@ -690,59 +731,61 @@ int launch_cfg2(const CUtensorMap& ta, const CUtensorMap& tb, const DMaps& dm, c
   return 0;
 }
 
-template <int EPI>
+template <int DT, int EPI>
 int launch_major2(int a_mn, int b_mn, const CUtensorMap& ta, const CUtensorMap& tb, const DMaps& dm,
                   const GemmTcArgs& g, cudaStream_t s) {
-  if (!a_mn && b_mn) return launch_cfg2<0, 1, EPI>(ta, tb, dm, g, s);
-  if (!a_mn && !b_mn) return launch_cfg2<0, 0, EPI>(ta, tb, dm, g, s);
-  if (a_mn && b_mn) return launch_cfg2<1, 1, EPI>(ta, tb, dm, g, s);
-  return launch_cfg2<1, 0, EPI>(ta, tb, dm, g, s);
+  if (!a_mn && b_mn) return launch_cfg2<DT, 0, 1, EPI>(ta, tb, dm, g, s);
+  if (!a_mn && !b_mn) return launch_cfg2<DT, 0, 0, EPI>(ta, tb, dm, g, s);
+  if (a_mn && b_mn) return launch_cfg2<DT, 1, 1, EPI>(ta, tb, dm, g, s);
+  return launch_cfg2<DT, 1, 0, EPI>(ta, tb, dm, g, s);
 }
 
+template <int DT>
 int launch_epi2(int epi, int a_mn, int b_mn, const CUtensorMap& ta, const CUtensorMap& tb, const DMaps& dm,
                 const GemmTcArgs& g, cudaStream_t s) {
   switch (epi) {
-    case EPI_STORE: return launch_major2<EPI_STORE>(a_mn, b_mn, ta, tb, dm, g, s);
-    case EPI_BIAS_ACT: return launch_major2<EPI_BIAS_ACT>(a_mn, b_mn, ta, tb, dm, g, s);
-    case EPI_ACTGRAD: return launch_major2<EPI_ACTGRAD>(a_mn, b_mn, ta, tb, dm, g, s);
-    case EPI_PUSH: return launch_major2<EPI_PUSH>(a_mn, b_mn, ta, tb, dm, g, s);
-    case EPI_PUSH_TMA: return launch_major2<EPI_PUSH_TMA>(a_mn, b_mn, ta, tb, dm, g, s);
+    case EPI_STORE: return launch_major2<DT, EPI_STORE>(a_mn, b_mn, ta, tb, dm, g, s);
+    case EPI_BIAS_ACT: return launch_major2<DT, EPI_BIAS_ACT>(a_mn, b_mn, ta, tb, dm, g, s);
+    case EPI_ACTGRAD: return launch_major2<DT, EPI_ACTGRAD>(a_mn, b_mn, ta, tb, dm, g, s);
+    case EPI_PUSH: return launch_major2<DT, EPI_PUSH>(a_mn, b_mn, ta, tb, dm, g, s);
+    case EPI_PUSH_TMA:
+      if (DT == DT_BF16) return launch_major2<DT_BF16, EPI_PUSH_TMA>(a_mn, b_mn, ta, tb, dm, g, s);
+      break;
   }
   dtfe_set_error("gemm_tc: unknown epilogue %d", epi);
   return -1;
 }
 
-template <int BN, int EPI>
+template <int DT, int BN, int EPI>
 int launch_major(int a_mn, int b_mn, const CUtensorMap& ta, const CUtensorMap& tb, const GemmTcArgs& g,
                  cudaStream_t s) {
-  if (!a_mn && b_mn) return launch_cfg<BN, 0, 1, EPI>(ta, tb, g, s);
-  if (!a_mn && !b_mn) return launch_cfg<BN, 0, 0, EPI>(ta, tb, g, s);
-  if (a_mn && b_mn) return launch_cfg<BN, 1, 1, EPI>(ta, tb, g, s);
-  return launch_cfg<BN, 1, 0, EPI>(ta, tb, g, s);
+  if (!a_mn && b_mn) return launch_cfg<DT, BN, 0, 1, EPI>(ta, tb, g, s);
+  if (!a_mn && !b_mn) return launch_cfg<DT, BN, 0, 0, EPI>(ta, tb, g, s);
+  if (a_mn && b_mn) return launch_cfg<DT, BN, 1, 1, EPI>(ta, tb, g, s);
+  return launch_cfg<DT, BN, 1, 0, EPI>(ta, tb, g, s);
 }
 
-template <int BN>
+template <int DT, int BN>
 int launch_epi(int epi, int a_mn, int b_mn, const CUtensorMap& ta, const CUtensorMap& tb, const GemmTcArgs& g,
                cudaStream_t s) {
   switch (epi) {
-    case EPI_STORE: return launch_major<BN, EPI_STORE>(a_mn, b_mn, ta, tb, g, s);
-    case EPI_BIAS_ACT: return launch_major<BN, EPI_BIAS_ACT>(a_mn, b_mn, ta, tb, g, s);
-    case EPI_ACTGRAD: return launch_major<BN, EPI_ACTGRAD>(a_mn, b_mn, ta, tb, g, s);
-    case EPI_PUSH: return launch_major<BN, EPI_PUSH>(a_mn, b_mn, ta, tb, g, s);
+    case EPI_STORE: return launch_major<DT, BN, EPI_STORE>(a_mn, b_mn, ta, tb, g, s);
+    case EPI_BIAS_ACT: return launch_major<DT, BN, EPI_BIAS_ACT>(a_mn, b_mn, ta, tb, g, s);
+    case EPI_ACTGRAD: return launch_major<DT, BN, EPI_ACTGRAD>(a_mn, b_mn, ta, tb, g, s);
+    case EPI_PUSH: return launch_major<DT, BN, EPI_PUSH>(a_mn, b_mn, ta, tb, g, s);
   }
   dtfe_set_error("gemm_tc: unknown epilogue %d", epi);
   return -1;
 }
 
-}  // namespace
-
-// D[M,N] (op)= A . B with bf16 operands and fp32 accumulation on the 5th-gen tensor cores.
-//   a_mn_major = 0: A is [M][lda] (K contiguous);  1: A is [K][lda] (M contiguous)
-//   b_mn_major = 0: B is [N][ldb] (K contiguous);  1: B is [K][ldb] (N contiguous)
-DTFE_API int dtfe_gemm_tc_bf16(const dtfe_gemm_tc* p, void* stream) {
+// Shared implementation of the two public entry points.
+template <int DT>
+int gemm_tc_impl(const dtfe_gemm_tc* p, void* stream) {
+  using E = Elem<DT>;
   DTFE_REQUIRE(p->M > 0 && p->N > 0 && p->K > 0, "gemm_tc: empty problem");
   DTFE_REQUIRE(p->tile_n == 128 || p->tile_n == 256 || p->tile_n == 0 || p->tile_n == 512,
                "gemm_tc: tile_n must be 0 (auto), 128, 256 (1-CTA kernels) or 512 (= 2-CTA 256x256 persistent kernel)");
+  DTFE_REQUIRE(!(DT == DT_TF32 && p->tile_n == 256), "gemm_tc: the fp32/tf32 path has 128-wide and 2-CTA tiles only");
   // auto: the 2-CTA kernel whenever the problem has at least one full 256x256 tile per SM pair
   const bool two_cta = p->tile_n == 512 ||
                        (p->tile_n == 0 && p->M >= 512 && p->N >= 512 && p->K >= 1024 &&
@@ -750,17 +793,17 @@ DTFE_API int dtfe_gemm_tc_bf16(const dtfe_gemm_tc* p, void* stream) {
   int bn = two_cta ? 128 : (p->tile_n ? p->tile_n : 128);   // B box rows: 128 = half of BN2
   CUtensorMap ta, tb;
   int rc;
-  if (p->a_mn_major) rc = make_tmap(&ta, p->A, (uint64_t)p->M, (uint64_t)p->K, (uint64_t)p->lda, 64, BK);
-  else rc = make_tmap(&ta, p->A, (uint64_t)p->K, (uint64_t)p->M, (uint64_t)p->lda, BK, BM);
+  if (p->a_mn_major) rc = make_tmap(&ta, p->A, (uint64_t)p->M, (uint64_t)p->K, (uint64_t)p->lda, E::MNB, E::BKE, E::ES);
+  else rc = make_tmap(&ta, p->A, (uint64_t)p->K, (uint64_t)p->M, (uint64_t)p->lda, E::BKE, BM, E::ES);
   if (rc) return rc;
-  if (p->b_mn_major) rc = make_tmap(&tb, p->B, (uint64_t)p->N, (uint64_t)p->K, (uint64_t)p->ldb, 64, BK);
-  else rc = make_tmap(&tb, p->B, (uint64_t)p->K, (uint64_t)p->N, (uint64_t)p->ldb, BK, (uint32_t)bn);
+  if (p->b_mn_major) rc = make_tmap(&tb, p->B, (uint64_t)p->N, (uint64_t)p->K, (uint64_t)p->ldb, E::MNB, E::BKE, E::ES);
+  else rc = make_tmap(&tb, p->B, (uint64_t)p->K, (uint64_t)p->N, (uint64_t)p->ldb, E::BKE, (uint32_t)bn, E::ES);
   if (rc) return rc;
   GemmTcArgs g{};
   g.M = p->M; g.N = p->N; g.K = p->K;
   g.D = p->D; g.ldd = p->ldd; g.out_dtype = p->out_bf16 ? OUT_BF16 : OUT_F32;
   g.bias = p->bias; g.bias_dtype = p->bias_bf16 ? OUT_BF16 : OUT_F32;
-  g.H = (const __nv_bfloat16*)p->H; g.ldh = p->ldh;
+  g.H = p->H; g.ldh = p->ldh; g.h_f32 = DT == DT_TF32;
   g.alpha = p->alpha; g.act = p->act; g.G = p->G; g.ldg = p->ldg;
   DTFE_REQUIRE(p->nparts >= 0 && p->nparts <= 8, "gemm_tc: nparts must be in [0,8]");
   if (p->nparts) {
@@ -779,7 +822,7 @@ DTFE_API int dtfe_gemm_tc_bf16(const dtfe_gemm_tc* p, void* stream) {
     // (locally the per-thread red.add path keeps two more pipeline stages and is ~10 % faster; the bulk path
     // is for targets in peer HBM, where 16 KB operations instead of 16 B ones matter - callers ask for it)
     const bool want_tma = (p->tma_push || getenv("DTFE_TMA_PUSH") != nullptr) && getenv("DTFE_NO_TMA_PUSH") == nullptr;
-    const bool tma_ok = want_tma && epi == EPI_PUSH && p->out_bf16 && p->G == nullptr &&
+    const bool tma_ok = DT == DT_BF16 && want_tma && epi == EPI_PUSH && p->out_bf16 && p->G == nullptr &&
                         (p->ldd * 2) % 16 == 0 && (p->nparts == 0 ? p->D != nullptr : p->rows_per_part % BM == 0);
     if (tma_ok) {
       const int np = p->nparts ? p->nparts : 1;
@@ -792,8 +835,21 @@ DTFE_API int dtfe_gemm_tc_bf16(const dtfe_gemm_tc* p, void* stream) {
       }
       if (ok) epi = EPI_PUSH_TMA;
     }
-    return launch_epi2(epi, p->a_mn_major, p->b_mn_major, ta, tb, epi == EPI_PUSH_TMA ? local : dm, g, (cudaStream_t)stream);
+    return launch_epi2<DT>(epi, p->a_mn_major, p->b_mn_major, ta, tb, epi == EPI_PUSH_TMA ? local : dm, g, (cudaStream_t)stream);
   }
-  return bn == 256 ? launch_epi<256>(p->epilogue, p->a_mn_major, p->b_mn_major, ta, tb, g, (cudaStream_t)stream)
-                   : launch_epi<128>(p->epilogue, p->a_mn_major, p->b_mn_major, ta, tb, g, (cudaStream_t)stream);
+  if (DT == DT_BF16 && bn == 256)
+    return launch_epi<DT_BF16, 256>(p->epilogue, p->a_mn_major, p->b_mn_major, ta, tb, g, (cudaStream_t)stream);
+  return launch_epi<DT, 128>(p->epilogue, p->a_mn_major, p->b_mn_major, ta, tb, g, (cudaStream_t)stream);
 }
+
+}  // namespace
+
+// D[M,N] (op)= A . B with bf16 operands and fp32 accumulation on the 5th-gen tensor cores.
+//   a_mn_major = 0: A is [M][lda] (K contiguous);  1: A is [K][lda] (M contiguous)
+//   b_mn_major = 0: B is [N][ldb] (K contiguous);  1: B is [K][ldb] (N contiguous)
+DTFE_API int dtfe_gemm_tc_bf16(const dtfe_gemm_tc* p, void* stream) { return gemm_tc_impl<DT_BF16>(p, stream); }
+
+// Same kernels with fp32 operands fed to the tensor cores as tf32 (kind::tf32; fp32 accumulation): lets
+// fp32 parameter shards - the reference's dtype - be pulled by TMA straight into the MMA without a cast.
+// H (EPI_ACTGRAD) and bias are fp32 here; row pitches must be multiples of 4 elements.
+DTFE_API int dtfe_gemm_tc_tf32(const dtfe_gemm_tc* p, void* stream) { return gemm_tc_impl<DT_TF32>(p, stream); }

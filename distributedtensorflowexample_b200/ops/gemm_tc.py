@@ -34,12 +34,13 @@ class _GemmTc(ctypes.Structure):
     ]
 
 
-cuda_ops.register_sigs({"dtfe_gemm_tc_bf16": ([c_void_p, c_void_p], c_int)})
+cuda_ops.register_sigs({"dtfe_gemm_tc_bf16": ([c_void_p, c_void_p], c_int),
+                        "dtfe_gemm_tc_tf32": ([c_void_p, c_void_p], c_int)})
 
 
-def _bf16(t: torch.Tensor, name: str) -> torch.Tensor:
-    if t.dtype != torch.bfloat16 or not t.is_cuda or t.dim() != 2 or t.stride(1) != 1:
-        raise TypeError(f"{name}: expected a 2-D CUDA bfloat16 tensor with contiguous rows, got {t.dtype} {tuple(t.shape)}")
+def _bf16(t: torch.Tensor, name: str, dtype=torch.bfloat16) -> torch.Tensor:
+    if t.dtype != dtype or not t.is_cuda or t.dim() != 2 or t.stride(1) != 1:
+        raise TypeError(f"{name}: expected a 2-D CUDA {dtype} tensor with contiguous rows, got {t.dtype} {tuple(t.shape)}")
     return t
 
 
@@ -47,7 +48,11 @@ def gemm_tc(A: torch.Tensor, B: torch.Tensor, M: int, N: int, K: int, a_mn_major
             D: Optional[torch.Tensor], epilogue: int = EPI_STORE, bias: Optional[torch.Tensor] = None, act: int = 0,
             H: Optional[torch.Tensor] = None, alpha: float = 0.0, G: Optional[torch.Tensor] = None,
             tile_n: int = 0, D_parts=None, tma_push: bool = False) -> None:
-    _bf16(A, "A"); _bf16(B, "B")
+    """bf16 operands run as kind::f16, float32 operands as kind::tf32 (both accumulate in fp32)."""
+    dt = A.dtype
+    if dt not in (torch.bfloat16, torch.float32):
+        raise TypeError("gemm_tc operands must be bfloat16 or float32")
+    _bf16(A, "A", dt); _bf16(B, "B", dt)
     p = _GemmTc()
     p.M, p.N, p.K = M, N, K
     p.A, p.lda, p.a_mn_major = A.data_ptr(), A.stride(0), int(a_mn_major)
@@ -61,7 +66,7 @@ def gemm_tc(A: torch.Tensor, B: torch.Tensor, M: int, N: int, K: int, a_mn_major
         p.bias, p.bias_bf16 = bias.data_ptr(), int(bias.dtype == torch.bfloat16)
     p.act = act
     if H is not None:
-        _bf16(H, "H")
+        _bf16(H, "H", dt)
         p.H, p.ldh = H.data_ptr(), H.stride(0)
     p.alpha = alpha
     if G is not None:
@@ -73,8 +78,8 @@ def gemm_tc(A: torch.Tensor, B: torch.Tensor, M: int, N: int, K: int, a_mn_major
         p.ldd, p.out_bf16 = D_parts[0].stride(0), int(D_parts[0].dtype == torch.bfloat16)
         for i, t in enumerate(D_parts):
             p.D_parts[i] = t.data_ptr()
-    check(cuda_ops.lib().dtfe_gemm_tc_bf16(ctypes.byref(p), torch.cuda.current_stream().cuda_stream),
-          "dtfe_gemm_tc_bf16")
+    fn = cuda_ops.lib().dtfe_gemm_tc_bf16 if dt == torch.bfloat16 else cuda_ops.lib().dtfe_gemm_tc_tf32
+    check(fn(ctypes.byref(p), torch.cuda.current_stream().cuda_stream), "dtfe_gemm_tc")
 
 
 def dense_fwd_tc(x, W, b, act: int, out, tile_n: int = 0):

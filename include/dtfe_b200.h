@@ -187,6 +187,10 @@ typedef struct dtfe_gemm_tc {
                                       /* row blocks are multiples of 128 rows): 16 KB bulk adds, meant for peer shards   */
 } dtfe_gemm_tc;
 int dtfe_gemm_tc_bf16(const dtfe_gemm_tc* p, void* stream);
+/* Same struct, fp32 operands consumed by the tensor cores as tf32 (kind::tf32), fp32 H/bias/outputs: fp32
+ * parameter shards - the reference's dtype (worker.py:47-53) - go from TMA straight into the MMA.  Row pitches
+ * must be multiples of 4 elements; tile_n 0, 128 or 512. */
+int dtfe_gemm_tc_tf32(const dtfe_gemm_tc* p, void* stream);
 
 #ifdef __cplusplus
 }

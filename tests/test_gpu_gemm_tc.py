@@ -96,3 +96,49 @@ def test_push_epilogue_through_tma_reduce(M, N, K, parts):
     tol = 2 ** -7 * ref.abs().max().item() + 1e-3
     assert (outs[0] - ref).abs().max().item() <= tol
     assert (outs[1] - ref).abs().max().item() <= tol
+
+
+@pytest.mark.parametrize("tile_n", [128, 512])
+@pytest.mark.parametrize("M,N,K", [(128, 128, 32), (100, 100, 784), (300, 520, 200), (1024, 768, 1024)])
+@pytest.mark.parametrize("a_mn,b_mn", [(0, 0), (0, 1), (1, 1), (1, 0)])
+def test_gemm_tc_tf32_all_majors(M, N, K, a_mn, b_mn, tile_n):
+    """fp32 operands through kind::tf32 (10-bit mantissa inputs, fp32 accumulation)."""
+    from distributedtensorflowexample_b200.ops import gemm_tc as G
+    pad = lambda n: (n + 3) // 4 * 4
+    g = torch.Generator(device="cuda").manual_seed(7)
+    A = torch.randn((K, pad(M)) if a_mn else (M, pad(K)), device="cuda", generator=g)
+    B = torch.randn((K, pad(N)) if b_mn else (N, pad(K)), device="cuda", generator=g)
+    Av = A[:, :M] if a_mn else A[:, :K]
+    Bv = B[:, :N] if b_mn else B[:, :K]
+    D = torch.full((M, N), float("nan"), device="cuda")
+    G.gemm_tc(Av, Bv, M, N, K, bool(a_mn), bool(b_mn), D, tile_n=tile_n)
+    torch.cuda.synchronize()
+    Af = Av.double().T if a_mn else Av.double()
+    Bf = Bv.double() if b_mn else Bv.double().T
+    ref = Af @ Bf
+    assert torch.isfinite(D).all()
+    err = (D.double() - ref).abs().max().item()
+    assert err <= 2e-3 * (K ** 0.5) * 1.0 + 1e-3, (err, ref.abs().max().item())     # tf32: ~1e-3 relative per product
+
+
+def test_dense_layer_ops_tf32_on_reference_shapes():
+    """The reference model's own shapes and dtype (fp32 [784,100] kernel, batch 100) on the tensor cores."""
+    from distributedtensorflowexample_b200.ops import gemm_tc as G
+    g = torch.Generator(device="cuda").manual_seed(3)
+    x = torch.rand(100, 784, device="cuda", generator=g)
+    W = torch.randn(784, 100, device="cuda", generator=g) * 0.05
+    b = torch.randn(100, device="cuda", generator=g)
+    out = torch.empty(100, 100, device="cuda")
+    G.dense_fwd_tc(x, W, b, 1, out)
+    ref = torch.sigmoid(x.double() @ W.double() + b.double())
+    assert (out.double() - ref).abs().max().item() < 5e-3
+    dY = torch.randn(100, 100, device="cuda", generator=g) * 0.1
+    Wn = W.clone()
+    G.dense_bwd_dw_push_tc(x, dY, Wn, -0.1)
+    want = W.double() - 0.1 * (x.double().T @ dY.double())
+    assert (Wn.double() - want).abs().max().item() < 5e-3
+    Hprev = torch.rand(100, 784, device="cuda", generator=g)
+    dX = torch.empty(100, 784, device="cuda")
+    G.dense_bwd_dx_tc(dY, W, Hprev, dX)
+    ref_dx = (dY.double() @ W.double().T) * Hprev.double() * (1 - Hprev.double())
+    assert (dX.double() - ref_dx).abs().max().item() < 5e-3
