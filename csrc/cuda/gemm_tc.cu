@@ -46,6 +46,10 @@ template <int DT> struct Elem {
   static constexpr int UKE = 32 / ES;                     // K elements per tcgen05.mma (16 / 8)
   static constexpr int MNB = 128 / ES;                    // MN elements per MN-major TMA box (64 / 32)
   static constexpr uint32_t FMT = DT == DT_BF16 ? 1u : 2u;  // instruction-descriptor operand format
+  // MN-major operands: bf16 uses the ordinary 128B swizzle (8-row atoms); tf32 must use the 32-byte-base
+  // variant (4-row atoms) on both the TMA side (SWIZZLE_128B_ATOM_32B) and the descriptor side.
+  static constexpr uint32_t MN_LAYOUT = DT == DT_BF16 ? 2u : 1u;
+  static constexpr uint32_t MN_SBO = DT == DT_BF16 ? 1024u : 512u;
 };
 constexpr int kThreads = 192;
 
@@ -146,13 +150,16 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* r) {
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // Shared-memory matrix descriptor (version 1, SWIZZLE_128B).  lbo/sbo in bytes.
-__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+// layout_type: 2 = SWIZZLE_128B (16-byte chunks), 1 = SWIZZLE_128B_BASE32B (32-byte chunks, 4-row period; the
+// only layout tcgen05 accepts for MN-major tf32 operands - CUTLASS sm100_common.inl says the same).
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes,
+                                                   uint32_t layout_type = 2) {
   uint64_t d = 0;
   d |= (uint64_t)((saddr >> 4) & 0x3fff);
   d |= (uint64_t)((lbo_bytes >> 4) & 0x3fff) << 16;
   d |= (uint64_t)((sbo_bytes >> 4) & 0x3fff) << 32;
   d |= (uint64_t)1 << 46;   // descriptor version (Blackwell)
-  d |= (uint64_t)2 << 61;   // SWIZZLE_128B
+  d |= (uint64_t)layout_type << 61;
   return d;
 }
 
@@ -362,9 +369,9 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CU
         const uint32_t sb = sa + A_BYTES;
 #pragma unroll
         for (int k = 0; k < 4; ++k) {   // 128-byte rows / 32 bytes of K per MMA
-          const uint64_t adesc = A_MN ? make_smem_desc(sa + k * (E::UKE * 128), BOX_BYTES, 1024)
+          const uint64_t adesc = A_MN ? make_smem_desc(sa + k * (E::UKE * 128), BOX_BYTES, E::MN_SBO, E::MN_LAYOUT)
                                       : make_smem_desc(sa + k * 32, 16, 1024);
-          const uint64_t bdesc = B_MN ? make_smem_desc(sb + k * (E::UKE * 128), BOX_BYTES, 1024)
+          const uint64_t bdesc = B_MN ? make_smem_desc(sb + k * (E::UKE * 128), BOX_BYTES, E::MN_SBO, E::MN_LAYOUT)
                                       : make_smem_desc(sb + k * 32, 16, 1024);
           umma_1sm<DT>(tmem_base, adesc, bdesc, idesc, (kb | k) != 0);
         }
@@ -569,9 +576,9 @@ k_gemm_tc2(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ C
           const uint32_t sb = sa + A_BYTES;
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
-            const uint64_t adesc = A_MN ? make_smem_desc(sa + k * (E::UKE * 128), BOX_BYTES, 1024)
+            const uint64_t adesc = A_MN ? make_smem_desc(sa + k * (E::UKE * 128), BOX_BYTES, E::MN_SBO, E::MN_LAYOUT)
                                         : make_smem_desc(sa + k * 32, 16, 1024);
-            const uint64_t bdesc = B_MN ? make_smem_desc(sb + k * (E::UKE * 128), BOX_BYTES, 1024)
+            const uint64_t bdesc = B_MN ? make_smem_desc(sb + k * (E::UKE * 128), BOX_BYTES, E::MN_SBO, E::MN_LAYOUT)
                                         : make_smem_desc(sb + k * 32, 16, 1024);
             umma_2sm<DT>(tmem_d, adesc, bdesc, idesc, (kb | k) != 0);
           }
@@ -673,7 +680,7 @@ PFN_encodeTiled get_encode() {
 
 // 2-D tensor map (bf16 or fp32 elements) over a row-major [rows][ld] matrix: inner dim = contiguous columns.
 int make_tmap(CUtensorMap* map, const void* base, uint64_t inner, uint64_t rows, uint64_t ld_elems,
-              uint32_t box_inner, uint32_t box_rows, int es = 2) {
+              uint32_t box_inner, uint32_t box_rows, int es = 2, bool atom32 = false) {
   PFN_encodeTiled enc = get_encode();
   DTFE_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled is not available from this driver");
   DTFE_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "gemm_tc: operand base must be 16-byte aligned");
@@ -684,7 +691,8 @@ int make_tmap(CUtensorMap* map, const void* base, uint64_t inner, uint64_t rows,
   cuuint32_t box[2] = {box_inner, box_rows};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = enc(map, es == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), dims, strides, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, atom32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   DTFE_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
   return 0;
@@ -793,10 +801,10 @@ int gemm_tc_impl(const dtfe_gemm_tc* p, void* stream) {
   int bn = two_cta ? 128 : (p->tile_n ? p->tile_n : 128);   // B box rows: 128 = half of BN2
   CUtensorMap ta, tb;
   int rc;
-  if (p->a_mn_major) rc = make_tmap(&ta, p->A, (uint64_t)p->M, (uint64_t)p->K, (uint64_t)p->lda, E::MNB, E::BKE, E::ES);
+  if (p->a_mn_major) rc = make_tmap(&ta, p->A, (uint64_t)p->M, (uint64_t)p->K, (uint64_t)p->lda, E::MNB, E::BKE, E::ES, DT == DT_TF32);
   else rc = make_tmap(&ta, p->A, (uint64_t)p->K, (uint64_t)p->M, (uint64_t)p->lda, E::BKE, BM, E::ES);
   if (rc) return rc;
-  if (p->b_mn_major) rc = make_tmap(&tb, p->B, (uint64_t)p->N, (uint64_t)p->K, (uint64_t)p->ldb, E::MNB, E::BKE, E::ES);
+  if (p->b_mn_major) rc = make_tmap(&tb, p->B, (uint64_t)p->N, (uint64_t)p->K, (uint64_t)p->ldb, E::MNB, E::BKE, E::ES, DT == DT_TF32);
   else rc = make_tmap(&tb, p->B, (uint64_t)p->K, (uint64_t)p->N, (uint64_t)p->ldb, E::BKE, (uint32_t)bn, E::ES);
   if (rc) return rc;
   GemmTcArgs g{};

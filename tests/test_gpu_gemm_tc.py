@@ -118,7 +118,12 @@ def test_gemm_tc_tf32_all_majors(M, N, K, a_mn, b_mn, tile_n):
     ref = Af @ Bf
     assert torch.isfinite(D).all()
     err = (D.double() - ref).abs().max().item()
-    assert err <= 2e-3 * (K ** 0.5) * 1.0 + 1e-3, (err, ref.abs().max().item())     # tf32: ~1e-3 relative per product
+    # tf32 operands are TRUNCATED to 10 mantissa bits by the tensor core: compare with that model exactly,
+    # and with fp64 loosely
+    t32 = lambda x: (x.contiguous().view(torch.int32) & ~0x1fff).view(torch.float32).double()
+    ref_t = (t32(Av).T if a_mn else t32(Av)) @ (t32(Bv) if b_mn else t32(Bv).T)
+    assert (D.double() - ref_t).abs().max().item() <= 1e-3 * (1 + ref.abs().max().item() * 1e-2)
+    assert err <= 5e-3 * (K ** 0.5) + 1e-3, (err, ref.abs().max().item())
 
 
 def test_dense_layer_ops_tf32_on_reference_shapes():
