@@ -100,12 +100,20 @@ class LayerwiseStepper:
 
     def __init__(self, spec: MLPSpec, batch: int, params: Sequence[torch.Tensor], global_step: torch.Tensor,
                  lr: float, device, atomic: bool = True, grad_buffers: Optional[Sequence[torch.Tensor]] = None,
-                 adam: Optional[dict] = None):
-        """``adam``: {'slots': [...], 'm': [...], 'v': [...], 't': int32 tensor, 'apply': bool, betas/eps} - gradients
+                 adam: Optional[dict] = None, tf32: bool = False):
+        """``tf32``: run the GEMMs whose operands satisfy TMA's 16-byte pitch rule on the tensor cores
+        (tcgen05 kind::tf32, fp32 accumulation, weights pulled by TMA straight from the fp32 shard); the
+        rest - here the 10-wide output layer - stays on the exact fp32 SIMT kernels.
+
+        ``adam``: {'slots': [...], 'm': [...], 'v': [...], 't': int32 tensor, 'apply': bool, betas/eps} - gradients
         are pushed (red.add, unscaled) into the owner-side slots; the rank with ``apply=True`` (the chief)
         then runs the owner-side Adam kernel over every variable, consuming and clearing the slots."""
         self.adam = adam
         self._adam_t = 0
+        self.tf32 = tf32
+        if tf32:
+            from ..ops import gemm_tc
+            self._tc = gemm_tc
         self.spec, self.batch, self.lr, self.atomic = spec, batch, lr, atomic
         self.params = list(params)
         self.global_step = global_step
@@ -134,9 +142,16 @@ class LayerwiseStepper:
             W, b = self.params[2 * l], self.params[2 * l + 1]
             last = l == L - 1
             out = logits if last else acts[l]
-            ops.dense_fwd(h, W, b, ops.ACT_NONE if last else ops.ACT_SIGMOID, out=out, shard_reads=True)
+            if self.tf32 and self._tc_ok(h, W):
+                self._tc.dense_fwd_tc(h, W, b, ops.ACT_NONE if last else ops.ACT_SIGMOID, out)
+            else:
+                ops.dense_fwd(h, W, b, ops.ACT_NONE if last else ops.ACT_SIGMOID, out=out, shard_reads=True)
             h = out
         return logits
+
+    @staticmethod
+    def _tc_ok(*mats) -> bool:
+        return all(m.dim() == 2 and m.stride(1) == 1 and m.stride(0) % 4 == 0 and m.data_ptr() % 16 == 0 for m in mats)
 
     def run(self, X: torch.Tensor, labels: torch.Tensor, train: bool = True) -> None:
         B = X.shape[0]
@@ -152,8 +167,17 @@ class LayerwiseStepper:
             W, b = self.params[2 * l], self.params[2 * l + 1]
             h_in = X if l == 0 else self.acts[l - 1]
             d_prev = None
+            tc = self.tf32 and self._tc_ok(h_in, d, W)
             if l > 0:
-                d_prev = ops.dense_bwd_dx(d, W, h_in, ops.ACT_SIGMOID, out=self.dacts[l - 1], shard_reads=True)
+                if tc:
+                    d_prev = self._tc.dense_bwd_dx_tc(d, W, h_in, self.dacts[l - 1])
+                else:
+                    d_prev = ops.dense_bwd_dx(d, W, h_in, ops.ACT_SIGMOID, out=self.dacts[l - 1], shard_reads=True)
+            if tc and self.adam is None and self.grad_buffers is None and self.atomic:
+                self._tc.dense_bwd_dw_push_tc(h_in, d, W, alpha)
+                ops.bias_grad_push(d, b, alpha, atomic=True)
+                d = d_prev
+                continue
             if self.adam is not None:
                 ops.dense_bwd_dw_push(h_in, d, self.adam["slots"][2 * l], 1.0, atomic=True)
                 ops.bias_grad_push(d, self.adam["slots"][2 * l + 1], 1.0, atomic=True)

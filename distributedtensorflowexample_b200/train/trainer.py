@@ -22,7 +22,7 @@ from .gpu_step import DeviceDataset, FusedMlp2Stepper, LayerwiseStepper, TcStepp
 class GpuTrainer:
     def __init__(self, spec: MLPSpec, batch: int, lr: float, params: Sequence[torch.Tensor],
                  global_step: torch.Tensor, device, steps_per_launch: int = 1, atomic: bool = True,
-                 engine: str = "auto", remote: bool = True):
+                 engine: str = "auto", remote: bool = True, tf32: bool = False):
         self.spec, self.batch, self.lr = spec, batch, lr
         self.device = torch.device(device)
         self.params = list(params)
@@ -38,10 +38,10 @@ class GpuTrainer:
         if engine == "fused":
             self.fused = FusedMlp2Stepper(spec, batch, self.params, global_step, lr, self.device,
                                           max_steps_per_launch=self.steps_per_launch, atomic=atomic, remote=remote)
-            self.layer = LayerwiseStepper(spec, batch, self.params, global_step, lr, self.device, atomic=atomic)
+            self.layer = LayerwiseStepper(spec, batch, self.params, global_step, lr, self.device, atomic=atomic, tf32=tf32)
         elif engine == "layerwise":
             self.fused = None
-            self.layer = LayerwiseStepper(spec, batch, self.params, global_step, lr, self.device, atomic=atomic)
+            self.layer = LayerwiseStepper(spec, batch, self.params, global_step, lr, self.device, atomic=atomic, tf32=tf32)
         elif engine == "tc":
             self.fused = None
             self.layer = TcStepper(spec, batch, self.params, global_step, lr, self.device, stage_all=remote)

@@ -110,7 +110,7 @@ class Worker:
         if f.sync or f.optimizer == "adam":
             from .gpu_step import LayerwiseStepper
             tr = GpuTrainer(self.spec, f.batch_size, f.learning_rate, [store.tensor(n) for n in names],
-                            store.tensor(self.global_step.name), dev, engine="layerwise", remote=True)
+                            store.tensor(self.global_step.name), dev, engine="layerwise", remote=True, tf32=f.tf32)
             kw = {}
             if f.sync:
                 if self.server.num_workers > max(1, f.num_gpus):
@@ -130,13 +130,13 @@ class Worker:
                                   m=[store.tensor(n + "/Adam") for n in names],
                                   v=[store.tensor(n + "/Adam_1") for n in names], apply=self.is_chief)
             tr.layer = LayerwiseStepper(self.spec, f.batch_size, tr.params, tr.global_step, f.learning_rate, dev,
-                                        atomic=not f.unlocked_apply, **kw)
+                                        atomic=not f.unlocked_apply, tf32=f.tf32, **kw)
             self.trainer = tr
         else:
             self.trainer = GpuTrainer(self.spec, f.batch_size, f.learning_rate,
                                       [store.tensor(n) for n in names], store.tensor(self.global_step.name), dev,
-                                      steps_per_launch=f.steps_per_launch,
-                                      atomic=not f.unlocked_apply, remote=True)
+                                      steps_per_launch=f.steps_per_launch, engine=f.engine,
+                                      atomic=not f.unlocked_apply, remote=True, tf32=f.tf32)
         self.engine = None
 
     def build_summary_op(self) -> None:

@@ -194,3 +194,29 @@ def test_layerwise_adam_matches_oracle():
     assert store.read("global/global_step").item() == 4
     assert float(np.abs(store.read(names[0] + "/grad_slot")).max()) == 0.0
     store.close()
+
+
+def test_layerwise_tf32_tensor_core_path():
+    """--tf32: layer 1 of the reference model (fp32 [784,100] kernel in the shard) runs on tcgen05 kind::tf32 with
+    the weights pulled by TMA; the 10-wide output layer stays on the fp32 kernels."""
+    from distributedtensorflowexample_b200.train.gpu_step import LayerwiseStepper
+    spec = reference_mlp_spec()
+    model, store, names = _store(spec, num_ps=1, seed=21)
+    for n in names:                                   # unsaturated sigmoids so that tf32 rounding is visible
+        if store.tensor(n).dim() == 2:
+            store.assign(n, (np.random.default_rng(1).normal(size=store.tensor(n).shape) * 0.05).astype(np.float32))
+    params_np = [store.read(n).astype(np.float64) for n in names]
+    x, y = _data(400)
+    X = torch.tensor(x, device="cuda"); Y = torch.tensor(y, device="cuda")
+    B, lr = 100, 0.5
+    st = LayerwiseStepper(spec, B, [store.tensor(n) for n in names], store.tensor("global/global_step"), lr, "cuda:0",
+                          tf32=True)
+    for s in range(3):
+        rows = slice(s * B, (s + 1) * B)
+        st.run(X[rows], Y[rows])
+        l, a = oracle.sgd_step(params_np, x[rows].astype(np.float64), y[rows], lr)
+        assert abs(st.loss.item() - l) < 5e-3 * max(1.0, l)
+    for n, p in zip(names, params_np):
+        np.testing.assert_allclose(store.read(n), p, rtol=0, atol=3e-3 * (np.abs(p).max() + 1))
+    assert store.read("global/global_step").item() == 3
+    store.close()
