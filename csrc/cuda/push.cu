@@ -146,7 +146,10 @@ __global__ void __launch_bounds__(256) k_sync_rs_apply(SyncArgs a) {
   __shared__ unsigned s_go;
   if (threadIdx.x == 0) {
     unsigned v;
-    while ((v = dtfe::ld_acquire_gpu(a.local_sync)) < a.epoch) { __nanosleep(20); }
+    do {
+      asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(a.local_sync) : "memory");
+    } while (v < a.epoch);
+    __threadfence();
     s_go = v;
   }
   __syncthreads();
@@ -188,16 +191,17 @@ __global__ void __launch_bounds__(256) k_sync_rs_apply(SyncArgs a) {
 
   // (c) depart: once the whole grid has applied, publish and wait until every owner has too,
   // so that on kernel exit all shards hold the new parameters and no gradient buffer is still
-  // being read by a peer.
-  __threadfence_system();
+  // being read by a peer.  One gpu-scope fence per CTA chains the CTAs through the done counter;
+  // only the CTA that arrives last pays the system-scope fence before signalling the peers.
   __syncthreads();
   if (threadIdx.x == 0) {
+    __threadfence();
     unsigned prev = atomicAdd(a.local_sync + 1, 1u);
     if (prev == gridDim.x - 1) {
       a.local_sync[1] = 0;
       a.local_sync[3] = a.epoch;
-      if (a.global_step) dtfe::atom_add_sys_s32(a.global_step, 1);
       __threadfence_system();
+      if (a.global_step) dtfe::atom_add_sys_s32(a.global_step, 1);
       for (int p = 0; p < a.world; ++p)
         dtfe::st_release_sys(a.flags[p] + kMaxRanks + a.rank, a.epoch);
       bool ok = true;
