@@ -62,6 +62,10 @@ struct Mlp2Args {
   long long* dbg;           // optional [nsteps][G][16] globaltimer stamps (profiling)
   float *gW1, *gb1, *gW2, *gb2;  // sync mode: raw gradients are stored here instead of being pushed
   int* cursor;              // optional device-side step cursor: batches start at *cursor (graph replay)
+  // In-kernel synchronous exchange (phase D): reduce-scatter of all ranks' gradient buffers + apply,
+  // with flag barriers in peer memory, once per step.  has_sx = 0: none.
+  int has_sx;
+  dtfe_sync_exchange sx;
 };
 
 __device__ __forceinline__ void grid_barrier(unsigned* ctr, unsigned& target, unsigned G) {
@@ -95,6 +99,20 @@ __device__ __forceinline__ void push1(float* p, float v, int atomic) {
 __device__ __forceinline__ void emit(float* shard, float* gbuf, long i, float g, float nlr, int atomic) {
   if (gbuf) __stcg(gbuf + i, g);
   else push1(shard + i, nlr * g, atomic);
+}
+
+// Wait for a peer's flag; gives up (returns false) when the stop word is raised or the timeout expires, so a
+// rank that left can never hang this GPU.
+__device__ __forceinline__ bool sx_wait(const unsigned* flag, unsigned epoch, const dtfe_sync_exchange& sx,
+                                        long long t0) {
+  unsigned it = 0;
+  while (dtfe::ld_acquire_sys(flag) < epoch) {
+    if ((++it & 0xff) == 0) {
+      if (sx.abort_flag && dtfe::ld_acquire_sys(sx.abort_flag) != 0) return false;
+      if (sx.timeout_ns && (unsigned long long)(gtime() - t0) > sx.timeout_ns) return false;
+    }
+  }
+  return true;
 }
 
 template <int KS>
@@ -181,6 +199,10 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
   };
   fetch_w1();
   int pending_step = 0;                                 // CTA 0 / thread 0: global step observed for the previous step
+  const unsigned sx_epoch0 = a.has_sx ? *reinterpret_cast<volatile unsigned*>(a.sx.epoch) : 0u;
+  const unsigned long long sx_t0 = gtime();
+  __shared__ unsigned s_go;
+  int steps_done = 0;
   auto fetch_label_row = [&](int st) {
     int r = 2 * g + slot;
     if (r < B && st < a.nsteps)
@@ -247,7 +269,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
     // Every CTA has passed barrier 1, so every push of step s-1 has been issued and fenced: count that update
     // now.  The atomic's result (the global step the previous step observed, what the reference fetches next
     // to train_op) is not consumed until the end of phase B, so its round trip costs nothing.
-    if (g == 0 && tid == 0 && s > 0 && a.train)
+    if (g == 0 && tid == 0 && s > 0 && a.train && !a.has_sx)
       pending_step = a.gW1 ? *reinterpret_cast<volatile int*>(a.global_step) : dtfe::atom_add_sys_s32(a.global_step, 1);
     // Small parameters are read after the barrier so that every CTA sees the pushes all CTAs made in
     // the previous step's phase C.  They go to registers first; the reduction loads below are issued
@@ -388,7 +410,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
       }
       __syncthreads();
     }
-    if (g == 0 && tid == 0 && s > 0 && a.train) a.step_out[s - 1] = pending_step;
+    if (g == 0 && tid == 0 && s > 0 && a.train && !a.has_sx) a.step_out[s - 1] = pending_step;
     DBG_STAMP(3);
     grid_barrier(a.sync, bar_target, G);
     DBG_STAMP(4);
@@ -469,7 +491,8 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
         }
       }
       // pull for the next step: the same thread reads back exactly the elements it just pushed
-      fetch_w1();
+      // (synchronous mode: the parameters only change in phase D, the read-back happens there)
+      if (!a.has_sx) fetch_w1();
       DBG_STAMP(13);
       // small gradients, one or two classes per warp
       for (int tt = t0, rnd = 0; tt < H; tt += (int)G, ++rnd) {
@@ -509,6 +532,80 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
       // of this step's pushes before the global_step increment that counts them.
       __syncthreads();                            // dAs / Xs are rewritten by the next step
       DBG_STAMP(7);
+      if (a.has_sx) {
+        // ------------------------------ phase D (synchronous mode) -------------------------------
+        // D1: every CTA's gradients are in this rank's exchange buffer
+        grid_barrier(a.sync, bar_target, G);
+        const unsigned epoch = sx_epoch0 + (unsigned)s + 1u;
+        const unsigned kAbort = 0xffffffffu;
+        // D2: tell every peer, wait for every peer (CTA 0), then release the grid
+        if (g == 0 && tid == 0) {
+          __threadfence_system();
+          for (int p = 0; p < a.sx.world; ++p) dtfe::st_release_sys(a.sx.flags[p] + a.sx.rank, epoch);
+          bool ok = true;
+          for (int q = 0; q < a.sx.world && ok; ++q) ok = sx_wait(a.sx.flags[a.sx.rank] + q, epoch, a.sx, sx_t0);
+          asm volatile("st.release.gpu.global.u32 [%0], %1;" :: "l"(a.sync + 2), "r"(ok ? epoch : kAbort) : "memory");
+        }
+        if (tid == 0) {
+          unsigned v;
+          do { asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(a.sync + 2) : "memory"); } while (v < epoch);
+          __threadfence();
+          s_go = v;
+        }
+        __syncthreads();
+        const bool aborted = s_go == kAbort;
+        // D3: reduce the slices of the variables this rank owns out of all ranks' buffers and apply in place
+        if (!aborted) {
+          const size_t gtid = (size_t)g * kThreads + tid, gstride = (size_t)G * kThreads;
+          for (int sg = 0; sg < a.sx.nseg; ++sg) {
+            const size_t begin = a.sx.seg_begin[sg], n = a.sx.seg_end[sg] - begin;
+            float* param = a.sx.seg_param[sg];
+            const bool vec_ok = (begin % 4 == 0) && ((reinterpret_cast<uintptr_t>(param) & 15) == 0);
+            const size_t nv = vec_ok ? n / 4 : 0;
+            for (size_t v = gtid; v < nv; v += gstride) {
+              float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+              for (int q = 0; q < a.sx.world; ++q) {
+                float4 gq = dtfe::ld_relaxed_sys_v4(a.sx.grads[q] + begin + v * 4);
+                acc.x += gq.x; acc.y += gq.y; acc.z += gq.z; acc.w += gq.w;
+              }
+              float4 w = dtfe::ld_relaxed_sys_v4(param + v * 4);
+              w.x += a.sx.alpha * acc.x; w.y += a.sx.alpha * acc.y; w.z += a.sx.alpha * acc.z; w.w += a.sx.alpha * acc.w;
+              *reinterpret_cast<float4*>(param + v * 4) = w;
+            }
+            for (size_t e = nv * 4 + gtid; e < n; e += gstride) {
+              float acc = 0.f;
+              for (int q = 0; q < a.sx.world; ++q) acc += dtfe::ld_relaxed_sys(a.sx.grads[q] + begin + e);
+              param[e] = dtfe::ld_relaxed_sys(param + e) + a.sx.alpha * acc;
+            }
+          }
+        }
+        // D4: all of this rank's applies are done; wait until every rank's are (nobody may read a stale
+        // parameter or overwrite a gradient buffer that a peer is still reducing)
+        grid_barrier(a.sync, bar_target, G);
+        if (g == 0 && tid == 0) {
+          bool ok = !aborted;
+          if (ok) {
+            __threadfence_system();
+            if (a.sx.global_step) dtfe::atom_add_sys_s32(a.sx.global_step, 1);
+            for (int p = 0; p < a.sx.world; ++p) dtfe::st_release_sys(a.sx.flags[p] + 16 + a.sx.rank, epoch);
+            for (int q = 0; q < a.sx.world && ok; ++q) ok = sx_wait(a.sx.flags[a.sx.rank] + 16 + q, epoch, a.sx, sx_t0);
+            if (ok) a.step_out[s] = (int)dtfe::ld_acquire_sys(reinterpret_cast<const unsigned*>(a.global_step)) - 1;
+          }
+          if (!ok) a.sx.status[0] = aborted ? 1u : 2u;
+          asm volatile("st.release.gpu.global.u32 [%0], %1;" :: "l"(a.sync + 3), "r"(ok ? epoch : kAbort) : "memory");
+        }
+        if (tid == 0) {
+          unsigned v;
+          do { asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(a.sync + 3) : "memory"); } while (v < epoch);
+          __threadfence();
+          s_go = v;
+        }
+        __syncthreads();
+        if (s_go == kAbort) break;                // a rank left: stop after this step, on every CTA alike
+        ++steps_done;
+        fetch_w1();                               // the pull of the next step sees every owner's update
+        __syncthreads();
+      }
     } else {
       fetch_w1();
       if (g == 0 && tid == 0) a.step_out[s] = *reinterpret_cast<volatile int*>(a.global_step);
@@ -524,7 +621,9 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
     unsigned prev = atomicAdd(a.sync + 1, 1u);
     if (prev == G - 1) {
       a.sync[0] = 0; a.sync[1] = 0;
-      if (a.train && a.nsteps > 0) {
+      if (a.has_sx) {
+        *a.sx.epoch = sx_epoch0 + (unsigned)steps_done;
+      } else if (a.train && a.nsteps > 0) {
         if (a.remote) __threadfence_system();
         int old = a.gW1 ? *reinterpret_cast<volatile int*>(a.global_step) : dtfe::atom_add_sys_s32(a.global_step, 1);
         a.step_out[a.nsteps - 1] = old;
@@ -580,6 +679,14 @@ static int mlp2_fill(const Mlp2Launch& L, Mlp2Args& a) {
   a.loss_out = L.loss_out; a.acc_out = L.acc_out; a.step_out = L.step_out;
   a.lr = L.lr; a.nsteps = L.nsteps; a.atomic = L.atomic; a.train = L.train; a.remote = L.remote; a.dbg = L.dbg;
   a.gW1 = L.gW1; a.gb1 = L.gb1; a.gW2 = L.gW2; a.gb2 = L.gb2; a.cursor = L.cursor;
+  a.has_sx = 0;
+  if (L.sync_exchange) {
+    a.sx = *L.sync_exchange;
+    a.has_sx = 1;
+    DTFE_REQUIRE(a.gW1 != nullptr, "mlp2_step: sync_exchange needs the four gradient buffers (they are what is exchanged)");
+    DTFE_REQUIRE(a.sx.world >= 1 && a.sx.world <= 16 && a.sx.nseg >= 0 && a.sx.nseg <= 8 && a.sx.epoch && a.sx.status,
+                 "mlp2_step: malformed sync_exchange");
+  }
   DTFE_REQUIRE((a.gW1 != nullptr) == (a.gb1 != nullptr) && (a.gW1 != nullptr) == (a.gW2 != nullptr) &&
                (a.gW1 != nullptr) == (a.gb2 != nullptr), "mlp2_step: pass all four gradient buffers or none");
   return 0;

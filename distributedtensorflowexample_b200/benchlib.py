@@ -127,47 +127,38 @@ def run_mnist(args, rank: int, world: int, dev, ClockSampler) -> int:
 
 
 def _run_mnist_sync(args, rank, world, dev, ClockSampler, spec, model, store, names, ds, x, y, B, lr, K, W) -> int:
-    """Synchronous SGD: layer-wise kernels write gradients to a peer-visible buffer, then ONE kernel per
-    rank does barrier + reduce-scatter + apply + barrier over peer memory (parallel/sync.py)."""
+    """Synchronous SGD: the fused step kernel writes its gradients to this rank's peer-visible exchange buffer
+    and, as its last phase, runs barrier + reduce-scatter + apply + barrier over peer memory - every step,
+    any number of steps per launch (parallel/sync.py, mlp2_step.cu phase D)."""
     from .parallel.sync import SyncGroup
     from .train.gpu_step import FusedMlp2Stepper
     sg = SyncGroup(store, names, rank, world)
     shapes = {n: tuple(store.tensor(n).shape) for n in names}
+    spl = args.steps_per_launch or min(K, 500)
     st = FusedMlp2Stepper(spec, B, [store.tensor(n) for n in names], store.tensor("global/global_step"), lr, dev,
-                          remote=not store.all_local(), grad_buffers=sg.grad_views(shapes))
-    idx = ds.next_indices(B, K + W + 8)
-    st.cursor = torch.zeros(1, dtype=torch.int32, device=dev)
+                          max_steps_per_launch=spl, remote=not store.all_local(), grad_buffers=sg.grad_views(shapes))
+    idx = ds.next_indices(B, K + W)
+    st.sync_exchange = sg.exchange_struct(lr)       # phase D of the step kernel: exchange + apply, every step
 
-    def one_step():
-        st.run(ds.images, ds.labels, nsteps=1, batch_idx=idx)   # fwd/bwd in one kernel, gradients -> exchange buffer
-        sg.reduce_scatter_apply(lr)                             # barrier + reduce-scatter + apply + barrier
+    def run_steps(first, n):
+        done = 0
+        while done < n:
+            m = min(spl, n - done)
+            st.run(ds.images, ds.labels, nsteps=m, batch_idx=idx[(first + done) * B:(first + done + m) * B])
+            done += m
+        return (n + spl - 1) // spl
 
-    # Both launches are captured once and replayed: per-step host work is one cudaGraphLaunch, so a slow
-    # host on one rank cannot stall the others' GPUs at the exchange.
-    side = torch.cuda.Stream(device=dev)
-    with torch.cuda.stream(side):
-        one_step()
-    torch.cuda.current_stream().wait_stream(side)
-    _barrier(world)
-    graph = torch.cuda.CUDAGraph()
-    with torch.cuda.graph(graph):
-        one_step()
-
-    def step(i):
-        graph.replay()
-
-    for i in range(W):
-        step(i)
+    run_steps(0, W)
     _barrier(world)
     clocks = ClockSampler(dev.index or 0)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     clocks.start()
     e0.record()
-    for i in range(K):
-        step(W + i)
+    launches = run_steps(W, K)
     e1.record()
     torch.cuda.synchronize()
     clk = clocks.stop()
+    assert sg.aborted() == 0, "a rank abandoned the exchange"
     ms = _max_over_ranks(e0.elapsed_time(e1), world, dev)
     _barrier(world)
     out = {"metric": METRIC, "value": world * B * K / (ms * 1e-3), "unit": "examples/sec", "n_gpus": world,
@@ -175,8 +166,8 @@ def _run_mnist_sync(args, rank, world, dev, ClockSampler, spec, model, store, na
            "vs_baseline": None, "dtype": "fp32", "data": "synthetic", "impl": "ours",
            "config": {"model": "MNIST MLP 784-100-10", "global_batch": B * world, "batch_per_worker": B,
                       "parallelism": f"sync-ps dp{world}: reduce-scatter fused with apply over peer memory",
-                      "engine": "fused step kernel (gradients to the exchange buffer) + sync_rs_apply"},
-           "gpu_launches": 2 * K, "cuda_graph": True, "clocks": clk,
+                      "engine": "fused step kernel with the exchange (barrier, reduce-scatter, apply, barrier) as its phase D", "steps_per_launch": spl},
+           "gpu_launches": launches, "clocks": clk,
            "global_step_after": int(store.tensor("global/global_step").item())}
     if rank == 0:
         print(json.dumps(out), flush=True)

@@ -295,6 +295,20 @@ def sync_rs_apply(grad_ptrs: Sequence[int], flag_ptrs: Sequence[int], rank: int,
 # --------------------------------------------------------------------------------------
 # fused 2-layer-MLP step (the reference model's whole step in one cooperative kernel)
 # --------------------------------------------------------------------------------------
+class SyncExchange(ctypes.Structure):
+    """ctypes mirror of ``dtfe_sync_exchange`` (include/dtfe_b200.h)."""
+    _fields_ = [
+        ("grads", _P * 16), ("flags", _P * 16),
+        ("rank", c_int), ("world", c_int),
+        ("nseg", c_int),
+        ("seg_param", _P * 8), ("seg_begin", c_size_t * 8), ("seg_end", c_size_t * 8),
+        ("alpha", c_float),
+        ("epoch", _P), ("status", _P), ("abort_flag", _P),
+        ("timeout_ns", ctypes.c_ulonglong),
+        ("global_step", _P),
+    ]
+
+
 class _Mlp2Launch(ctypes.Structure):
     _fields_ = [
         ("B", c_int), ("D", c_int), ("H", c_int), ("C", c_int), ("ks", c_int),
@@ -310,6 +324,7 @@ class _Mlp2Launch(ctypes.Structure):
         ("dbg", _P),
         ("gW1", _P), ("gb1", _P), ("gW2", _P), ("gb2", _P),
         ("cursor", _P),
+        ("sync_exchange", _P),
     ]
 
 
@@ -373,7 +388,7 @@ class Mlp2Step:
 
     def run(self, W1, b1, W2, b2, global_step, X, labels, lr: float, nsteps: int = 1, batch_idx=None,
             rows_per_step: int = 0, atomic: bool = True, train: bool = True, out_offset: int = 0,
-            remote: bool = True, dbg=None, grads=None, cursor=None):
+            remote: bool = True, dbg=None, grads=None, cursor=None, sync_exchange=None):
         assert nsteps + out_offset <= self.max_steps
         L = _Mlp2Launch()
         L.B, L.D, L.H, L.C, L.ks = self.B, self.D, self.H, self.C, self.ks
@@ -393,4 +408,6 @@ class Mlp2Step:
         if grads is not None:
             L.gW1, L.gb1, L.gW2, L.gb2 = (g.data_ptr() for g in grads)
         L.cursor = _ptr(cursor)
+        if sync_exchange is not None:
+            L.sync_exchange = ctypes.addressof(sync_exchange)
         check(lib().dtfe_mlp2_step(ctypes.byref(L), _stream()), "dtfe_mlp2_step")

@@ -94,6 +94,25 @@ class SyncGroup:
                           -lr / self.world, 0 if device_epoch else self.epoch, self.local_sync, self.global_step,
                           abort_flag_ptr=self._abort_ptr, timeout_s=self.timeout_s)
 
+    def exchange_struct(self, lr: float):
+        """Arguments for the exchange run INSIDE the fused step kernel (``dtfe_mlp2_launch.sync_exchange``): same
+        buffers, flags and epoch counter as ``reduce_scatter_apply``, so the two forms can be mixed."""
+        x = ops.SyncExchange()
+        for r in range(self.world):
+            x.grads[r] = self.grad_ptrs[r]
+            x.flags[r] = self.flag_ptrs[r]
+        x.rank, x.world, x.nseg = self.rank, self.world, len(self.segments)
+        for i, (t, b, e) in enumerate(self.segments):
+            x.seg_param[i], x.seg_begin[i], x.seg_end[i] = t.data_ptr(), b, e
+        x.alpha = -lr / self.world
+        x.epoch = self.local_sync.data_ptr() + 12          # local_sync[3]
+        x.status = self.local_sync.data_ptr() + 8          # local_sync[2]
+        x.abort_flag = self._abort_ptr
+        x.timeout_ns = int(self.timeout_s * 1e9)
+        x.global_step = self.global_step.data_ptr() if self.global_step is not None else None
+        self._xs = x                                       # keep the ctypes object alive
+        return x
+
     def aborted(self) -> int:
         """0 if the last reduce_scatter_apply completed, else which barrier gave up (needs a sync)."""
         return int(self.local_sync[2].item())

@@ -61,6 +61,7 @@ class FusedMlp2Stepper:
         buffer) instead of being pushed; ``parallel.sync.SyncGroup.reduce_scatter_apply`` finishes the step."""
         self.grad_buffers = list(grad_buffers) if grad_buffers is not None else None
         self.cursor = None
+        self.sync_exchange = None     # parallel.sync.SyncGroup.exchange_struct(lr): exchange inside the kernel
         if spec.num_layers != 2 or spec.param_dtype != "float32":
             raise ValueError("FusedMlp2Stepper handles 2-layer float32 models")
         D, H, C = spec.dims
@@ -83,7 +84,7 @@ class FusedMlp2Stepper:
         self.k.run(self.W1, self.b1, self.W2, self.b2, self.global_step, X, labels, self.lr, nsteps=nsteps,
                    batch_idx=batch_idx, rows_per_step=rows_per_step, atomic=self.atomic, train=train,
                    out_offset=out_offset, remote=self.remote, dbg=self.dbg, grads=self.grad_buffers,
-                   cursor=self.cursor)
+                   cursor=self.cursor, sync_exchange=self.sync_exchange)
 
     @property
     def loss(self): return self.k.loss

@@ -108,6 +108,25 @@ int dtfe_sync_max_ranks(void);
 int dtfe_gather_rows_f32(const float* X, long ldx, const int* labels, const int* idx, const int* cursor, int B,
                          int D, float* Xout, int* Yout, void* stream);
 
+/* Arguments of the in-kernel synchronous exchange (phase D of dtfe_mlp2_step): same protocol and same
+ * buffers as dtfe_sync_rs_apply_f32 (exchange buffers + flag arrays from dtfe_shard_alloc, opened by all
+ * ranks), but run at the end of every step inside the step kernel, so a launch can cover many synchronous
+ * steps.  One rank per GPU. */
+typedef struct dtfe_sync_exchange {
+  const float* grads[16];     /* every rank's gradient buffer (this rank's own one is where the step writes) */
+  unsigned* flags[16];        /* every rank's flag array, 32 u32: [0..15] arrive, [16..31] depart */
+  int rank, world;
+  int nseg;                   /* variables this rank owns: flat-gradient range and parameter base */
+  float* seg_param[8];
+  size_t seg_begin[8], seg_end[8];
+  float alpha;                /* -lr / world */
+  unsigned* epoch;            /* device word: number of completed exchanges (shared with dtfe_sync_rs_apply_f32's local_sync[3]) */
+  unsigned* status;           /* device word: set non-zero when a wait was abandoned (1 arrive, 2 depart) */
+  const unsigned* abort_flag; /* optional peer-visible stop word */
+  unsigned long long timeout_ns;
+  int* global_step;           /* non-NULL on the rank that owns global_step */
+} dtfe_sync_exchange;
+
 /* ---- the whole reference training step in one cooperative kernel ------------------------------- */
 /* pull -> fwd -> xent/accuracy -> bwd -> push+apply -> global_step for nsteps consecutive steps
  * (reference worker.py:129-141, model worker.py:46-57).  Limits: B<=128, H<=128, C<=16, D/ks<=148. */
@@ -127,6 +146,7 @@ typedef struct dtfe_mlp2_launch {
                                          no global_step increment (dtfe_sync_rs_apply_f32 does both) */
   int* cursor;                        /* NULL, or device int: batches start at batch_idx[*cursor * B]; advanced by
                                          nsteps at kernel end (lets a captured graph walk through the data) */
+  const dtfe_sync_exchange* sync_exchange;  /* NULL, or: synchronous SGD with the exchange inside the kernel */
 } dtfe_mlp2_launch;
 int dtfe_mlp2_step_grid(int D, int ks);
 size_t dtfe_mlp2_step_workspace_words(int B, int D, int H, int C, int ks);

@@ -66,6 +66,22 @@ def main():
         np.testing.assert_allclose(store.read(n), r, rtol=1e-3, atol=3e-4, err_msg=f"sync fused {n}")
     assert store.read("global/global_step").item() == 2 * nsteps and fs.cursor.item() == 2 * nsteps
     dist.barrier()
+    # and with the exchange INSIDE the step kernel (phase D), several synchronous steps in one launch
+    fx = FusedMlp2Stepper(spec, B, [store.tensor(n) for n in names], store.tensor("global/global_step"), lr, dev,
+                          max_steps_per_launch=nsteps, remote=True, grad_buffers=sg.grad_views(shapes))
+    fx.sync_exchange = sg.exchange_struct(lr)
+    fx.cursor = torch.full((1,), 2 * nsteps, dtype=torch.int32, device=dev)
+    fx.run(X, Y, nsteps=nsteps, batch_idx=order)
+    torch.cuda.synchronize(); dist.barrier()
+    assert sg.aborted() == 0
+    for s in range(2 * nsteps, 3 * nsteps):
+        rows = slice(s * world * B, (s + 1) * world * B)
+        oracle.sgd_step(ref, x[rows].astype(np.float64), y[rows].astype(np.int64), lr)
+    for n, r in zip(names, ref):
+        np.testing.assert_allclose(store.read(n), r, rtol=1e-3, atol=4e-4, err_msg=f"sync in-kernel {n}")
+    assert store.read("global/global_step").item() == 3 * nsteps
+    assert fx.step[:nsteps].cpu().tolist() == list(range(2 * nsteps, 3 * nsteps))
+    dist.barrier()
     sg.close(); store.close()
 
     # ---------------- async: conservation of pushed deltas with exact arithmetic ---------------

@@ -220,3 +220,40 @@ def test_layerwise_tf32_tensor_core_path():
         np.testing.assert_allclose(store.read(n), p, rtol=0, atol=3e-3 * (np.abs(p).max() + 1))
     assert store.read("global/global_step").item() == 3
     store.close()
+
+
+def test_fused_step_with_in_kernel_sync_exchange_single_rank():
+    """Synchronous mode with the exchange as phase D of the step kernel (world = 1: the protocol still runs -
+    flags, epochs, reduce of the single buffer, apply): must equal plain SGD, several steps per launch."""
+    from distributedtensorflowexample_b200.parallel.sync import SyncGroup
+    from distributedtensorflowexample_b200.train.gpu_step import FusedMlp2Stepper
+    spec = reference_mlp_spec()
+    model, store, names = _store(spec, num_ps=2, seed=13)
+    params_np = [store.read(n).astype(np.float64) for n in names]
+    x, y = _data(1000)
+    X = torch.tensor(x, device="cuda"); Y = torch.tensor(y, device="cuda")
+    B, lr, nsteps = 100, 0.05, 5
+    sg = SyncGroup(store, names, 0, 1, timeout_s=5.0)
+    shapes = {n: tuple(store.tensor(n).shape) for n in names}
+    st = FusedMlp2Stepper(spec, B, [store.tensor(n) for n in names], store.tensor("global/global_step"), lr, "cuda:0",
+                          max_steps_per_launch=nsteps, grad_buffers=sg.grad_views(shapes))
+    st.sync_exchange = sg.exchange_struct(lr)
+    idx = torch.arange(nsteps * B, device="cuda", dtype=torch.int32)
+    st.run(X, Y, nsteps=nsteps, batch_idx=idx)
+    torch.cuda.synchronize()
+    assert sg.aborted() == 0
+    for s in range(nsteps):
+        rows = slice(s * B, (s + 1) * B)
+        oracle.sgd_step(params_np, x[rows].astype(np.float64), y[rows], lr)
+    for n, p in zip(names, params_np):
+        np.testing.assert_allclose(store.read(n), p, rtol=1e-3, atol=2e-4)
+    assert store.read("global/global_step").item() == nsteps
+    assert st.step[:nsteps].cpu().tolist() == list(range(nsteps))
+    # the separate exchange kernel continues the same epoch sequence
+    st2 = FusedMlp2Stepper(spec, B, [store.tensor(n) for n in names], store.tensor("global/global_step"), lr, "cuda:0",
+                           grad_buffers=sg.grad_views(shapes))
+    st2.run(X, Y, nsteps=1, batch_idx=idx[:B])
+    sg.reduce_scatter_apply(lr)
+    torch.cuda.synchronize()
+    assert store.read("global/global_step").item() == nsteps + 1 and sg.aborted() == 0
+    sg.close(); store.close()
