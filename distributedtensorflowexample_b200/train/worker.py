@@ -107,10 +107,9 @@ class Worker:
         names = [v.name for v in self.model.global_trainable]
         f = self.flags
         self.sync_group = None
+        self._sync_in_kernel = False
         if f.sync or f.optimizer == "adam":
-            from .gpu_step import LayerwiseStepper
-            tr = GpuTrainer(self.spec, f.batch_size, f.learning_rate, [store.tensor(n) for n in names],
-                            store.tensor(self.global_step.name), dev, engine="layerwise", remote=True, tf32=f.tf32)
+            from .gpu_step import FusedMlp2Stepper, LayerwiseStepper
             kw = {}
             if f.sync:
                 if self.server.num_workers > max(1, f.num_gpus):
@@ -129,8 +128,20 @@ class Worker:
                 kw["adam"] = dict(slots=[store.tensor(n + "/grad_slot") for n in names],
                                   m=[store.tensor(n + "/Adam") for n in names],
                                   v=[store.tensor(n + "/Adam_1") for n in names], apply=self.is_chief)
-            tr.layer = LayerwiseStepper(self.spec, f.batch_size, tr.params, tr.global_step, f.learning_rate, dev,
-                                        atomic=not f.unlocked_apply, tf32=f.tf32, **kw)
+            fused_ok = (f.sync and f.optimizer == "sgd" and f.engine in ("auto", "fused")
+                        and FusedMlp2Stepper.supports(self.spec, f.batch_size))
+            tr = GpuTrainer(self.spec, f.batch_size, f.learning_rate, [store.tensor(n) for n in names],
+                            store.tensor(self.global_step.name), dev, engine="fused" if fused_ok else "layerwise",
+                            steps_per_launch=f.steps_per_launch if fused_ok else 1, remote=True, tf32=f.tf32)
+            if fused_ok:
+                # the whole synchronous step - exchange included - is one kernel (mlp2_step.cu phase D)
+                tr.fused = FusedMlp2Stepper(self.spec, f.batch_size, tr.params, tr.global_step, f.learning_rate, dev,
+                                            max_steps_per_launch=max(1, f.steps_per_launch), remote=True, **kw)
+                tr.fused.sync_exchange = self.sync_group.exchange_struct(f.learning_rate)
+                self._sync_in_kernel = True
+            else:
+                tr.layer = LayerwiseStepper(self.spec, f.batch_size, tr.params, tr.global_step, f.learning_rate, dev,
+                                            atomic=not f.unlocked_apply, tf32=f.tf32, **kw)
             self.trainer = tr
         else:
             self.trainer = GpuTrainer(self.spec, f.batch_size, f.learning_rate,
@@ -231,16 +242,17 @@ class Worker:
         test_x = torch.as_tensor(dataset.test.images, dtype=torch.float32).to(dev)
         test_y = torch.as_tensor(dataset.test.label_ids, dtype=torch.int32).to(dev)
         eval_fn = lambda: tr.evaluate(test_x, test_y)
-        n = 1 if self.sync_group is not None else max(1, f.steps_per_launch)   # sync: one update per exchange
+        separate_exchange = self.sync_group is not None and not self._sync_in_kernel
+        n = 1 if separate_exchange else max(1, f.steps_per_launch)
         step = 0
         while not sv.should_stop():
             loss_d, acc_d, step_d = tr.train_device_steps(train, n)
-            if self.sync_group is not None:
+            if separate_exchange:
                 self.sync_group.reduce_scatter_apply(f.learning_rate)
                 step_d = self.store.tensor(self.global_step.name)[:1] - 1      # the aggregated update just applied
-                if self.sync_group.aborted():
-                    print("sync: a peer left, stopping", flush=True)
-                    break
+            if self.sync_group is not None and self.sync_group.aborted():
+                print("sync: a peer left, stopping", flush=True)
+                break
             loss, acc, steps = loss_d.tolist(), acc_d.tolist(), step_d.tolist()   # one sync per launch
             stop = False
             for l, a, s in zip(loss, acc, steps):
