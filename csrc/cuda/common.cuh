@@ -96,6 +96,35 @@ __device__ __forceinline__ int atom_add_sys_s32(int* p, int v) {
   asm volatile("atom.acq_rel.sys.global.add.s32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(v) : "memory");
   return old;
 }
+// Same counter bump without the acquire half: later loads of the issuing thread do not wait for the
+// atomic's round trip (over NVLink that is microseconds); the result is scoreboarded until first use.
+__device__ __forceinline__ int atom_add_release_sys_s32(int* p, int v) {
+  int old;
+  asm volatile("atom.release.sys.global.add.s32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(v) : "memory");
+  return old;
+}
+__device__ __forceinline__ int atom_add_relaxed_sys_s32(int* p, int v) {
+  int old;
+  asm volatile("atom.relaxed.sys.global.add.s32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(v) : "memory");
+  return old;
+}
+// 16-byte asynchronous global->shared copy that bypasses L1 (.cg).  No register (and no scoreboard
+// slot) holds the data in flight, so a slow source (a peer GPU) cannot delay unrelated waits of the
+// issuing warp.  Only `src_bytes` (<= 16) are read, the rest of the 16 bytes is zero-filled.
+__device__ __forceinline__ void cp_async_cg16(void* smem_dst, const void* gsrc, int src_bytes = 16) {
+  unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" :: "r"(d), "l"(gsrc), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" :: "n"(N) : "memory"); }
+// Whole-CTA copy of n floats (both sides 16-byte aligned; the tail quad is read partially, never past n).
+__device__ __forceinline__ void cta_copy_async(float* smem_dst, const float* gsrc, int n, int tid, int nthreads) {
+  for (int f = tid; 4 * f < n; f += nthreads) {
+    int rem = n - 4 * f;
+    cp_async_cg16(smem_dst + 4 * f, gsrc + 4 * f, rem >= 4 ? 16 : 4 * rem);
+  }
+}
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&v);

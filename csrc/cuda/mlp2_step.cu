@@ -13,19 +13,27 @@
 //            HBM: this is the pull) and the matching KS columns of the batch, and
 //            writes a split-K partial of X.W1 to scratch.
 //   barrier
-//   phase B  two batch rows per CTA: reduce the partials, +b1, sigmoid, logits with
-//            W2/b2 read from the shard, softmax cross-entropy fwd+bwd, accuracy,
+//   phase B  one batch row per CTA (the grid has max(slices, B+1) CTAs; the ones beyond the
+//            slices only work here and on the small gradients): reduce the partials, +b1,
+//            sigmoid, logits with W2/b2, softmax cross-entropy fwd+bwd, accuracy,
 //            dA = (dZ.W2^T) * h(1-h).
 //   barrier
 //   phase C  each CTA computes dW1 for the SAME KS rows it pulled (X slice is still in
 //            shared memory) and pushes -lr*dW1 into the shard with red.add.sys: the
 //            push is the apply, there is no ps-side kernel.  dW2/db1/db2 rows are
-//            spread over CTAs the same way.  The last CTA to finish bumps global_step
-//            with a system-scope atomic and records the pre-increment value
-//            (the `step` the reference fetches).
+//            spread over all CTAs.  The last CTA of the grid (which owns no batch row when
+//            the grid is B+1 wide) keeps the books: metrics, db2, and the system-scope
+//            global_step atomic whose pre-increment value is the `step` the reference fetches.
+//
+// The pull runs one step ahead ("ahead" mode, asynchronous training): a thread reads its W1
+// elements BEFORE it pushes to them and adds its own update in registers; the small parameters
+// are fetched (cp.async / registers) during phase B for the NEXT step and completed there with
+// this worker's own deltas from a local buffer.  Own updates are therefore seen exactly (bitwise
+// what the shard holds when no other worker interferes), other workers' updates one step later,
+// and no load from a peer GPU is ever waited for on the critical path.
 //
 // Scratch (global memory beyond inputs/outputs): the split-K partials, H, dA, dZ,
-// per-row loss/correct flags and three sync words.
+// per-row loss/correct flags, the small-parameter deltas and four sync words.
 #include "common.cuh"
 #include <math.h>
 #include <stdlib.h>
@@ -50,7 +58,8 @@ struct Mlp2Args {
   float* dZ;                // [B][C]
   float* rowloss;           // [B]
   int* rowcorrect;          // [B]
-  unsigned* sync;           // [4]: grid barrier, exit count, done count, -
+  float* delta;             // [H*C + H + C] this worker's last small-parameter updates (ahead mode)
+  unsigned* sync;           // [4]: grid barrier, exit count, phase-D go words
   float* loss_out;          // [nsteps]
   float* acc_out;           // [nsteps]
   int* step_out;            // [nsteps]
@@ -58,8 +67,10 @@ struct Mlp2Args {
   int nsteps;
   int atomic;
   int train;                // 0: forward/metrics only (no phase C)
+  int nslices;              // G: CTAs that own a KS-row slice of W1 (the grid may be wider)
+  int ahead;                // pull one step ahead + own deltas (see the file header)
   int remote;               // some shard lives on a peer GPU: completion fence must be .sys
-  long long* dbg;           // optional [nsteps][G][16] globaltimer stamps (profiling)
+  long long* dbg;           // optional [nsteps][grid][16] globaltimer stamps (profiling)
   float *gW1, *gb1, *gW2, *gb2;  // sync mode: raw gradients are stored here instead of being pushed
   int* cursor;              // optional device-side step cursor: batches start at *cursor (graph replay)
   // In-kernel synchronous exchange (phase D): reduce-scatter of all ranks' gradient buffers + apply,
@@ -88,7 +99,7 @@ __device__ __forceinline__ long long gtime() {
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
   return t;
 }
-#define DBG_STAMP(i) do { if (a.dbg && tid == 0) a.dbg[((long)s * G + g) * 16 + (i)] = gtime(); } while (0)
+#define DBG_STAMP(i) do { if (a.dbg && tid == 0) a.dbg[((long)s * NC + g) * 16 + (i)] = gtime(); } while (0)
 
 __device__ __forceinline__ void push1(float* p, float v, int atomic) {
   if (atomic) dtfe::red_add_sys(p, v);
@@ -98,7 +109,13 @@ __device__ __forceinline__ void push1(float* p, float v, int atomic) {
 // rank's exchange buffer for the reduce-scatter kernel.
 __device__ __forceinline__ void emit(float* shard, float* gbuf, long i, float g, float nlr, int atomic) {
   if (gbuf) __stcg(gbuf + i, g);
-  else push1(shard + i, nlr * g, atomic);
+  else push1(shard + i, __fmul_rn(nlr, g), atomic);
+}
+// Small parameters in ahead mode: the update also goes to the local delta buffer every CTA reads next step.
+__device__ __forceinline__ void emit_small(float* shard, float* gbuf, float* delta, long i, float g, float nlr,
+                                           int atomic) {
+  if (delta) __stcg(delta + i, __fmul_rn(nlr, g));
+  emit(shard, gbuf, i, g, nlr, atomic);
 }
 
 // Wait for a peer's flag; gives up (returns false) when the stop word is raised or the timeout expires, so a
@@ -126,18 +143,25 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
   float* W2s = Ws + KS * kMaxH;           // [H][C]
   float* b1s = W2s + kMaxH * kMaxC;       // [H]
   float* b2s = b1s + kMaxH;               // [C]
-  float* hs = b2s + kMaxC;                // [2][H]
-  float* zs = hs + 2 * kMaxH;             // [2][C]
-  float* dzs = zs + 2 * kMaxC;            // [2][C]
+  float* hs = b2s + kMaxC;                // [H] (2*kMaxH reserved)
+  float* zs = hs + 2 * kMaxH;             // [8][C] per-warp partial logits
+  float* dzs = zs + 8 * kMaxC;            // [C] (2*kMaxC reserved)
   float* red = dzs + 2 * kMaxC;           // [256]
   float* dZs = red + kThreads;            // [B][C]
   float* dAs = dZs + kMaxB * kMaxC;       // [B][H]  (phase C)
-  float* red_part = dAs;                  // [2][8][kMaxH] phase-B scratch, aliases dAs (never live together)
+  float* red_part = dAs;                  // [16][kMaxH] phase-B scratch, aliases dAs (never live together)
+  // ahead mode: small parameters as fetched one step ahead, double buffered (cp.async destinations)
+  float* W2n = dAs + kMaxB * kMaxH;       // [2][H][C]
+  float* b1n = W2n + 2 * kMaxH * kMaxC;   // [2][H]
+  float* b2n = b1n + 2 * kMaxH;           // [2][C]
   (void)red;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const unsigned G = gridDim.x;
+  const unsigned NC = gridDim.x;          // CTAs in the grid
+  const unsigned G = (unsigned)a.nslices; // the first G of them own a W1 slice
   const int g = blockIdx.x;
+  const bool slice = g < (int)G;
+  const int book = (int)NC - 1;           // the CTA that keeps the books (no batch row when NC > B)
   const int k0 = g * KS;
   unsigned bar_target = 0;
   const float invB = 1.f / (float)B;
@@ -156,7 +180,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
     for (int i = 0; i < kXPer; ++i) {
       int e = tid + i * kThreads;
       int row = 0;
-      if (e < B * KS && st < a.nsteps) {
+      if (slice && e < B * KS && st < a.nsteps) {
         int r = e / KS;
         row = a.batch_idx ? __ldg(a.batch_idx + (sbase + st) * B + r) : (int)((sbase + st) * a.rows_per_step + r);
       }
@@ -168,7 +192,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
     for (int i = 0; i < kXPer; ++i) {
       int e = tid + i * kThreads;
       float v = 0.f;
-      if (e < B * KS && st < a.nsteps) {
+      if (slice && e < B * KS && st < a.nsteps) {
         int k = k0 + e % KS;
         if (k < D) v = __ldg(a.X + (long)rownext[i] * a.ldx + k);
       }
@@ -179,7 +203,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
   fetch_x(0);
   fetch_rows(1);
 
-  const int slot = tid >> 7, t = tid & 127, wq = warp & 3;   // phase B roles: 2 rows per CTA, 4 warps each
+  const int t = tid;                                         // phase B: one row per CTA, thread = hidden unit
 
   // Ownership of the W1 slice inside the CTA (used by the phase-C dW1 tiling AND by the pull): a warp owns
   // 4 consecutive rows and a contiguous block of columns; a lane owns up to two columns of those rows.
@@ -197,14 +221,31 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
       wnext1[q] = (wv1 && k < D) ? dtfe::ld_relaxed_sys(a.W1 + (long)k * H + wj1) : 0.f;
     }
   };
-  fetch_w1();
-  int pending_step = 0;                                 // CTA 0 / thread 0: global step observed for the previous step
+  const bool ahead = a.ahead != 0;
+  const bool has_row = g < B;                           // this CTA handles batch row g in phase B
+  // delta buffer layout (each part starts on a float4): [H*C] W2 | [H] b1 | [C] b2
+  const int dOffB1 = (H * C + 3) & ~3, dOffB2 = dOffB1 + ((H + 3) & ~3);
+  float* const delta = ahead ? a.delta : nullptr;
+  const int nW1 = slice ? (min(D, k0 + KS) - k0) * H : 0;   // floats of this CTA's W1 slice (contiguous)
+  auto fetch_small_async = [&](int buf) {               // W2, b1, b2 -> staging buffer `buf` (this thread's quads)
+    dtfe::cta_copy_async(W2n + buf * kMaxH * kMaxC, a.W2, H * C, tid, kThreads);
+    dtfe::cta_copy_async(b1n + buf * kMaxH, a.b1, H, tid, kThreads);
+    dtfe::cta_copy_async(b2n + buf * kMaxC, a.b2, C, tid, kThreads);
+  };
+  if (ahead) {
+    if (has_row) fetch_small_async(0);
+    dtfe::cta_copy_async(Ws, a.W1 + (long)k0 * H, nW1, tid, kThreads);
+    dtfe::cp_async_commit();
+  } else {
+    fetch_w1();
+  }
+  int pending_step = 0;                                 // book CTA / thread 0: global step observed for the previous step
   const unsigned sx_epoch0 = a.has_sx ? *reinterpret_cast<volatile unsigned*>(a.sx.epoch) : 0u;
   const unsigned long long sx_t0 = gtime();
   __shared__ unsigned s_go;
   int steps_done = 0;
   auto fetch_label_row = [&](int st) {
-    int r = 2 * g + slot;
+    int r = g;
     if (r < B && st < a.nsteps)
       ylab_row = a.batch_idx ? __ldg(a.batch_idx + (sbase + st) * B + r) : (int)((sbase + st) * a.rows_per_step + r);
   };
@@ -213,21 +254,27 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
   for (int s = 0; s < a.nsteps; ++s) {
     // ------------------------------ phase A ------------------------------------
     DBG_STAMP(0);
+    int ylab = 0;
+    if (slice) {
 #pragma unroll
     for (int i = 0; i < kXPer; ++i) {
       int e = tid + i * kThreads;
       if (e < B * KS) Xs[e] = xnext[i];
     }
-    // W1 slice: every thread re-read, right after its own pushes in the previous step's phase C (same
-    // thread, same addresses: program order guarantees it sees them), exactly the elements it owns.
+    if (ahead) {
+      // W1 slice: already in Ws (fetched during the previous step's phase C, own update added there)
+      dtfe::cp_async_wait<0>();              // only the first step of a launch still has copies in flight here
+    } else {
+      // W1 slice: every thread re-read, right after its own pushes in the previous step's phase C (same
+      // thread, same addresses: program order guarantees it sees them), exactly the elements it owns.
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      if (wv0) Ws[(wgrp * 4 + q) * HP + wj0] = wnext0[q];
-      if (wv1) Ws[(wgrp * 4 + q) * HP + wj1] = wnext1[q];
+      for (int q = 0; q < 4; ++q) {
+        if (wv0) Ws[(wgrp * 4 + q) * HP + wj0] = wnext0[q];
+        if (wv1) Ws[(wgrp * 4 + q) * HP + wj1] = wnext1[q];
+      }
     }
-    // label of the first row this thread's slot handles in phase B (latency hidden behind phase A)
-    int ylab = 0;
-    if (2 * g + slot < B) ylab = __ldg(a.labels + ylab_row);   // row index arrived a step ago
+    // label of the row this CTA handles in phase B (latency hidden behind phase A)
+    if (g < B) ylab = __ldg(a.labels + ylab_row);   // row index arrived a step ago
     __syncthreads();
     {
       // W slice in registers once; X rows as broadcast float4 loads: KS/4 + 0 shared loads per 4*KS FMAs
@@ -257,8 +304,11 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
         }
       }
     }
+    } else if (g < B) {
+      ylab = __ldg(a.labels + ylab_row);
+    }
     DBG_STAMP(1);
-    grid_barrier(a.sync, bar_target, G);
+    grid_barrier(a.sync, bar_target, NC);
     DBG_STAMP(2);
 
     // ------------------------------ phase B ------------------------------------
@@ -268,50 +318,86 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
     fetch_label_row(s + 1);
     // Every CTA has passed barrier 1, so every push of step s-1 has been issued and fenced: count that update
     // now.  The atomic's result (the global step the previous step observed, what the reference fetches next
-    // to train_op) is not consumed until the end of phase B, so its round trip costs nothing.
-    if (g == 0 && tid == 0 && s > 0 && a.train && !a.has_sx)
-      pending_step = a.gW1 ? *reinterpret_cast<volatile int*>(a.global_step) : dtfe::atom_add_sys_s32(a.global_step, 1);
-    // Small parameters are read after the barrier so that every CTA sees the pushes all CTAs made in
-    // the previous step's phase C.  They go to registers first; the reduction loads below are issued
-    // before anything waits, so all of it shares one L2 round trip.
+    // to train_op) is not consumed until the end of phase B and the atomic carries no acquire, so its round
+    // trip (microseconds when global_step lives on a peer GPU) costs nothing.
+    if (g == book && tid == 0 && s > 0 && a.train && !a.has_sx)
+      pending_step = a.gW1 ? *reinterpret_cast<volatile int*>(a.global_step)
+                   : a.remote ? dtfe::atom_add_release_sys_s32(a.global_step, 1)
+                              : dtfe::atom_add_relaxed_sys_s32(a.global_step, 1);
+    // Small parameters.  Direct mode (evaluation, synchronous mode): read from the shard after the barrier,
+    // so every CTA sees the pushes all CTAs made in the previous step's phase C.  Ahead mode: the values
+    // fetched (cp.async) during the previous step's phase B plus this worker's own deltas of the previous
+    // step (local buffer, written in phase C); the fetch for the NEXT step starts right here, between the
+    // two grid barriers, when no CTA of this worker pushes, and is complete before barrier 2.
     constexpr int kW2Per = (kMaxH * kMaxC + kThreads - 1) / kThreads;
+    constexpr int kW2Vec = kW2Per / 4;
+    static_assert(kW2Per % 4 == 0 && kMaxH / 4 <= kThreads, "small-parameter staging: whole float4s per thread");
+    const bool from_delta = ahead && s > 0;
     float w2r[kW2Per];
+    float4 b1q = make_float4(0.f, 0.f, 0.f, 0.f), b2q = b1q;    // ahead: delta quads; direct: .x = b1[tid] / b2[tid]
+    if (has_row) {
+      if (!ahead) {
 #pragma unroll
-    for (int i = 0; i < kW2Per; ++i) {
-      int e = tid + i * kThreads;
-      w2r[i] = (e < H * C) ? dtfe::ld_relaxed_sys(a.W2 + e) : 0.f;
+        for (int i = 0; i < kW2Per; ++i) {
+          int e = tid + i * kThreads;
+          w2r[i] = (e < H * C) ? dtfe::ld_relaxed_sys(a.W2 + e) : 0.f;
+        }
+        b1q.x = (tid < H) ? dtfe::ld_relaxed_sys(a.b1 + tid) : 0.f;
+        b2q.x = (tid < C) ? dtfe::ld_relaxed_sys(a.b2 + tid) : 0.f;
+      } else {
+#pragma unroll
+        for (int i = 0; i < kW2Vec; ++i) {             // own deltas: thread owns quads tid, tid+256, ..
+          int f = tid + i * kThreads;
+          float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (from_delta && 4 * f < H * C) v = __ldcg(reinterpret_cast<const float4*>(delta) + f);
+          w2r[4 * i] = v.x; w2r[4 * i + 1] = v.y; w2r[4 * i + 2] = v.z; w2r[4 * i + 3] = v.w;
+        }
+        if (from_delta && 4 * tid < H) b1q = __ldcg(reinterpret_cast<const float4*>(delta + dOffB1) + tid);
+        if (from_delta && 4 * tid < C) b2q = __ldcg(reinterpret_cast<const float4*>(delta + dOffB2) + tid);
+      }
     }
-    float b1r = (tid < H) ? dtfe::ld_relaxed_sys(a.b1 + tid) : 0.f;
-    float b2r = (tid < C) ? dtfe::ld_relaxed_sys(a.b2 + tid) : 0.f;
-    bool params_in_smem = false;
-    for (int r0 = 2 * g; r0 < B || !params_in_smem; r0 += 2 * (int)G) {
-      const int r = r0 + slot;
-      const bool rv = r < B;
+    for (int r = g; r < B; r += (int)NC) {
+      const bool first_round = r == g;
       float z = 0.f;
       const bool vec_reduce = (H & 3) == 0;
+      const int nq4 = vec_reduce ? (H >> 2) : 1;      // float4 columns per row (25)
+      const int nqg = min(kThreads / nq4, 16);        // partial groups (10)
       if (vec_reduce) {
         // Cooperative float4 reduction of the G split-K partials of row r: thread = (column quad, partial
         // group); every thread sums ~G/nqg float4 loads in registers, the nqg group sums meet in smem.
-        const int nq4 = H >> 2;                     // float4 columns per row (25)
-        const int nqg = 128 / nq4;                  // partial groups per row slot (5)
         const int c4 = t % nq4, qg = t / nq4;
         float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (rv && qg < nqg) {
-          const float4* P4 = reinterpret_cast<const float4*>(a.part + (long)r * H) + c4;
-          const long gs4 = ((long)B * H) >> 2;
-          for (unsigned q0 = qg; q0 < G; q0 += 10 * nqg) {     // up to 10 loads in flight per thread
-            float4 v[10];
+        const float4* P4 = reinterpret_cast<const float4*>(a.part + (long)r * H) + c4;
+        const long gs4 = ((long)B * H) >> 2;
+        const bool mine = qg < nqg;
+        float4 v[10];                                           // up to 10 loads in flight per thread
+        auto load_batch = [&](unsigned q0) {
 #pragma unroll
-            for (int u = 0; u < 10; ++u) {
-              unsigned q = q0 + u * nqg;
-              v[u] = (q < G) ? __ldcg(P4 + (long)q * gs4) : make_float4(0.f, 0.f, 0.f, 0.f);
-            }
-#pragma unroll
-            for (int u = 0; u < 10; ++u) { acc.x += v[u].x; acc.y += v[u].y; acc.z += v[u].z; acc.w += v[u].w; }
+          for (int u = 0; u < 10; ++u) {
+            unsigned q = q0 + u * nqg;
+            v[u] = (mine && q < G) ? __ldcg(P4 + (long)q * gs4) : make_float4(0.f, 0.f, 0.f, 0.f);
           }
-          reinterpret_cast<float4*>(red_part + (slot * 8 + qg) * kMaxH)[c4] = acc;
+        };
+        auto add_batch = [&]() {
+#pragma unroll
+          for (int u = 0; u < 10; ++u) { acc.x += v[u].x; acc.y += v[u].y; acc.z += v[u].z; acc.w += v[u].w; }
+        };
+        load_batch(qg);
+        // Ahead mode: the fetch of the next step's small parameters goes out right BEHIND the first batch of
+        // reduction loads (measured: local loads issued after a request to a peer GPU wait behind it).
+        if (ahead && first_round) {
+          if (s + 1 < a.nsteps) fetch_small_async((s + 1) & 1);
+          dtfe::cp_async_commit();
         }
-      } else if (rv && t < H) {
+        add_batch();
+        for (unsigned q0 = qg + 10 * nqg; q0 < G; q0 += 10 * nqg) { load_batch(q0); add_batch(); }
+        if (mine) reinterpret_cast<float4*>(red_part + qg * kMaxH)[c4] = acc;
+      } else {
+        if (ahead && first_round) {
+          if (s + 1 < a.nsteps) fetch_small_async((s + 1) & 1);
+          dtfe::cp_async_commit();
+        }
+        if (t < H) {
         const float* P = a.part + (long)r * H + t;
         const long gs = (long)B * H;
         float z0 = 0.f, z1 = 0.f;
@@ -319,81 +405,100 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
         for (; q + 2 <= G; q += 2) { z0 += __ldcg(P + (long)q * gs); z1 += __ldcg(P + (long)(q + 1) * gs); }
         if (q < G) z0 += __ldcg(P + (long)q * gs);
         z = z0 + z1;
+        }
       }
       DBG_STAMP(8);
-      if (!params_in_smem) {
+      if (first_round) {
+        if (!ahead) {
 #pragma unroll
-        for (int i = 0; i < kW2Per; ++i) {
-          int e = tid + i * kThreads;
-          if (e < H * C) W2s[e] = w2r[i];
+          for (int i = 0; i < kW2Per; ++i) {
+            int e = tid + i * kThreads;
+            if (e < H * C) W2s[e] = w2r[i];
+          }
+          if (tid < H) b1s[tid] = b1q.x;
+          if (tid < C) b2s[tid] = b2q.x;
+        } else {
+          // fetched value + own update = what the shard holds now (bitwise, absent other writers).  Every
+          // thread stages the quads it copied itself, so the wait below is all the ordering needed.
+          dtfe::cp_async_wait<1>();                  // all but the fetch just issued for the next step
+          const float* w2f = W2n + (s & 1) * kMaxH * kMaxC;
+#pragma unroll
+          for (int i = 0; i < kW2Vec; ++i) {
+            int f = tid + i * kThreads;
+            if (4 * f < H * C) {
+              float4 o = reinterpret_cast<const float4*>(w2f)[f];
+              o.x = __fadd_rn(o.x, w2r[4 * i]); o.y = __fadd_rn(o.y, w2r[4 * i + 1]);
+              o.z = __fadd_rn(o.z, w2r[4 * i + 2]); o.w = __fadd_rn(o.w, w2r[4 * i + 3]);
+              reinterpret_cast<float4*>(W2s)[f] = o;
+            }
+          }
+          if (4 * tid < H) {
+            float4 o = reinterpret_cast<const float4*>(b1n + (s & 1) * kMaxH)[tid];
+            o.x = __fadd_rn(o.x, b1q.x); o.y = __fadd_rn(o.y, b1q.y); o.z = __fadd_rn(o.z, b1q.z); o.w = __fadd_rn(o.w, b1q.w);
+            reinterpret_cast<float4*>(b1s)[tid] = o;
+          }
+          if (4 * tid < C) {
+            float4 o = reinterpret_cast<const float4*>(b2n + (s & 1) * kMaxC)[tid];
+            o.x = __fadd_rn(o.x, b2q.x); o.y = __fadd_rn(o.y, b2q.y); o.z = __fadd_rn(o.z, b2q.z); o.w = __fadd_rn(o.w, b2q.w);
+            reinterpret_cast<float4*>(b2s)[tid] = o;
+          }
         }
-        if (tid < H) b1s[tid] = b1r;
-        if (tid < C) b2s[tid] = b2r;
-        params_in_smem = true;
       }
       __syncthreads();
-      if (r0 >= B) break;                    // CTA without rows: parameters staged, nothing else to do
       float h = 0.f;
-      if (rv && t < H) {
-        if (vec_reduce) {
-          const int nqg = 128 / (H >> 2);
-          for (int qg = 0; qg < nqg; ++qg) z += red_part[(slot * 8 + qg) * kMaxH + t];
-        }
+      if (t < H) {
+        if (vec_reduce)
+          for (int qg = 0; qg < nqg; ++qg) z += red_part[qg * kMaxH + t];
         h = dtfe::sigmoidf_fast(z + b1s[t]);
-        hs[slot * kMaxH + t] = h;
+        hs[t] = h;
         __stcg(a.Hbuf + (long)r * H + t, h);
       }
       __syncthreads();
       DBG_STAMP(9);
-      DBG_STAMP(10);
-      if (wq == 0 && rv) {
-        // One warp per row: lane = class + C*group; each group covers a third (32/C groups) of the hidden
-        // units, partial logits are folded with shuffles, then the same lanes do the softmax.
+      {
+        // Logits: lane = class + C*group in every warp; warp w covers hidden units [w*per, (w+1)*per), its
+        // groups interleave inside that range; groups fold with shuffles, warps meet in smem (zs).
         const int ngrp = 32 / C;                      // C <= 16 -> at least 2 groups
         const int cls = lane % C, grp = lane / C;
-        float p0 = 0.f, p1 = 0.f, p2 = 0.f, p3 = 0.f;
-        if (grp < ngrp) {
-          const float* hrow = hs + slot * kMaxH;
-          const float* wcol = W2s + cls;
-          int u = grp;
-          const int st = ngrp;
-#pragma unroll 2
-          for (; u + 3 * st < H; u += 4 * st) {
-            p0 = fmaf(hrow[u], wcol[u * C], p0);
-            p1 = fmaf(hrow[u + st], wcol[(u + st) * C], p1);
-            p2 = fmaf(hrow[u + 2 * st], wcol[(u + 2 * st) * C], p2);
-            p3 = fmaf(hrow[u + 3 * st], wcol[(u + 3 * st) * C], p3);
-          }
-          for (; u < H; u += st) p0 = fmaf(hrow[u], wcol[u * C], p0);
-        }
-        p0 = (p0 + p1) + (p2 + p3);
-        p1 = 0.f;
-        float p = p0 + p1;
+        const int per = (H + 7) / 8;
+        const int ubeg = warp * per, uend = min(H, ubeg + per);
+        float p = 0.f;
+        if (grp < ngrp)
+          for (int u = ubeg + grp; u < uend; u += ngrp) p = fmaf(hs[u], W2s[u * C + cls], p);
         for (int gsh = 1; gsh < ngrp; ++gsh) {        // fold group gsh into group 0
           float other = __shfl_down_sync(0xffffffffu, p, gsh * C);
-          if (grp == 0) p += (lane + gsh * C < ngrp * C) ? other : 0.f;
+          if (grp == 0) p += other;
         }
-        float zc = (lane < C) ? p + b2s[lane] : -INFINITY;
-        float mx = zc; int am = (lane < C) ? lane : 0x7fffffff;
+        if (lane < C) zs[warp * kMaxC + lane] = p;
+      }
+      __syncthreads();
+      DBG_STAMP(10);
+      if (warp == 0) {
+        float zc = -INFINITY;
+        if (lane < C) {
+          float p = b2s[lane];
 #pragma unroll
-        for (int o = 8; o > 0; o >>= 1) {          // C <= 16: the classes live in lanes 0..15
-          float om = __shfl_xor_sync(0xffffffffu, mx, o);
-          int oa = __shfl_xor_sync(0xffffffffu, am, o);
-          if (om > mx || (om == mx && oa < am)) { mx = om; am = oa; }
+          for (int w = 0; w < 8; ++w) p += zs[w * kMaxC + lane];
+          zc = p;
         }
+        float mx = zc;
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));   // classes live in lanes 0..15
+        // first index wins on ties, like tf.argmax
+        const int am = __ffs(__ballot_sync(0xffffffffu, lane < C && zc == mx)) - 1;
         float ex = (lane < C) ? __expf(zc - mx) : 0.f;
         float se = ex;
 #pragma unroll
         for (int o = 8; o > 0; o >>= 1) se += __shfl_xor_sync(0xffffffffu, se, o);
         int y = ylab;
-        if (r0 != 2 * g) {                   // later rounds (B > 2*G): fetch the label now
+        if (!first_round) {                  // later rounds (B > grid): fetch the label now
           long row = a.batch_idx ? (long)a.batch_idx[(sbase + s) * B + r] : (sbase + s) * a.rows_per_step + r;
           y = a.labels[row];
         }
         float zy = __shfl_sync(0xffffffffu, zc, y);
         if (lane < C) {
           float dz = (ex / se - (lane == y ? 1.f : 0.f)) * invB;
-          dzs[slot * kMaxC + lane] = dz;
+          dzs[lane] = dz;
           __stcg(a.dZ + (long)r * C + lane, dz);
         }
         if (lane == 0) {
@@ -403,20 +508,21 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
       }
       __syncthreads();
       DBG_STAMP(11);
-      if (rv && t < H) {
+      if (t < H) {
         float dh = 0.f;
-        for (int c = 0; c < C; ++c) dh = fmaf(dzs[slot * kMaxC + c], W2s[t * C + c], dh);
+        for (int c = 0; c < C; ++c) dh = fmaf(dzs[c], W2s[t * C + c], dh);
         __stcg(a.dA + (long)r * H + t, dh * h * (1.f - h));
       }
       __syncthreads();
     }
-    if (g == 0 && tid == 0 && s > 0 && a.train && !a.has_sx) a.step_out[s - 1] = pending_step;
+    if (g == book && tid == 0 && s > 0 && a.train && !a.has_sx) a.step_out[s - 1] = pending_step;
+    if (ahead) dtfe::cp_async_wait<0>();     // the fetch for the next step has landed before anyone pushes (phase C)
     DBG_STAMP(3);
-    grid_barrier(a.sync, bar_target, G);
+    grid_barrier(a.sync, bar_target, NC);
     DBG_STAMP(4);
 
     // ------------------------------ phase C ------------------------------------
-    if (g == 0 && warp == 7) {
+    if (g == book && warp == 7) {
       // metrics of this step, fixed summation order -> bitwise reproducible
       float l = 0.f; int cnt = 0;
       for (int r = lane; r < B; r += 32) { l += __ldcg(a.rowloss + r); cnt += __ldcg(a.rowcorrect + r); }
@@ -430,102 +536,149 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
     }
     if (a.train) {
       const float nlr = -a.lr;
-      // Small gradients: hidden unit t0 = g (and t1 = g + G on the first CTAs when H > G).  Every warp
-      // takes one or two classes of the dW2 row, so the H column is requested by all warps now and its L2
-      // latency hides behind the dA load and the dW1 loop.
-      const int t0 = g, t1 = g + (int)G;
-      float hcol0[4] = {0.f, 0.f, 0.f, 0.f}, hcol1[4] = {0.f, 0.f, 0.f, 0.f};
+      // Everything this phase reads is requested up front with cp.async, in the order it is needed:
+      //   groups 1..4  dA in four row chunks      -> dW1 starts on chunk 0 while the others are in flight
+      //   group 5      dZ                         -> small gradients
+      //   group 6      (ahead mode) the W1 slice for the next step: fetched BEFORE this CTA pushes to it (only
+      //                this CTA of this worker does), its own update is added in shared memory below.
+      constexpr int kChunks = 4;
+      const int rb = (((B + kChunks - 1) / kChunks) + 3) & ~3;     // rows per chunk, multiple of 4 (16-byte starts)
+      // Who computes the small gradients: the helper CTAs (the ones without a W1 slice) when there are enough
+      // of them, in parallel with the slice CTAs' dW1; otherwise every CTA, after its dW1.
+      const int nhelp = (int)NC - (int)G;
+      const bool on_helpers = nhelp * 4 >= H;
+      const bool does_small = on_helpers ? !slice : true;
+      const int t0 = on_helpers ? g - (int)G : g, tstride = on_helpers ? nhelp : (int)NC;
+      const int t1 = t0 + tstride;
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        int b = lane + 32 * i;
-        if (b < B && t0 < H) hcol0[i] = __ldcg(a.Hbuf + (long)b * H + t0);
-        if (b < B && t1 < H) hcol1[i] = __ldcg(a.Hbuf + (long)b * H + t1);
+      for (int c = 0; c < kChunks; ++c) {
+        const int b0 = min(B, c * rb), b1 = min(B, b0 + rb);
+        if (slice) dtfe::cta_copy_async(dAs + b0 * HP, a.dA + (long)b0 * H, (b1 - b0) * H, tid, kThreads);
+        dtfe::cp_async_commit();
       }
-      for (int e = tid; e < (B * H) / 4; e += kThreads)
-        reinterpret_cast<float4*>(dAs)[e] = __ldcg(reinterpret_cast<const float4*>(a.dA) + e);
-      for (int e = (B * H) / 4 * 4 + tid; e < B * H; e += kThreads) dAs[e] = __ldcg(a.dA + e);
-      for (int e = tid; e < B * C; e += kThreads) dZs[e] = __ldcg(a.dZ + e);
-      __syncthreads();
-      DBG_STAMP(12);
-      {
-        // dW1 rows [k0, k0+KS): a warp owns 4 consecutive rows (one broadcast float4 of X per batch row)
-        // and a contiguous block of columns, so each dA value fetched from shared memory feeds 4 FMAs.
-        float acc0[4] = {0.f, 0.f, 0.f, 0.f}, acc1[4] = {0.f, 0.f, 0.f, 0.f};
-        float bcc0[4] = {0.f, 0.f, 0.f, 0.f}, bcc1[4] = {0.f, 0.f, 0.f, 0.f};
+      if (does_small) dtfe::cta_copy_async(dZs, a.dZ, B * C, tid, kThreads);
+      dtfe::cp_async_commit();
+      // H and dA columns of this CTA's hidden units (local loads: issued before the fetch from the peer)
+      float hcol0[4] = {0.f, 0.f, 0.f, 0.f}, hcol1[4] = {0.f, 0.f, 0.f, 0.f}, dacol[4] = {0.f, 0.f, 0.f, 0.f};
+      if (does_small) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          int b = lane + 32 * i;
+          if (b < B && t0 < H) hcol0[i] = __ldcg(a.Hbuf + (long)b * H + t0);
+          if (b < B && t1 < H) hcol1[i] = __ldcg(a.Hbuf + (long)b * H + t1);
+          if (warp == 5 && b < B && t0 < H) dacol[i] = __ldcg(a.dA + (long)b * H + t0);
+        }
+      }
+      if (ahead && s + 1 < a.nsteps) dtfe::cta_copy_async(Ws, a.W1 + (long)k0 * H, nW1, tid, kThreads);
+      dtfe::cp_async_commit();
+      // dW1 rows [k0, k0+KS): a warp owns 4 consecutive rows (one broadcast float4 of X per batch row)
+      // and a contiguous block of columns, so each dA value fetched from shared memory feeds 4 FMAs.
+      float acc0[4] = {0.f, 0.f, 0.f, 0.f}, acc1[4] = {0.f, 0.f, 0.f, 0.f};
+      float bcc0[4] = {0.f, 0.f, 0.f, 0.f}, bcc1[4] = {0.f, 0.f, 0.f, 0.f};
+      if (slice) {
         const float* xp = Xs + wgrp * 4;
-        int b = 0;
-        for (; b + 2 <= B; b += 2) {          // two independent chains
-          float4 xa = *reinterpret_cast<const float4*>(xp + b * KS);
-          float4 xb = *reinterpret_cast<const float4*>(xp + (b + 1) * KS);
-          float da0 = wv0 ? dAs[b * HP + wj0] : 0.f, db0 = wv0 ? dAs[(b + 1) * HP + wj0] : 0.f;
-          acc0[0] = fmaf(xa.x, da0, acc0[0]); acc0[1] = fmaf(xa.y, da0, acc0[1]);
-          acc0[2] = fmaf(xa.z, da0, acc0[2]); acc0[3] = fmaf(xa.w, da0, acc0[3]);
-          bcc0[0] = fmaf(xb.x, db0, bcc0[0]); bcc0[1] = fmaf(xb.y, db0, bcc0[1]);
-          bcc0[2] = fmaf(xb.z, db0, bcc0[2]); bcc0[3] = fmaf(xb.w, db0, bcc0[3]);
-          if (kParts < 4) {                   // wide parts (KS = 16): a second column per lane
-            float da1 = wv1 ? dAs[b * HP + wj1] : 0.f, db1 = wv1 ? dAs[(b + 1) * HP + wj1] : 0.f;
-            acc1[0] = fmaf(xa.x, da1, acc1[0]); acc1[1] = fmaf(xa.y, da1, acc1[1]);
-            acc1[2] = fmaf(xa.z, da1, acc1[2]); acc1[3] = fmaf(xa.w, da1, acc1[3]);
-            bcc1[0] = fmaf(xb.x, db1, bcc1[0]); bcc1[1] = fmaf(xb.y, db1, bcc1[1]);
-            bcc1[2] = fmaf(xb.z, db1, bcc1[2]); bcc1[3] = fmaf(xb.w, db1, bcc1[3]);
+        for (int c = 0; c < kChunks; ++c) {
+          switch (c) {                            // chunk c has landed: all but the (kChunks + 1 - c) newer groups
+            case 0: dtfe::cp_async_wait<kChunks + 1>(); break;
+            case 1: dtfe::cp_async_wait<kChunks>(); break;
+            case 2: dtfe::cp_async_wait<kChunks - 1>(); break;
+            default: dtfe::cp_async_wait<kChunks - 2>(); break;
+          }
+          __syncthreads();
+          if (c == 0) DBG_STAMP(12);
+          int b = min(B, c * rb);
+          const int bend = min(B, b + rb);
+          for (; b + 2 <= bend; b += 2) {         // two independent chains
+            float4 xa = *reinterpret_cast<const float4*>(xp + b * KS);
+            float4 xb = *reinterpret_cast<const float4*>(xp + (b + 1) * KS);
+            float da0 = wv0 ? dAs[b * HP + wj0] : 0.f, db0 = wv0 ? dAs[(b + 1) * HP + wj0] : 0.f;
+            acc0[0] = fmaf(xa.x, da0, acc0[0]); acc0[1] = fmaf(xa.y, da0, acc0[1]);
+            acc0[2] = fmaf(xa.z, da0, acc0[2]); acc0[3] = fmaf(xa.w, da0, acc0[3]);
+            bcc0[0] = fmaf(xb.x, db0, bcc0[0]); bcc0[1] = fmaf(xb.y, db0, bcc0[1]);
+            bcc0[2] = fmaf(xb.z, db0, bcc0[2]); bcc0[3] = fmaf(xb.w, db0, bcc0[3]);
+            if (kParts < 4) {                     // wide parts (KS = 16): a second column per lane
+              float da1 = wv1 ? dAs[b * HP + wj1] : 0.f, db1 = wv1 ? dAs[(b + 1) * HP + wj1] : 0.f;
+              acc1[0] = fmaf(xa.x, da1, acc1[0]); acc1[1] = fmaf(xa.y, da1, acc1[1]);
+              acc1[2] = fmaf(xa.z, da1, acc1[2]); acc1[3] = fmaf(xa.w, da1, acc1[3]);
+              bcc1[0] = fmaf(xb.x, db1, bcc1[0]); bcc1[1] = fmaf(xb.y, db1, bcc1[1]);
+              bcc1[2] = fmaf(xb.z, db1, bcc1[2]); bcc1[3] = fmaf(xb.w, db1, bcc1[3]);
+            }
+          }
+          for (; b < bend; ++b) {
+            float4 xa = *reinterpret_cast<const float4*>(xp + b * KS);
+            float da0 = wv0 ? dAs[b * HP + wj0] : 0.f;
+            acc0[0] = fmaf(xa.x, da0, acc0[0]); acc0[1] = fmaf(xa.y, da0, acc0[1]);
+            acc0[2] = fmaf(xa.z, da0, acc0[2]); acc0[3] = fmaf(xa.w, da0, acc0[3]);
+            if (kParts < 4) {
+              float da1 = wv1 ? dAs[b * HP + wj1] : 0.f;
+              acc1[0] = fmaf(xa.x, da1, acc1[0]); acc1[1] = fmaf(xa.y, da1, acc1[1]);
+              acc1[2] = fmaf(xa.z, da1, acc1[2]); acc1[3] = fmaf(xa.w, da1, acc1[3]);
+            }
           }
         }
-        for (; b < B; ++b) {
-          float4 xa = *reinterpret_cast<const float4*>(xp + b * KS);
-          float da0 = wv0 ? dAs[b * HP + wj0] : 0.f;
-          acc0[0] = fmaf(xa.x, da0, acc0[0]); acc0[1] = fmaf(xa.y, da0, acc0[1]);
-          acc0[2] = fmaf(xa.z, da0, acc0[2]); acc0[3] = fmaf(xa.w, da0, acc0[3]);
-          if (kParts < 4) {
-            float da1 = wv1 ? dAs[b * HP + wj1] : 0.f;
-            acc1[0] = fmaf(xa.x, da1, acc1[0]); acc1[1] = fmaf(xa.y, da1, acc1[1]);
-            acc1[2] = fmaf(xa.z, da1, acc1[2]); acc1[3] = fmaf(xa.w, da1, acc1[3]);
+      }
+      DBG_STAMP(13);
+      dtfe::cp_async_wait<1>();                   // dZ has landed (this thread's quads) ...
+      __syncthreads();                            // ... and everybody else's
+      if (does_small) {
+        // small gradients: every warp takes one or two classes of the dW2 row; warp 5 also sums the dA column
+        for (int tt = t0, rnd = 0; tt < H; tt += tstride, ++rnd) {
+          float hc[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            int b = lane + 32 * i;
+            hc[i] = rnd == 0 ? hcol0[i] : rnd == 1 ? hcol1[i] : (b < B ? __ldcg(a.Hbuf + (long)b * H + tt) : 0.f);
+          }
+          for (int c = warp; c < C; c += 8) {     // dW2[tt][c] = sum_b H[b][tt] * dZ[b][c]
+            float v = 0.f;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              int b = lane + 32 * i;
+              if (b < B) v = fmaf(hc[i], dZs[b * C + c], v);
+            }
+            v = dtfe::warp_sum(v);
+            if (lane == 0) emit_small(a.W2, a.gW2, delta, (long)tt * C + c, v, nlr, a.atomic);
+          }
+          if (warp == 5) {                        // db1[tt] = sum_b dA[b][tt]
+            float v = 0.f;
+            if (rnd == 0) v = (dacol[0] + dacol[1]) + (dacol[2] + dacol[3]);
+            else for (int b = lane; b < B; b += 32) v += __ldcg(a.dA + (long)b * H + tt);
+            v = dtfe::warp_sum(v);
+            if (lane == 0) emit_small(a.b1, a.gb1, delta ? delta + dOffB1 : nullptr, tt, v, nlr, a.atomic);
           }
         }
+        if (g == book) {                          // db2[c] = sum_b dZ[b][c], spread over the warps
+          for (int c = warp; c < C; c += 8) {
+            float v = 0.f;
+            for (int b = lane; b < B; b += 32) v += dZs[b * C + c];
+            v = dtfe::warp_sum(v);
+            if (lane == 0) emit_small(a.b2, a.gb2, delta ? delta + dOffB2 : nullptr, c, v, nlr, a.atomic);
+          }
+        }
+      }
+      DBG_STAMP(14);
+      if (ahead) {                                // next step's W1 slice is in Ws before this CTA pushes to it
+        dtfe::cp_async_wait<0>();
+        __syncthreads();
+      }
+      if (slice) {
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           int k = k0 + wgrp * 4 + q;
           if (k < D) {
-            if (wv0) emit(a.W1, a.gW1, (long)k * H + wj0, acc0[q] + bcc0[q], nlr, a.atomic);
-            if (kParts < 4 && wv1) emit(a.W1, a.gW1, (long)k * H + wj1, acc1[q] + bcc1[q], nlr, a.atomic);
+            const float g0 = acc0[q] + bcc0[q], g1 = acc1[q] + bcc1[q];
+            if (wv0) emit(a.W1, a.gW1, (long)k * H + wj0, g0, nlr, a.atomic);
+            if (kParts < 4 && wv1) emit(a.W1, a.gW1, (long)k * H + wj1, g1, nlr, a.atomic);
+            if (ahead) {        // fetched value + own update = what the shard holds (bitwise, absent other writers)
+              float* w0 = Ws + (wgrp * 4 + q) * HP + wj0;
+              if (wv0) *w0 = __fadd_rn(*w0, __fmul_rn(nlr, g0));
+              if (kParts < 4 && wv1) w0[32] = __fadd_rn(w0[32], __fmul_rn(nlr, g1));
+            }
           }
         }
-      }
-      // pull for the next step: the same thread reads back exactly the elements it just pushed
-      // (synchronous mode: the parameters only change in phase D, the read-back happens there)
-      if (!a.has_sx) fetch_w1();
-      DBG_STAMP(13);
-      // small gradients, one or two classes per warp
-      for (int tt = t0, rnd = 0; tt < H; tt += (int)G, ++rnd) {
-        float hc[4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          int b = lane + 32 * i;
-          hc[i] = rnd == 0 ? hcol0[i] : rnd == 1 ? hcol1[i] : (b < B ? __ldcg(a.Hbuf + (long)b * H + tt) : 0.f);
-        }
-        for (int c = warp; c < C; c += 8) {       // dW2[tt][c] = sum_b H[b][tt] * dZ[b][c]
-          float v = 0.f;
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            int b = lane + 32 * i;
-            if (b < B) v = fmaf(hc[i], dZs[b * C + c], v);
-          }
-          v = dtfe::warp_sum(v);
-          if (lane == 0) emit(a.W2, a.gW2, (long)tt * C + c, v, nlr, a.atomic);
-        }
-        if (warp == 5) {                          // db1[tt] = sum_b dA[b][tt]
-          float v = 0.f;
-          for (int b = lane; b < B; b += 32) v += dAs[b * HP + tt];
-          v = dtfe::warp_sum(v);
-          if (lane == 0) emit(a.b1, a.gb1, tt, v, nlr, a.atomic);
-        }
-      }
-      if (g == (int)G - 1) {                      // db2[c] = sum_b dZ[b][c], spread over the warps
-        for (int c = warp; c < C; c += 8) {
-          float v = 0.f;
-          for (int b = lane; b < B; b += 32) v += dZs[b * C + c];
-          v = dtfe::warp_sum(v);
-          if (lane == 0) emit(a.b2, a.gb2, c, v, nlr, a.atomic);
-        }
+        // Direct mode: the same thread reads back exactly the elements it just pushed (synchronous mode:
+        // the parameters only change in phase D, the read-back happens there)
+        if (!ahead && !a.has_sx) fetch_w1();
       }
       DBG_STAMP(5);
       // No per-step completion handshake: the next grid barrier (or the exit handshake below) orders all
@@ -535,7 +688,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
       if (a.has_sx) {
         // ------------------------------ phase D (synchronous mode) -------------------------------
         // D1: every CTA's gradients are in this rank's exchange buffer
-        grid_barrier(a.sync, bar_target, G);
+        grid_barrier(a.sync, bar_target, NC);
         const unsigned epoch = sx_epoch0 + (unsigned)s + 1u;
         const unsigned kAbort = 0xffffffffu;
         // D2: tell every peer, wait for every peer (CTA 0), then release the grid
@@ -556,7 +709,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
         const bool aborted = s_go == kAbort;
         // D3: reduce the slices of the variables this rank owns out of all ranks' buffers and apply in place
         if (!aborted) {
-          const size_t gtid = (size_t)g * kThreads + tid, gstride = (size_t)G * kThreads;
+          const size_t gtid = (size_t)g * kThreads + tid, gstride = (size_t)NC * kThreads;
           for (int sg = 0; sg < a.sx.nseg; ++sg) {
             const size_t begin = a.sx.seg_begin[sg], n = a.sx.seg_end[sg] - begin;
             float* param = a.sx.seg_param[sg];
@@ -581,7 +734,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
         }
         // D4: all of this rank's applies are done; wait until every rank's are (nobody may read a stale
         // parameter or overwrite a gradient buffer that a peer is still reducing)
-        grid_barrier(a.sync, bar_target, G);
+        grid_barrier(a.sync, bar_target, NC);
         if (g == 0 && tid == 0) {
           bool ok = !aborted;
           if (ok) {
@@ -619,7 +772,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
   if (tid == 0) {
     __threadfence();
     unsigned prev = atomicAdd(a.sync + 1, 1u);
-    if (prev == G - 1) {
+    if (prev == NC - 1) {
       a.sync[0] = 0; a.sync[1] = 0;
       if (a.has_sx) {
         *a.sx.epoch = sx_epoch0 + (unsigned)steps_done;
@@ -636,21 +789,22 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
 
 template <int KS>
 constexpr size_t smem_floats() {
-  return (size_t)kMaxB * KS + (size_t)KS * kMaxH + kMaxH * kMaxC + kMaxH + kMaxC + 2 * kMaxH + 2 * kMaxC +
-         2 * kMaxC + kThreads + kMaxB * kMaxC + (size_t)kMaxB * kMaxH;
+  return (size_t)kMaxB * KS + (size_t)KS * kMaxH + kMaxH * kMaxC + kMaxH + kMaxC + 2 * kMaxH + 8 * kMaxC +
+         2 * kMaxC + kThreads + kMaxB * kMaxC + (size_t)kMaxB * kMaxH + 2 * (size_t)kMaxH * kMaxC + 2 * kMaxH +
+         2 * kMaxC;
 }
 
 }  // namespace
 
-// Scratch sizing for callers: floats needed for `part` given the grid, plus the fixed rest.
+// Number of W1 slices (= CTAs that own one; split-K factor of the first layer).
 DTFE_API int dtfe_mlp2_step_grid(int D, int ks) { return (D + ks - 1) / ks; }
 
 // Element counts (4-byte words) of the scratch regions, in the order the workspace is carved:
-// part[G*B*H] | Hbuf[B*H] | dA[B*H] | dZ[B*C] | rowloss[B] | rowcorrect[B] | sync[4]
+// part[G*B*H] | dA[B*H] | Hbuf[B*H] | dZ[B*C] | rowloss[B] | rowcorrect[B] | delta[H*C+H+C] | sync[4]
 DTFE_API size_t dtfe_mlp2_step_workspace_words(int B, int D, int H, int C, int ks) {
   size_t G = (size_t)((D + ks - 1) / ks);
-  size_t w = G * B * H + 2 * (size_t)B * H + (size_t)B * C + 2 * (size_t)B + 4;
-  return (w + 3) / 4 * 4 + 16;
+  size_t w = G * B * H + 2 * (size_t)B * H + (size_t)B * C + 2 * (size_t)B + ((size_t)H * C + H + C + 12) + 4;
+  return (w + 3) / 4 * 4 + 32;
 }
 
 using Mlp2Launch = dtfe_mlp2_launch;
@@ -672,10 +826,14 @@ static int mlp2_fill(const Mlp2Launch& L, Mlp2Args& a) {
   a.dA = w;                 w += (size_t)L.B * L.H;
   w = (float*)(((uintptr_t)w + 15) & ~(uintptr_t)15);
   a.Hbuf = w;               w += (size_t)L.B * L.H;
+  w = (float*)(((uintptr_t)w + 15) & ~(uintptr_t)15);
   a.dZ = w;                 w += (size_t)L.B * L.C;
   a.rowloss = w;            w += L.B;
   a.rowcorrect = (int*)w;   w += L.B;
+  w = (float*)(((uintptr_t)w + 15) & ~(uintptr_t)15);
+  a.delta = w;              w += (size_t)L.H * L.C + L.H + L.C + 12;
   a.sync = (unsigned*)w;
+  a.nslices = (int)G;
   a.loss_out = L.loss_out; a.acc_out = L.acc_out; a.step_out = L.step_out;
   a.lr = L.lr; a.nsteps = L.nsteps; a.atomic = L.atomic; a.train = L.train; a.remote = L.remote; a.dbg = L.dbg;
   a.gW1 = L.gW1; a.gb1 = L.gb1; a.gW2 = L.gW2; a.gb2 = L.gb2; a.cursor = L.cursor;
@@ -689,23 +847,64 @@ static int mlp2_fill(const Mlp2Launch& L, Mlp2Args& a) {
   }
   DTFE_REQUIRE((a.gW1 != nullptr) == (a.gb1 != nullptr) && (a.gW1 != nullptr) == (a.gW2 != nullptr) &&
                (a.gW1 != nullptr) == (a.gb2 != nullptr), "mlp2_step: pass all four gradient buffers or none");
+  // Pull-ahead copies in 16-byte units (cp.async) and only applies where this kernel itself pushes the updates.
+  static const bool ahead_off = getenv("DTFE_MLP2_NO_AHEAD") != nullptr;
+  const bool aligned16 = (((uintptr_t)L.W1 | (uintptr_t)L.W2 | (uintptr_t)L.b1 | (uintptr_t)L.b2) % 16) == 0;
+  a.ahead = (!ahead_off && a.train && !a.gW1 && aligned16) ? 1 : 0;
+  return 0;
+}
+
+// CTAs the cooperative grid can hold on the current device (1 per SM with this kernel's registers/smem).
+template <int KS>
+static int mlp2_max_ctas(int* out) {
+  static int cached[64] = {};
+  int dev;
+  DTFE_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev >= 64 || cached[dev] == 0) {
+    size_t smem = smem_floats<KS>() * sizeof(float);
+    DTFE_CUDA_CHECK(cudaFuncSetAttribute(k_mlp2_step<KS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 0, sms = 0;
+    DTFE_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_mlp2_step<KS>, kThreads, smem));
+    DTFE_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    int n = per_sm * sms;
+    if (dev < 64) cached[dev] = n;
+    *out = n;
+    return 0;
+  }
+  *out = cached[dev];
+  return 0;
+}
+
+// Grid width: the W1 slices, widened to one CTA per batch row plus one that keeps the books when the
+// device can hold them all at once (cooperative launch).
+template <int KS>
+static int mlp2_grid_width(int B, int D, int H, int* out) {
+  int G = (D + KS - 1) / KS, cap = 0;
+  if (int rc = mlp2_max_ctas<KS>(&cap)) return rc;
+  DTFE_REQUIRE(G <= cap, "mlp2_step: %d W1 slices need %d co-resident CTAs, this device holds %d", G, G, cap);
+  // B+1: one CTA per batch row plus the bookkeeper; G + H/2: helper CTAs that take the small gradients
+  // (two hidden units each) off the slice CTAs.
+  int want = B + 1 > G + (H + 1) / 2 ? B + 1 : G + (H + 1) / 2;
+  if (want > cap) want = cap;
+  *out = G > want ? G : want;
   return 0;
 }
 
 template <int KS>
 static int mlp2_launch(Mlp2Args& a, cudaStream_t stream) {
-  static bool configured[64] = {};
-  int dev;
-  DTFE_CUDA_CHECK(cudaGetDevice(&dev));
   size_t smem = smem_floats<KS>() * sizeof(float);
-  if (dev < 64 && !configured[dev]) {
-    DTFE_CUDA_CHECK(cudaFuncSetAttribute(k_mlp2_step<KS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured[dev] = true;
-  }
-  int G = (a.D + KS - 1) / KS;
+  int NC = 0;
+  if (int rc = mlp2_grid_width<KS>(a.B, a.D, a.H, &NC)) return rc;   // also sets the kernel's smem attribute once
   void* args[] = {&a};
-  DTFE_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)k_mlp2_step<KS>, dim3(G), dim3(kThreads), args, smem, stream));
+  DTFE_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)k_mlp2_step<KS>, dim3(NC), dim3(kThreads), args, smem, stream));
   return 0;
+}
+
+// CTAs one launch uses on the current device (the first dimension of the optional `dbg` stamp array).
+DTFE_API int dtfe_mlp2_step_ctas(int B, int D, int H, int ks) {
+  int NC = 0;
+  int rc = ks == 8 ? mlp2_grid_width<8>(B, D, H, &NC) : mlp2_grid_width<16>(B, D, H, &NC);
+  return rc ? -1 : NC;
 }
 
 // Run `nsteps` full training (train=1) or metric-only (train=0) steps of the 2-layer MLP.

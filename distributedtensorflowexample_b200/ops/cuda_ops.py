@@ -45,6 +45,7 @@ _SIGS = {
     "dtfe_sync_max_ranks": ([], c_int),
     "dtfe_gather_rows_f32": ([_P, c_long, _P, _P, _P, c_int, c_int, _P, _P, _P], c_int),
     "dtfe_mlp2_step_grid": ([c_int, c_int], c_int),
+    "dtfe_mlp2_step_ctas": ([c_int, c_int, c_int, c_int], c_int),
     "dtfe_mlp2_step_workspace_words": ([c_int, c_int, c_int, c_int, c_int], c_size_t),
     "dtfe_mlp2_step": ([_P, _P], c_int),
     "dtfe_hostfeed_create": ([c_int, c_int, c_int, POINTER(_P)], c_int),
@@ -340,7 +341,11 @@ class Mlp2Step:
         self.loss = torch.zeros(max_steps, dtype=torch.float32, device=self.device)
         self.acc = torch.zeros(max_steps, dtype=torch.float32, device=self.device)
         self.step = torch.zeros(max_steps, dtype=torch.int32, device=self.device)
-        self.grid = lib().dtfe_mlp2_step_grid(D, ks)
+        self.slices = lib().dtfe_mlp2_step_grid(D, ks)
+        with torch.cuda.device(self.device):
+            self.grid = lib().dtfe_mlp2_step_ctas(B, D, H, ks)     # CTAs per launch (rows of the dbg stamp array)
+        if self.grid < 0:
+            check(1, "dtfe_mlp2_step_ctas")
 
     def _launch_struct(self, W1, b1, W2, b2, global_step, lr, atomic, train, remote, out_offset=0):
         L = _Mlp2Launch()

@@ -141,14 +141,16 @@ typedef struct dtfe_mlp2_launch {
   float* workspace;                   /* dtfe_mlp2_step_workspace_words() 4-byte words, zeroed once */
   float* loss_out; float* acc_out; int* step_out;   /* [nsteps] each */
   float lr; int nsteps; int atomic; int train; int remote;
-  long long* dbg;                     /* NULL, or [nsteps][grid][16] globaltimer stamps */
+  long long* dbg;                     /* NULL, or [nsteps][dtfe_mlp2_step_ctas()][16] globaltimer stamps */
   float *gW1, *gb1, *gW2, *gb2;       /* all NULL (async: push), or sync mode: raw gradients stored here, no push,
                                          no global_step increment (dtfe_sync_rs_apply_f32 does both) */
   int* cursor;                        /* NULL, or device int: batches start at batch_idx[*cursor * B]; advanced by
                                          nsteps at kernel end (lets a captured graph walk through the data) */
   const dtfe_sync_exchange* sync_exchange;  /* NULL, or: synchronous SGD with the exchange inside the kernel */
 } dtfe_mlp2_launch;
-int dtfe_mlp2_step_grid(int D, int ks);
+int dtfe_mlp2_step_grid(int D, int ks);          /* W1 slices = split-K factor of layer 1 */
+int dtfe_mlp2_step_ctas(int B, int D, int H, int ks);  /* CTAs per launch on the current device (slices + row/helper
+                                                          CTAs, at most one per SM); -1 on error */
 size_t dtfe_mlp2_step_workspace_words(int B, int D, int H, int C, int ks);
 int dtfe_mlp2_step(const dtfe_mlp2_launch* launch, void* stream);
 

@@ -35,7 +35,8 @@ def test_async_two_workers_one_gpu_then_resume(tmp_path):
     assert abs(codes["ps"]) in (15, 143)                       # the ps only ever leaves by signal, like the reference
     w0 = cl.lines["worker0"]
     assert any(l.startswith("Per-process GPU memory fraction: 0.45") for l in w0)
-    assert any(l.startswith("test accuracy: ") for l in w0)
+    # printed by whichever worker observes global step 0 (usually the chief, but the other worker may win the race)
+    assert any(l.startswith("test accuracy: ") for l in w0 + cl.lines["worker1"])
     pat = re.compile(r"^step: (\d+)\t\| cost: ([-0-9.e]+)\t\| speed: ([-0-9.e]+)step/sec$")
     costs = [float(m.group(2)) for l in w0 + cl.lines["worker1"] if (m := pat.match(l))]
     assert costs and min(costs) < 2.0 < max(costs) + 20         # it trains from ~9 down
