@@ -96,13 +96,8 @@ __device__ __forceinline__ int atom_add_sys_s32(int* p, int v) {
   asm volatile("atom.acq_rel.sys.global.add.s32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(v) : "memory");
   return old;
 }
-// Same counter bump without the acquire half: later loads of the issuing thread do not wait for the
+// Same counter bump with no ordering attached: later loads of the issuing thread do not wait for the
 // atomic's round trip (over NVLink that is microseconds); the result is scoreboarded until first use.
-__device__ __forceinline__ int atom_add_release_sys_s32(int* p, int v) {
-  int old;
-  asm volatile("atom.release.sys.global.add.s32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(v) : "memory");
-  return old;
-}
 __device__ __forceinline__ int atom_add_relaxed_sys_s32(int* p, int v) {
   int old;
   asm volatile("atom.relaxed.sys.global.add.s32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(v) : "memory");

@@ -58,7 +58,8 @@ struct Mlp2Args {
   float* dZ;                // [B][C]
   float* rowloss;           // [B]
   int* rowcorrect;          // [B]
-  float* delta;             // [H*C + H + C] this worker's last small-parameter updates (ahead mode)
+  float* delta;             // [H*C + H + C (+pad)] this worker's last small-parameter updates (ahead mode)
+  float* mirror;            // [2][same] the small parameters as the bookkeeper last fetched them (ahead mode)
   unsigned* sync;           // [4]: grid barrier, exit count, phase-D go words
   float* loss_out;          // [nsteps]
   float* acc_out;           // [nsteps]
@@ -146,15 +147,14 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
   float* hs = b2s + kMaxC;                // [H] (2*kMaxH reserved)
   float* zs = hs + 2 * kMaxH;             // [8][C] per-warp partial logits
   float* dzs = zs + 8 * kMaxC;            // [C] (2*kMaxC reserved)
-  float* red = dzs + 2 * kMaxC;           // [256]
+  float* red = dzs + 2 * kMaxC;           // [2][kMaxB] phase C: the H columns of this CTA's hidden units
   float* dZs = red + kThreads;            // [B][C]
   float* dAs = dZs + kMaxB * kMaxC;       // [B][H]  (phase C)
   float* red_part = dAs;                  // [16][kMaxH] phase-B scratch, aliases dAs (never live together)
-  // ahead mode: small parameters as fetched one step ahead, double buffered (cp.async destinations)
-  float* W2n = dAs + kMaxB * kMaxH;       // [2][H][C]
-  float* b1n = W2n + 2 * kMaxH * kMaxC;   // [2][H]
-  float* b2n = b1n + 2 * kMaxH;           // [2][C]
-  (void)red;
+  // ahead mode, bookkeeping CTA: the small parameters as fetched from the shard (cp.async destination),
+  // laid out like the delta / mirror buffers: W2 | b1 | b2, each part starting on a float4
+  float* stg = dAs + kMaxB * kMaxH;       // [kMaxH*kMaxC + kMaxH + kMaxC]
+  float* dwp = stg + kMaxH * kMaxC + kMaxH + kMaxC;   // [8][KS][kMaxH] per-warp partial dW1 tiles (phase C)
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const unsigned NC = gridDim.x;          // CTAs in the grid
@@ -223,17 +223,23 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
   };
   const bool ahead = a.ahead != 0;
   const bool has_row = g < B;                           // this CTA handles batch row g in phase B
-  // delta buffer layout (each part starts on a float4): [H*C] W2 | [H] b1 | [C] b2
-  const int dOffB1 = (H * C + 3) & ~3, dOffB2 = dOffB1 + ((H + 3) & ~3);
+  // delta / mirror / staging layout (each part starts on a float4): [H*C] W2 | [H] b1 | [C] b2
+  const int dOffB1 = (H * C + 3) & ~3, dOffB2 = dOffB1 + ((H + 3) & ~3), dWords = dOffB2 + ((C + 3) & ~3);
   float* const delta = ahead ? a.delta : nullptr;
   const int nW1 = slice ? (min(D, k0 + KS) - k0) * H : 0;   // floats of this CTA's W1 slice (contiguous)
-  auto fetch_small_async = [&](int buf) {               // W2, b1, b2 -> staging buffer `buf` (this thread's quads)
-    dtfe::cta_copy_async(W2n + buf * kMaxH * kMaxC, a.W2, H * C, tid, kThreads);
-    dtfe::cta_copy_async(b1n + buf * kMaxH, a.b1, H, tid, kThreads);
-    dtfe::cta_copy_async(b2n + buf * kMaxC, a.b2, C, tid, kThreads);
+  // Ahead mode: who fetches the small parameters from the shard.  The CTAs without a batch row share the
+  // quads (a few 16-byte requests per SM instead of hundreds from one); without such CTAs the bookkeeper
+  // does it alone.
+  const int nfetch = (int)NC > B ? (int)NC - B : 1;
+  const int fidx = (int)NC > B ? g - B : (g == book ? 0 : -1);
+  constexpr int kFetchSlots = (kMaxH * kMaxC + kMaxH + kMaxC + 4 * kThreads - 1) / (4 * kThreads);
+  auto small_quad_src = [&](int e, int& n) -> const float* {   // element e of the W2|b1|b2 layout
+    if (e < dOffB1) { n = H * C - e; return a.W2 + e; }
+    if (e < dOffB2) { n = H - (e - dOffB1); return a.b1 + (e - dOffB1); }
+    n = C - (e - dOffB2);
+    return a.b2 + (e - dOffB2);
   };
   if (ahead) {
-    if (has_row) fetch_small_async(0);
     dtfe::cta_copy_async(Ws, a.W1 + (long)k0 * H, nW1, tid, kThreads);
     dtfe::cp_async_commit();
   } else {
@@ -316,44 +322,58 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
     fetch_x(s + 1);
     fetch_rows(s + 2);
     fetch_label_row(s + 1);
-    // Every CTA has passed barrier 1, so every push of step s-1 has been issued and fenced: count that update
-    // now.  The atomic's result (the global step the previous step observed, what the reference fetches next
-    // to train_op) is not consumed until the end of phase B and the atomic carries no acquire, so its round
-    // trip (microseconds when global_step lives on a peer GPU) costs nothing.
+    // Every CTA has passed barrier 1, so every push of step s-1 has been issued and fenced (GPU scope): count
+    // that update now.  The atomic is relaxed - a release at system scope costs this CTA ~6 us when the
+    // counter lives on a peer GPU, and it would be late at barrier 2 for everybody - so WITHIN a launch an
+    // observer on another GPU may see the counter a few in-flight NVLink writes ahead of the parameters (the
+    // reference's global_step and variable updates are separate, unordered ops as well); the exit handshake
+    // puts a system fence before the launch's last increment.  The result (the global step the previous step
+    // observed, what the reference fetches next to train_op) is consumed at the end of phase C.
     if (g == book && tid == 0 && s > 0 && a.train && !a.has_sx)
       pending_step = a.gW1 ? *reinterpret_cast<volatile int*>(a.global_step)
-                   : a.remote ? dtfe::atom_add_release_sys_s32(a.global_step, 1)
-                              : dtfe::atom_add_relaxed_sys_s32(a.global_step, 1);
-    // Small parameters.  Direct mode (evaluation, synchronous mode): read from the shard after the barrier,
-    // so every CTA sees the pushes all CTAs made in the previous step's phase C.  Ahead mode: the values
-    // fetched (cp.async) during the previous step's phase B plus this worker's own deltas of the previous
-    // step (local buffer, written in phase C); the fetch for the NEXT step starts right here, between the
-    // two grid barriers, when no CTA of this worker pushes, and is complete before barrier 2.
+                           : dtfe::atom_add_relaxed_sys_s32(a.global_step, 1);
+    // Small parameters.  Direct mode (evaluation, synchronous mode, first step of a launch): read from the
+    // shard after the barrier, so every CTA sees the pushes all CTAs made in the previous step's phase C.
+    // Ahead mode: ONE CTA (the bookkeeper) fetches them from the shard during phase B - between the two grid
+    // barriers no CTA of this worker pushes - and republishes them in a local mirror before barrier 2; a step
+    // later every row CTA adds this worker's own deltas of the step in between (local buffer, written in
+    // phase C).  Row CTAs therefore only ever load local memory here, and the peer sees one reader, not 100.
     constexpr int kW2Per = (kMaxH * kMaxC + kThreads - 1) / kThreads;
-    constexpr int kW2Vec = kW2Per / 4;
-    static_assert(kW2Per % 4 == 0 && kMaxH / 4 <= kThreads, "small-parameter staging: whole float4s per thread");
-    const bool from_delta = ahead && s > 0;
+    constexpr int kSmallVec = (kMaxH * kMaxC + kMaxH + kMaxC + 4 * kThreads - 1) / (4 * kThreads);   // quads per thread
+    const bool from_mirror = ahead && s > 0;
+    const bool fetches = ahead && fidx >= 0 && s + 1 < a.nsteps;
+    if (fetches) {
+#pragma unroll
+      for (int k = 0; k < kFetchSlots; ++k) {
+        const int slot = tid + k * kThreads, e = 4 * (fidx + slot * nfetch);
+        if (e < dWords) {
+          int n;
+          const float* src = small_quad_src(e, n);
+          dtfe::cp_async_cg16(stg + 4 * slot, src, n >= 4 ? 16 : 4 * n);   // tails zero-filled
+        }
+      }
+      dtfe::cp_async_commit();
+    }
     float w2r[kW2Per];
-    float4 b1q = make_float4(0.f, 0.f, 0.f, 0.f), b2q = b1q;    // ahead: delta quads; direct: .x = b1[tid] / b2[tid]
+    float b1r = 0.f, b2r = 0.f;
+    float4 mq[kSmallVec], dq[kSmallVec];
     if (has_row) {
-      if (!ahead) {
+      if (!from_mirror) {
 #pragma unroll
         for (int i = 0; i < kW2Per; ++i) {
           int e = tid + i * kThreads;
           w2r[i] = (e < H * C) ? dtfe::ld_relaxed_sys(a.W2 + e) : 0.f;
         }
-        b1q.x = (tid < H) ? dtfe::ld_relaxed_sys(a.b1 + tid) : 0.f;
-        b2q.x = (tid < C) ? dtfe::ld_relaxed_sys(a.b2 + tid) : 0.f;
+        b1r = (tid < H) ? dtfe::ld_relaxed_sys(a.b1 + tid) : 0.f;
+        b2r = (tid < C) ? dtfe::ld_relaxed_sys(a.b2 + tid) : 0.f;
       } else {
+        const float4* m4 = reinterpret_cast<const float4*>(a.mirror + (s & 1) * dWords);
+        const float4* d4 = reinterpret_cast<const float4*>(delta);
 #pragma unroll
-        for (int i = 0; i < kW2Vec; ++i) {             // own deltas: thread owns quads tid, tid+256, ..
+        for (int i = 0; i < kSmallVec; ++i) {
           int f = tid + i * kThreads;
-          float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (from_delta && 4 * f < H * C) v = __ldcg(reinterpret_cast<const float4*>(delta) + f);
-          w2r[4 * i] = v.x; w2r[4 * i + 1] = v.y; w2r[4 * i + 2] = v.z; w2r[4 * i + 3] = v.w;
+          if (4 * f < dWords) { mq[i] = __ldcg(m4 + f); dq[i] = __ldcg(d4 + f); }
         }
-        if (from_delta && 4 * tid < H) b1q = __ldcg(reinterpret_cast<const float4*>(delta + dOffB1) + tid);
-        if (from_delta && 4 * tid < C) b2q = __ldcg(reinterpret_cast<const float4*>(delta + dOffB2) + tid);
       }
     }
     for (int r = g; r < B; r += (int)NC) {
@@ -383,20 +403,10 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
           for (int u = 0; u < 10; ++u) { acc.x += v[u].x; acc.y += v[u].y; acc.z += v[u].z; acc.w += v[u].w; }
         };
         load_batch(qg);
-        // Ahead mode: the fetch of the next step's small parameters goes out right BEHIND the first batch of
-        // reduction loads (measured: local loads issued after a request to a peer GPU wait behind it).
-        if (ahead && first_round) {
-          if (s + 1 < a.nsteps) fetch_small_async((s + 1) & 1);
-          dtfe::cp_async_commit();
-        }
         add_batch();
         for (unsigned q0 = qg + 10 * nqg; q0 < G; q0 += 10 * nqg) { load_batch(q0); add_batch(); }
         if (mine) reinterpret_cast<float4*>(red_part + qg * kMaxH)[c4] = acc;
       } else {
-        if (ahead && first_round) {
-          if (s + 1 < a.nsteps) fetch_small_async((s + 1) & 1);
-          dtfe::cp_async_commit();
-        }
         if (t < H) {
         const float* P = a.part + (long)r * H + t;
         const long gs = (long)B * H;
@@ -409,38 +419,26 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
       }
       DBG_STAMP(8);
       if (first_round) {
-        if (!ahead) {
+        if (!from_mirror) {
 #pragma unroll
           for (int i = 0; i < kW2Per; ++i) {
             int e = tid + i * kThreads;
             if (e < H * C) W2s[e] = w2r[i];
           }
-          if (tid < H) b1s[tid] = b1q.x;
-          if (tid < C) b2s[tid] = b2q.x;
+          if (tid < H) b1s[tid] = b1r;
+          if (tid < C) b2s[tid] = b2r;
         } else {
-          // fetched value + own update = what the shard holds now (bitwise, absent other writers).  Every
-          // thread stages the quads it copied itself, so the wait below is all the ordering needed.
-          dtfe::cp_async_wait<1>();                  // all but the fetch just issued for the next step
-          const float* w2f = W2n + (s & 1) * kMaxH * kMaxC;
+          // mirrored value + own update = what the shard holds now (bitwise, absent other writers)
 #pragma unroll
-          for (int i = 0; i < kW2Vec; ++i) {
-            int f = tid + i * kThreads;
-            if (4 * f < H * C) {
-              float4 o = reinterpret_cast<const float4*>(w2f)[f];
-              o.x = __fadd_rn(o.x, w2r[4 * i]); o.y = __fadd_rn(o.y, w2r[4 * i + 1]);
-              o.z = __fadd_rn(o.z, w2r[4 * i + 2]); o.w = __fadd_rn(o.w, w2r[4 * i + 3]);
-              reinterpret_cast<float4*>(W2s)[f] = o;
+          for (int i = 0; i < kSmallVec; ++i) {
+            int e = 4 * (tid + i * kThreads);
+            if (e < dWords) {
+              float4 o = mq[i];
+              o.x = __fadd_rn(o.x, dq[i].x); o.y = __fadd_rn(o.y, dq[i].y);
+              o.z = __fadd_rn(o.z, dq[i].z); o.w = __fadd_rn(o.w, dq[i].w);
+              float* dst = e < dOffB1 ? W2s + e : e < dOffB2 ? b1s + (e - dOffB1) : b2s + (e - dOffB2);
+              *reinterpret_cast<float4*>(dst) = o;
             }
-          }
-          if (4 * tid < H) {
-            float4 o = reinterpret_cast<const float4*>(b1n + (s & 1) * kMaxH)[tid];
-            o.x = __fadd_rn(o.x, b1q.x); o.y = __fadd_rn(o.y, b1q.y); o.z = __fadd_rn(o.z, b1q.z); o.w = __fadd_rn(o.w, b1q.w);
-            reinterpret_cast<float4*>(b1s)[tid] = o;
-          }
-          if (4 * tid < C) {
-            float4 o = reinterpret_cast<const float4*>(b2n + (s & 1) * kMaxC)[tid];
-            o.x = __fadd_rn(o.x, b2q.x); o.y = __fadd_rn(o.y, b2q.y); o.z = __fadd_rn(o.z, b2q.z); o.w = __fadd_rn(o.w, b2q.w);
-            reinterpret_cast<float4*>(b2s)[tid] = o;
           }
         }
       }
@@ -515,8 +513,17 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
       }
       __syncthreads();
     }
-    if (g == book && tid == 0 && s > 0 && a.train && !a.has_sx) a.step_out[s - 1] = pending_step;
-    if (ahead) dtfe::cp_async_wait<0>();     // the fetch for the next step has landed before anyone pushes (phase C)
+    if (fetches) {
+      // The fetch for the next step has landed before anyone pushes (phase C starts behind barrier 2);
+      // republish it locally for every row CTA.
+      dtfe::cp_async_wait<0>();
+      float4* m4 = reinterpret_cast<float4*>(a.mirror + ((s + 1) & 1) * dWords);
+#pragma unroll
+      for (int k = 0; k < kFetchSlots; ++k) {       // every thread republishes the quads it fetched itself
+        const int slot = tid + k * kThreads, f = fidx + slot * nfetch;
+        if (4 * f < dWords) __stcg(m4 + f, reinterpret_cast<const float4*>(stg)[slot]);
+      }
+    }
     DBG_STAMP(3);
     grid_barrier(a.sync, bar_target, NC);
     DBG_STAMP(4);
@@ -542,7 +549,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
       //   group 6      (ahead mode) the W1 slice for the next step: fetched BEFORE this CTA pushes to it (only
       //                this CTA of this worker does), its own update is added in shared memory below.
       constexpr int kChunks = 4;
-      const int rb = (((B + kChunks - 1) / kChunks) + 3) & ~3;     // rows per chunk, multiple of 4 (16-byte starts)
+      const int rb = (((B + kChunks - 1) / kChunks) + 7) & ~7;     // rows per chunk: 16-byte starts, whole rounds of 8 warps
       // Who computes the small gradients: the helper CTAs (the ones without a W1 slice) when there are enough
       // of them, in parallel with the slice CTAs' dW1; otherwise every CTA, after its dW1.
       const int nhelp = (int)NC - (int)G;
@@ -559,24 +566,29 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
       if (does_small) dtfe::cta_copy_async(dZs, a.dZ, B * C, tid, kThreads);
       dtfe::cp_async_commit();
       // H and dA columns of this CTA's hidden units (local loads: issued before the fetch from the peer)
-      float hcol0[4] = {0.f, 0.f, 0.f, 0.f}, hcol1[4] = {0.f, 0.f, 0.f, 0.f}, dacol[4] = {0.f, 0.f, 0.f, 0.f};
+      // (column loads touch one 32-byte sector per row: one warp fetches a column for the whole CTA)
+      float hreg[4] = {0.f, 0.f, 0.f, 0.f}, dacol0[4] = {0.f, 0.f, 0.f, 0.f}, dacol1[4] = {0.f, 0.f, 0.f, 0.f};
       if (does_small) {
+        const int tw = warp == 0 ? t0 : t1;
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
           int b = lane + 32 * i;
-          if (b < B && t0 < H) hcol0[i] = __ldcg(a.Hbuf + (long)b * H + t0);
-          if (b < B && t1 < H) hcol1[i] = __ldcg(a.Hbuf + (long)b * H + t1);
-          if (warp == 5 && b < B && t0 < H) dacol[i] = __ldcg(a.dA + (long)b * H + t0);
+          if (warp < 2 && b < B && tw < H) hreg[i] = __ldcg(a.Hbuf + (long)b * H + tw);
+          if (warp == 5 && b < B && t0 < H) dacol0[i] = __ldcg(a.dA + (long)b * H + t0);
+          if (warp == 5 && b < B && t1 < H) dacol1[i] = __ldcg(a.dA + (long)b * H + t1);
         }
       }
       if (ahead && s + 1 < a.nsteps) dtfe::cta_copy_async(Ws, a.W1 + (long)k0 * H, nW1, tid, kThreads);
       dtfe::cp_async_commit();
-      // dW1 rows [k0, k0+KS): a warp owns 4 consecutive rows (one broadcast float4 of X per batch row)
-      // and a contiguous block of columns, so each dA value fetched from shared memory feeds 4 FMAs.
-      float acc0[4] = {0.f, 0.f, 0.f, 0.f}, acc1[4] = {0.f, 0.f, 0.f, 0.f};
-      float bcc0[4] = {0.f, 0.f, 0.f, 0.f}, bcc1[4] = {0.f, 0.f, 0.f, 0.f};
+      // dW1 = Xslice^T . dA for rows [k0, k0+KS).  Warp w takes every 8th batch row: two broadcast float4 of X
+      // and one dA row (4 columns per lane) feed 4*KS FMAs, like phase A.  The eight per-warp partial tiles
+      // meet in shared memory, where every thread sums - in fixed order - the elements it owns and pushes.
       if (slice) {
-        const float* xp = Xs + wgrp * 4;
+        float acc[KS][4];
+#pragma unroll
+        for (int kk = 0; kk < KS; ++kk)
+#pragma unroll
+          for (int jj = 0; jj < 4; ++jj) acc[kk][jj] = 0.f;
         for (int c = 0; c < kChunks; ++c) {
           switch (c) {                            // chunk c has landed: all but the (kChunks + 1 - c) newer groups
             case 0: dtfe::cp_async_wait<kChunks + 1>(); break;
@@ -586,48 +598,47 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
           }
           __syncthreads();
           if (c == 0) DBG_STAMP(12);
-          int b = min(B, c * rb);
-          const int bend = min(B, b + rb);
-          for (; b + 2 <= bend; b += 2) {         // two independent chains
-            float4 xa = *reinterpret_cast<const float4*>(xp + b * KS);
-            float4 xb = *reinterpret_cast<const float4*>(xp + (b + 1) * KS);
-            float da0 = wv0 ? dAs[b * HP + wj0] : 0.f, db0 = wv0 ? dAs[(b + 1) * HP + wj0] : 0.f;
-            acc0[0] = fmaf(xa.x, da0, acc0[0]); acc0[1] = fmaf(xa.y, da0, acc0[1]);
-            acc0[2] = fmaf(xa.z, da0, acc0[2]); acc0[3] = fmaf(xa.w, da0, acc0[3]);
-            bcc0[0] = fmaf(xb.x, db0, bcc0[0]); bcc0[1] = fmaf(xb.y, db0, bcc0[1]);
-            bcc0[2] = fmaf(xb.z, db0, bcc0[2]); bcc0[3] = fmaf(xb.w, db0, bcc0[3]);
-            if (kParts < 4) {                     // wide parts (KS = 16): a second column per lane
-              float da1 = wv1 ? dAs[b * HP + wj1] : 0.f, db1 = wv1 ? dAs[(b + 1) * HP + wj1] : 0.f;
-              acc1[0] = fmaf(xa.x, da1, acc1[0]); acc1[1] = fmaf(xa.y, da1, acc1[1]);
-              acc1[2] = fmaf(xa.z, da1, acc1[2]); acc1[3] = fmaf(xa.w, da1, acc1[3]);
-              bcc1[0] = fmaf(xb.x, db1, bcc1[0]); bcc1[1] = fmaf(xb.y, db1, bcc1[1]);
-              bcc1[2] = fmaf(xb.z, db1, bcc1[2]); bcc1[3] = fmaf(xb.w, db1, bcc1[3]);
+          const int b0 = min(B, c * rb), bend = min(B, b0 + rb);
+          for (int b = b0 + warp; b < bend; b += 8) {
+            float x[KS], da[4];
+#pragma unroll
+            for (int q = 0; q < KS / 4; ++q) {
+              float4 v = *reinterpret_cast<const float4*>(Xs + b * KS + 4 * q);
+              x[4 * q] = v.x; x[4 * q + 1] = v.y; x[4 * q + 2] = v.z; x[4 * q + 3] = v.w;
             }
-          }
-          for (; b < bend; ++b) {
-            float4 xa = *reinterpret_cast<const float4*>(xp + b * KS);
-            float da0 = wv0 ? dAs[b * HP + wj0] : 0.f;
-            acc0[0] = fmaf(xa.x, da0, acc0[0]); acc0[1] = fmaf(xa.y, da0, acc0[1]);
-            acc0[2] = fmaf(xa.z, da0, acc0[2]); acc0[3] = fmaf(xa.w, da0, acc0[3]);
-            if (kParts < 4) {
-              float da1 = wv1 ? dAs[b * HP + wj1] : 0.f;
-              acc1[0] = fmaf(xa.x, da1, acc1[0]); acc1[1] = fmaf(xa.y, da1, acc1[1]);
-              acc1[2] = fmaf(xa.z, da1, acc1[2]); acc1[3] = fmaf(xa.w, da1, acc1[3]);
+#pragma unroll
+            for (int jj = 0; jj < 4; ++jj) {
+              int j = lane + 32 * jj;
+              da[jj] = (j < H) ? dAs[b * HP + j] : 0.f;
             }
+#pragma unroll
+            for (int kk = 0; kk < KS; ++kk)
+#pragma unroll
+              for (int jj = 0; jj < 4; ++jj) acc[kk][jj] = fmaf(x[kk], da[jj], acc[kk][jj]);
           }
         }
+        float* pt = dwp + warp * (KS * kMaxH);
+#pragma unroll
+        for (int kk = 0; kk < KS; ++kk)
+#pragma unroll
+          for (int jj = 0; jj < 4; ++jj) pt[kk * kMaxH + lane + 32 * jj] = acc[kk][jj];
       }
       DBG_STAMP(13);
-      dtfe::cp_async_wait<1>();                   // dZ has landed (this thread's quads) ...
-      __syncthreads();                            // ... and everybody else's
       if (does_small) {
+        if (warp < 2) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) red[warp * kMaxB + lane + 32 * i] = hreg[i];   // H columns t0, t1
+        }
+        dtfe::cp_async_wait<1>();                 // dZ has landed (this thread's quads) ...
+        __syncthreads();                          // ... and everybody else's
+        if (!slice) DBG_STAMP(12);
         // small gradients: every warp takes one or two classes of the dW2 row; warp 5 also sums the dA column
         for (int tt = t0, rnd = 0; tt < H; tt += tstride, ++rnd) {
           float hc[4];
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
             int b = lane + 32 * i;
-            hc[i] = rnd == 0 ? hcol0[i] : rnd == 1 ? hcol1[i] : (b < B ? __ldcg(a.Hbuf + (long)b * H + tt) : 0.f);
+            hc[i] = rnd < 2 ? red[rnd * kMaxB + b] : (b < B ? __ldcg(a.Hbuf + (long)b * H + tt) : 0.f);
           }
           for (int c = warp; c < C; c += 8) {     // dW2[tt][c] = sum_b H[b][tt] * dZ[b][c]
             float v = 0.f;
@@ -641,7 +652,8 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
           }
           if (warp == 5) {                        // db1[tt] = sum_b dA[b][tt]
             float v = 0.f;
-            if (rnd == 0) v = (dacol[0] + dacol[1]) + (dacol[2] + dacol[3]);
+            if (rnd == 0) v = (dacol0[0] + dacol0[1]) + (dacol0[2] + dacol0[3]);
+            else if (rnd == 1) v = (dacol1[0] + dacol1[1]) + (dacol1[2] + dacol1[3]);
             else for (int b = lane; b < B; b += 32) v += __ldcg(a.dA + (long)b * H + tt);
             v = dtfe::warp_sum(v);
             if (lane == 0) emit_small(a.b1, a.gb1, delta ? delta + dOffB1 : nullptr, tt, v, nlr, a.atomic);
@@ -657,16 +669,20 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
         }
       }
       DBG_STAMP(14);
-      if (ahead) {                                // next step's W1 slice is in Ws before this CTA pushes to it
-        dtfe::cp_async_wait<0>();
-        __syncthreads();
-      }
+      dtfe::cp_async_wait<0>();                   // (ahead) next step's W1 slice is in Ws before this CTA pushes to it
+      __syncthreads();                            // ... and all eight partial dW1 tiles are in shared memory
       if (slice) {
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           int k = k0 + wgrp * 4 + q;
           if (k < D) {
-            const float g0 = acc0[q] + bcc0[q], g1 = acc1[q] + bcc1[q];
+            float g0 = 0.f, g1 = 0.f;
+            const float* pq = dwp + (wgrp * 4 + q) * kMaxH;
+#pragma unroll
+            for (int w = 0; w < 8; ++w) {
+              if (wv0) g0 += pq[w * (KS * kMaxH) + wj0];
+              if (kParts < 4 && wv1) g1 += pq[w * (KS * kMaxH) + wj1];
+            }
             if (wv0) emit(a.W1, a.gW1, (long)k * H + wj0, g0, nlr, a.atomic);
             if (kParts < 4 && wv1) emit(a.W1, a.gW1, (long)k * H + wj1, g1, nlr, a.atomic);
             if (ahead) {        // fetched value + own update = what the shard holds (bitwise, absent other writers)
@@ -681,6 +697,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
         if (!ahead && !a.has_sx) fetch_w1();
       }
       DBG_STAMP(5);
+      if (g == book && tid == 0 && s > 0 && !a.has_sx) a.step_out[s - 1] = pending_step;
       // No per-step completion handshake: the next grid barrier (or the exit handshake below) orders all
       // of this step's pushes before the global_step increment that counts them.
       __syncthreads();                            // dAs / Xs are rewritten by the next step
@@ -790,8 +807,8 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
 template <int KS>
 constexpr size_t smem_floats() {
   return (size_t)kMaxB * KS + (size_t)KS * kMaxH + kMaxH * kMaxC + kMaxH + kMaxC + 2 * kMaxH + 8 * kMaxC +
-         2 * kMaxC + kThreads + kMaxB * kMaxC + (size_t)kMaxB * kMaxH + 2 * (size_t)kMaxH * kMaxC + 2 * kMaxH +
-         2 * kMaxC;
+         2 * kMaxC + kThreads + kMaxB * kMaxC + (size_t)kMaxB * kMaxH + (size_t)kMaxH * kMaxC + kMaxH + kMaxC +
+         8 * (size_t)KS * kMaxH;
 }
 
 }  // namespace
@@ -800,10 +817,10 @@ constexpr size_t smem_floats() {
 DTFE_API int dtfe_mlp2_step_grid(int D, int ks) { return (D + ks - 1) / ks; }
 
 // Element counts (4-byte words) of the scratch regions, in the order the workspace is carved:
-// part[G*B*H] | dA[B*H] | Hbuf[B*H] | dZ[B*C] | rowloss[B] | rowcorrect[B] | delta[H*C+H+C] | sync[4]
+// part[G*B*H] | dA[B*H] | Hbuf[B*H] | dZ[B*C] | rowloss[B] | rowcorrect[B] | delta | mirror[2] | sync[4]
 DTFE_API size_t dtfe_mlp2_step_workspace_words(int B, int D, int H, int C, int ks) {
   size_t G = (size_t)((D + ks - 1) / ks);
-  size_t w = G * B * H + 2 * (size_t)B * H + (size_t)B * C + 2 * (size_t)B + ((size_t)H * C + H + C + 12) + 4;
+  size_t w = G * B * H + 2 * (size_t)B * H + (size_t)B * C + 2 * (size_t)B + 3 * ((size_t)H * C + H + C + 12) + 4;
   return (w + 3) / 4 * 4 + 32;
 }
 
@@ -831,7 +848,10 @@ static int mlp2_fill(const Mlp2Launch& L, Mlp2Args& a) {
   a.rowloss = w;            w += L.B;
   a.rowcorrect = (int*)w;   w += L.B;
   w = (float*)(((uintptr_t)w + 15) & ~(uintptr_t)15);
-  a.delta = w;              w += (size_t)L.H * L.C + L.H + L.C + 12;
+  const size_t small_words = (((size_t)L.H * L.C + 3) & ~(size_t)3) + (((size_t)L.H + 3) & ~(size_t)3) +
+                             (((size_t)L.C + 3) & ~(size_t)3);   // W2 | b1 | b2, each part on a float4
+  a.delta = w;              w += small_words;
+  a.mirror = w;             w += 2 * small_words;
   a.sync = (unsigned*)w;
   a.nslices = (int)G;
   a.loss_out = L.loss_out; a.acc_out = L.acc_out; a.step_out = L.step_out;

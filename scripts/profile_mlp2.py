@@ -65,8 +65,16 @@ if "--stamps" in sys.argv and rank == world - 1:
     seg("  C wait W1 fetch + push", 13, 5, sl)
     hp = slice(tr.fused.k.slices, G)
     if G > tr.fused.k.slices:
-        seg("C helpers: small grads", 4, 5, hp)
+        seg("C helpers: wait dZ", 4, 12, hp)
+        seg("C helpers: small grads", 12, 14, hp)
+        seg("C helpers: tail", 14, 5, hp)
     seg("  C closing __syncthreads", 5, 7)
+    bt = ((t[:, :, 3] - t[:, :, 2]) / 1e3).mean(axis=0)          # phase B duration per CTA
+    worst = bt.argsort()[::-1][:6]
+    print("slowest CTAs in phase B:", ", ".join(f"cta {int(c)}: {bt[c]:.2f} us" for c in worst))
+    ct = ((t[:, :, 5] - t[:, :, 4]) / 1e3).mean(axis=0)
+    worst = ct.argsort()[::-1][:6]
+    print("slowest CTAs in phase C:", ", ".join(f"cta {int(c)}: {ct[c]:.2f} us" for c in worst))
     step = (t[1:, :, 0] - t[:-1, :, 0]) / 1e3
     print(f"step period             {step.mean():6.2f} us")
 
