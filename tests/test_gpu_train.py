@@ -78,6 +78,80 @@ def test_fused_step_matches_oracle(ks, atomic):
     store.close()
 
 
+@pytest.mark.parametrize("dims,B,ks", [((50, 30, 7), 33, 8), ((100, 128, 16), 128, 8), ((130, 20, 3), 5, 16)])
+def test_fused_step_odd_shapes_match_oracle(dims, B, ks):
+    """Shapes that are not whole float4s / whole K slices: partial cp.async quads, the scalar split-K
+    reduction, a short last W1 slice, grids with and without helper CTAs."""
+    from distributedtensorflowexample_b200.data import synthetic_arrays
+    from distributedtensorflowexample_b200.train.gpu_step import FusedMlp2Stepper
+    spec = MLPSpec(dims)
+    model, store, names = _store(spec, seed=2)
+    params_np = [store.read(n).astype(np.float64) for n in names]
+    x, y = synthetic_arrays(400, seed=7, num_classes=dims[-1], dim=dims[0])
+    y = y.astype(np.int32)
+    X = torch.tensor(x, device="cuda"); Y = torch.tensor(y, device="cuda")
+    lr, nsteps = 0.05, 5
+    st = FusedMlp2Stepper(spec, B, [store.tensor(n) for n in names], store.tensor("global/global_step"), lr,
+                          "cuda:0", max_steps_per_launch=nsteps, ks=ks)
+    idx = np.random.default_rng(4).integers(0, x.shape[0], size=nsteps * B).astype(np.int32)
+    st.run(X, Y, nsteps=nsteps, batch_idx=torch.tensor(idx, device="cuda"))
+    torch.cuda.synchronize()
+    losses = []
+    for s in range(nsteps):
+        rows = idx[s * B:(s + 1) * B]
+        losses.append(oracle.sgd_step(params_np, x[rows].astype(np.float64), y[rows], lr)[0])
+    np.testing.assert_allclose(st.loss[:nsteps].cpu().numpy(), losses, rtol=2e-4, atol=2e-4)
+    assert st.step[:nsteps].cpu().tolist() == list(range(nsteps))
+    for n, p in zip(names, params_np):
+        np.testing.assert_allclose(store.read(n), p, rtol=1e-3, atol=2e-4)
+    store.close()
+
+
+_PULL_MODE_SCRIPT = r"""
+import sys, numpy as np, torch
+sys.path.insert(0, {root!r})
+from distributedtensorflowexample_b200.models.mlp import reference_mlp_spec
+from distributedtensorflowexample_b200.train.replica import build_replicated_model
+from distributedtensorflowexample_b200.parallel.ps import PeerParamStore
+from distributedtensorflowexample_b200.train.gpu_step import FusedMlp2Stepper
+from distributedtensorflowexample_b200.data import synthetic_arrays
+spec = reference_mlp_spec()
+model = build_replicated_model(spec, num_ps=1)
+store = PeerParamStore(model.global_all, 1, torch.device("cuda:0")); store.allocate()
+store.initialize(np.random.default_rng(0))
+names = [v.name for v in model.global_trainable]
+x, y = synthetic_arrays(1000, seed=5)
+X = torch.tensor(x, device="cuda"); Y = torch.tensor(y.astype(np.int32), device="cuda")
+st = FusedMlp2Stepper(spec, 100, [store.tensor(n) for n in names], store.tensor("global/global_step"), 0.05,
+                      "cuda:0", max_steps_per_launch=12)
+idx = np.random.default_rng(1).integers(0, 1000, size=1200).astype(np.int32)
+st.run(X, Y, nsteps=12, batch_idx=torch.tensor(idx, device="cuda"))
+st.run(X, Y, nsteps=3, batch_idx=torch.tensor(idx[:300], device="cuda"))
+torch.cuda.synchronize()
+np.savez({out!r}, loss=st.loss[:3].cpu().numpy(), **{{n.replace("/", "."): store.read(n) for n in names}})
+"""
+
+
+def test_fused_pull_ahead_is_bitwise_the_direct_pull(tmp_path):
+    """With one worker the pull that runs a step ahead (fetch before the push + own update added locally)
+    must give exactly the bits of the pull that re-reads the shard after the push."""
+    import os, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    outs = []
+    for mode in ("ahead", "direct"):
+        out = str(tmp_path / f"{mode}.npz")
+        env = dict(os.environ)
+        env.pop("DTFE_MLP2_NO_AHEAD", None)
+        if mode == "direct":
+            env["DTFE_MLP2_NO_AHEAD"] = "1"
+        subprocess.run([sys.executable, "-c", _PULL_MODE_SCRIPT.format(root=root, out=out)], check=True, env=env,
+                       timeout=300)
+        outs.append(np.load(out))
+    assert sorted(outs[0].files) == sorted(outs[1].files) and len(outs[0].files) == 5
+    for k in outs[0].files:
+        np.testing.assert_array_equal(outs[0][k], outs[1][k], err_msg=k)
+
+
 def test_fused_single_step_contiguous_batch_and_eval_mode():
     from distributedtensorflowexample_b200.train.gpu_step import FusedMlp2Stepper
     spec = reference_mlp_spec()
