@@ -88,18 +88,22 @@ def run_mnist(args, rank: int, world: int, dev, ClockSampler) -> int:
         xs = [torch.from_numpy(x[i * B:(i + 1) * B].copy()).pin_memory() for i in range(ring)]
         ys = [torch.from_numpy(y[i * B:(i + 1) * B].astype(np.int32)).pin_memory() for i in range(ring)]
         loss_host = torch.zeros(max(Ke, W), dtype=torch.float32).pin_memory()
-        tr.train_host_batches([xs[s % ring] for s in range(W)], [ys[s % ring] for s in range(W)], loss_host)
+        espl = max(1, min(16, getattr(args, "e2e_steps_per_launch", 4)))
+        tr.train_host_batches([xs[s % ring] for s in range(W)], [ys[s % ring] for s in range(W)], loss_host,
+                              steps_per_launch=espl)
         _barrier(world)
         xl, yl = [xs[s % ring] for s in range(Ke)], [ys[s % ring] for s in range(Ke)]
         t0 = time.perf_counter()
-        tr.train_host_batches(xl, yl, loss_host)
+        tr.train_host_batches(xl, yl, loss_host, steps_per_launch=espl)
         torch.cuda.synchronize()
         t1 = time.perf_counter()
         sec = _max_over_ranks(t1 - t0, world, dev)
         assert np.isfinite(loss_host[:Ke].numpy()).all()
         e2e = {"value": world * B * Ke / sec, "unit": "examples/sec", "steps": Ke,
                "h2d_bytes_per_step": tr.h2d_bytes_per_step(), "d2h_bytes_per_step": tr.d2h_bytes_per_step(),
-               "steps_per_launch": 4, "timing": "host wall clock around GpuTrainer.train_host_batches (every step: H2D copy of its batch from pinned memory and D2H read of its loss; 4 consecutive steps share a kernel launch), max over ranks"}
+               "steps_per_launch": espl,
+               "timing": "host wall clock around GpuTrainer.train_host_batches (every step: H2D copy of its batch from "
+                         f"pinned memory and D2H read of its loss; {espl} consecutive steps share a kernel launch), max over ranks"}
         _barrier(world)
 
     final_step = int(gs.item())
