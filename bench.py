@@ -39,7 +39,7 @@ def parse_args():
                     help="training steps fused into one persistent-kernel launch (0 = auto)")
     ap.add_argument("--engine", default="auto", choices=["auto", "fused", "layerwise", "tc"])
     ap.add_argument("--e2e-steps", type=int, default=0, help="steps of the host-fed end-to-end measurement (0 = --steps)")
-    ap.add_argument("--e2e-steps-per-launch", type=int, default=4,
+    ap.add_argument("--e2e-steps-per-launch", type=int, default=8,
                     help="host-fed steps that share one kernel launch in the end-to-end measurement (1..16)")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()

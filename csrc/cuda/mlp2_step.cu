@@ -992,9 +992,11 @@ struct HostFeed {
   int B, D, S, dev;                    // S = training steps (host batches) fused into one kernel launch
   float* xs[2];                        // staging: S batches per slot
   int* ys[2];
+  int* ypin[2];                        // pinned host staging: the S label vectors of a group, gathered for ONE copy
   float* out[2];                       // per slot: loss[S] | acc[S] | step[S] (int)
-  cudaStream_t copy, back;             // H2D and D2H side streams
-  cudaEvent_t copied[2], done[2], readback[2];
+  cudaStream_t copy, copy2, back;      // two H2D side streams (a copy has ~4 us of fixed cost on its engine:
+                                       // alternating streams lets two engines overlap it), one D2H stream
+  cudaEvent_t copied[2], copied2[2], done[2], readback[2];
 };
 }  // namespace
 
@@ -1008,12 +1010,15 @@ DTFE_API int dtfe_hostfeed_create(int B, int D, int steps_per_launch, void** out
   for (int i = 0; i < 2; ++i) {
     DTFE_CUDA_CHECK(cudaMalloc(&h->xs[i], (size_t)h->S * B * D * sizeof(float)));
     DTFE_CUDA_CHECK(cudaMalloc(&h->ys[i], (size_t)h->S * B * sizeof(int)));
+    DTFE_CUDA_CHECK(cudaHostAlloc((void**)&h->ypin[i], (size_t)h->S * B * sizeof(int), cudaHostAllocDefault));
     DTFE_CUDA_CHECK(cudaMalloc(&h->out[i], 3 * kFeedMaxSteps * sizeof(float)));
     DTFE_CUDA_CHECK(cudaEventCreateWithFlags(&h->copied[i], cudaEventDisableTiming));
+    DTFE_CUDA_CHECK(cudaEventCreateWithFlags(&h->copied2[i], cudaEventDisableTiming));
     DTFE_CUDA_CHECK(cudaEventCreateWithFlags(&h->done[i], cudaEventDisableTiming));
     DTFE_CUDA_CHECK(cudaEventCreateWithFlags(&h->readback[i], cudaEventDisableTiming));
   }
   DTFE_CUDA_CHECK(cudaStreamCreateWithFlags(&h->copy, cudaStreamNonBlocking));
+  DTFE_CUDA_CHECK(cudaStreamCreateWithFlags(&h->copy2, cudaStreamNonBlocking));
   DTFE_CUDA_CHECK(cudaStreamCreateWithFlags(&h->back, cudaStreamNonBlocking));
   *out = h;
   return 0;
@@ -1023,10 +1028,12 @@ DTFE_API int dtfe_hostfeed_destroy(void* handle) {
   HostFeed* h = static_cast<HostFeed*>(handle);
   if (!h) return 0;
   for (int i = 0; i < 2; ++i) {
-    cudaFree(h->xs[i]); cudaFree(h->ys[i]); cudaFree(h->out[i]);
-    cudaEventDestroy(h->copied[i]); cudaEventDestroy(h->done[i]); cudaEventDestroy(h->readback[i]);
+    cudaFree(h->xs[i]); cudaFree(h->ys[i]); cudaFree(h->out[i]); cudaFreeHost(h->ypin[i]);
+    cudaEventDestroy(h->copied[i]); cudaEventDestroy(h->copied2[i]);
+    cudaEventDestroy(h->done[i]); cudaEventDestroy(h->readback[i]);
   }
   cudaStreamDestroy(h->copy);
+  cudaStreamDestroy(h->copy2);
   cudaStreamDestroy(h->back);
   delete h;
   return 0;
@@ -1050,18 +1057,30 @@ DTFE_API int dtfe_mlp2_train_host(void* handle, const dtfe_mlp2_launch* launch, 
   Mlp2Args a{};
   const size_t xbytes = (size_t)h->B * h->D * sizeof(float), ybytes = (size_t)h->B * sizeof(int);
   int group = 0, last_slot = 0, last_n = 0;
+  static const bool feed_timing = getenv("DTFE_FEED_TIMING") != nullptr;   // debugging aid: host issue cost
+  struct timespec ts0, ts1;
+  if (feed_timing) clock_gettime(CLOCK_MONOTONIC, &ts0);
   for (int i = 0; i < nsteps; i += h->S, ++group) {
     const int s = group & 1;
     const int n = nsteps - i < h->S ? nsteps - i : h->S;
     // H2D: the staging slot is free once the launch that last read it has finished
     DTFE_CUDA_CHECK(cudaStreamWaitEvent(h->copy, h->done[s], 0));
+    DTFE_CUDA_CHECK(cudaStreamWaitEvent(h->copy2, h->done[s], 0));
+    // A copy costs its engine ~4 us before the first byte moves (measured, scripts/h2d_probe.py), which
+    // is a third of a step: the 400-byte label vectors of the group are gathered on the host and go up in
+    // one copy; every image batch keeps its own copy, alternating between the two copy streams.
+    DTFE_CUDA_CHECK(cudaEventSynchronize(h->copied2[s]));      // the copy that last read this ypin slot is done
+    for (int j = 0; j < n; ++j) memcpy(h->ypin[s] + (size_t)j * h->B, y_host[i + j], ybytes);
     for (int j = 0; j < n; ++j) {
-      DTFE_CUDA_CHECK(cudaMemcpyAsync(h->xs[s] + (size_t)j * h->B * h->D, x_host[i + j], xbytes, cudaMemcpyHostToDevice, h->copy));
-      DTFE_CUDA_CHECK(cudaMemcpyAsync(h->ys[s] + (size_t)j * h->B, y_host[i + j], ybytes, cudaMemcpyHostToDevice, h->copy));
+      cudaStream_t cx = (j & 1) ? h->copy2 : h->copy;
+      DTFE_CUDA_CHECK(cudaMemcpyAsync(h->xs[s] + (size_t)j * h->B * h->D, x_host[i + j], xbytes, cudaMemcpyHostToDevice, cx));
     }
+    DTFE_CUDA_CHECK(cudaMemcpyAsync(h->ys[s], h->ypin[s], (size_t)n * ybytes, cudaMemcpyHostToDevice, h->copy2));
     DTFE_CUDA_CHECK(cudaEventRecord(h->copied[s], h->copy));
+    DTFE_CUDA_CHECK(cudaEventRecord(h->copied2[s], h->copy2));
     // steps: need their batches, and the slot's outputs must have been read back
     DTFE_CUDA_CHECK(cudaStreamWaitEvent(st, h->copied[s], 0));
+    DTFE_CUDA_CHECK(cudaStreamWaitEvent(st, h->copied2[s], 0));
     DTFE_CUDA_CHECK(cudaStreamWaitEvent(st, h->readback[s], 0));
     L.X = h->xs[s]; L.labels = h->ys[s]; L.nsteps = n;
     L.loss_out = h->out[s]; L.acc_out = h->out[s] + kFeedMaxSteps;
@@ -1075,6 +1094,12 @@ DTFE_API int dtfe_mlp2_train_host(void* handle, const dtfe_mlp2_launch* launch, 
     DTFE_CUDA_CHECK(cudaMemcpyAsync(loss_host + i, h->out[s], (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, h->back));
     DTFE_CUDA_CHECK(cudaEventRecord(h->readback[s], h->back));
     last_slot = s; last_n = n;
+  }
+  if (feed_timing && nsteps > 0) {
+    clock_gettime(CLOCK_MONOTONIC, &ts1);
+    fprintf(stderr, "dtfe_mlp2_train_host: issued %d steps in %.1f us of host time (%.2f us/step)\n", nsteps,
+            ((ts1.tv_sec - ts0.tv_sec) * 1e9 + (ts1.tv_nsec - ts0.tv_nsec)) * 1e-3,
+            ((ts1.tv_sec - ts0.tv_sec) * 1e9 + (ts1.tv_nsec - ts0.tv_nsec)) * 1e-3 / nsteps);
   }
   if (nsteps > 0) {
     DTFE_CUDA_CHECK(cudaStreamWaitEvent(st, h->readback[0], 0));

@@ -88,7 +88,7 @@ def run_mnist(args, rank: int, world: int, dev, ClockSampler) -> int:
         xs = [torch.from_numpy(x[i * B:(i + 1) * B].copy()).pin_memory() for i in range(ring)]
         ys = [torch.from_numpy(y[i * B:(i + 1) * B].astype(np.int32)).pin_memory() for i in range(ring)]
         loss_host = torch.zeros(max(Ke, W), dtype=torch.float32).pin_memory()
-        espl = max(1, min(16, getattr(args, "e2e_steps_per_launch", 4)))
+        espl = max(1, min(16, getattr(args, "e2e_steps_per_launch", 8)))
         tr.train_host_batches([xs[s % ring] for s in range(W)], [ys[s % ring] for s in range(W)], loss_host,
                               steps_per_launch=espl)
         _barrier(world)
