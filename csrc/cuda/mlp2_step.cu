@@ -981,22 +981,28 @@ DTFE_API int dtfe_mlp2_step_noalloc(const dtfe_mlp2_launch* launch, void* stream
 }
 
 // ---- host-fed training loop (the reference's feed_dict path, worker.py:133-137) -----------------
-// One call runs `nsteps` steps, each fed by its own batch in pinned host memory: the H2D copies go
-// through a private copy stream into two staging buffers (batch i+1 is copied while batch i
-// trains), the step kernel waits on the copy's event, and the step's loss is copied back D2H on the
-// compute stream.  Doing the loop here instead of in Python keeps the per-step host cost at a few
-// microseconds of driver calls.
+// One call runs `nsteps` steps, each fed by its own batch in pinned host memory.  Up to
+// `steps_per_launch` consecutive steps form a group that shares one kernel launch; groups go through a
+// ring of staging slots:
+//   copy stream     H2D of every image batch of the group (its own copy each) and ONE copy of the
+//                   group's label vectors, gathered on the host (a copy costs its engine ~4 us before
+//                   the first byte moves - scripts/h2d_probe.py - a third of a step);
+//   caller's stream the step kernel, waiting on exactly one event (the group's copies);
+//   back stream     D2H of the group's losses.
+// Slots are recycled by the HOST (cudaEventSynchronize on events that completed kFeedRing groups ago), so
+// the kernel stream waits on exactly one event per launch.  Doing the loop here instead of in Python keeps
+// the per-step host cost at one driver call (measured 1.6 us per step).
 namespace {
 constexpr int kFeedMaxSteps = 16;
+constexpr int kFeedRing = 4;
 struct HostFeed {
   int B, D, S, dev;                    // S = training steps (host batches) fused into one kernel launch
-  float* xs[2];                        // staging: S batches per slot
-  int* ys[2];
-  int* ypin[2];                        // pinned host staging: the S label vectors of a group, gathered for ONE copy
-  float* out[2];                       // per slot: loss[S] | acc[S] | step[S] (int)
-  cudaStream_t copy, copy2, back;      // two H2D side streams (a copy has ~4 us of fixed cost on its engine:
-                                       // alternating streams lets two engines overlap it), one D2H stream
-  cudaEvent_t copied[2], copied2[2], done[2], readback[2];
+  float* xs[kFeedRing];                // staging: S batches per slot
+  int* ys[kFeedRing];
+  int* ypin[kFeedRing];                // pinned host staging: the S label vectors of a group, gathered for ONE copy
+  float* out[kFeedRing];               // per slot: loss[S] | acc[S] | step[S] (int)
+  cudaStream_t copy, back;             // H2D and D2H side streams
+  cudaEvent_t copied[kFeedRing], done[kFeedRing], readback[kFeedRing];
 };
 }  // namespace
 
@@ -1007,18 +1013,16 @@ DTFE_API int dtfe_hostfeed_create(int B, int D, int steps_per_launch, void** out
   HostFeed* h = new HostFeed();
   h->B = B; h->D = D; h->S = steps_per_launch;
   DTFE_CUDA_CHECK(cudaGetDevice(&h->dev));
-  for (int i = 0; i < 2; ++i) {
+  for (int i = 0; i < kFeedRing; ++i) {
     DTFE_CUDA_CHECK(cudaMalloc(&h->xs[i], (size_t)h->S * B * D * sizeof(float)));
     DTFE_CUDA_CHECK(cudaMalloc(&h->ys[i], (size_t)h->S * B * sizeof(int)));
     DTFE_CUDA_CHECK(cudaHostAlloc((void**)&h->ypin[i], (size_t)h->S * B * sizeof(int), cudaHostAllocDefault));
     DTFE_CUDA_CHECK(cudaMalloc(&h->out[i], 3 * kFeedMaxSteps * sizeof(float)));
     DTFE_CUDA_CHECK(cudaEventCreateWithFlags(&h->copied[i], cudaEventDisableTiming));
-    DTFE_CUDA_CHECK(cudaEventCreateWithFlags(&h->copied2[i], cudaEventDisableTiming));
     DTFE_CUDA_CHECK(cudaEventCreateWithFlags(&h->done[i], cudaEventDisableTiming));
     DTFE_CUDA_CHECK(cudaEventCreateWithFlags(&h->readback[i], cudaEventDisableTiming));
   }
   DTFE_CUDA_CHECK(cudaStreamCreateWithFlags(&h->copy, cudaStreamNonBlocking));
-  DTFE_CUDA_CHECK(cudaStreamCreateWithFlags(&h->copy2, cudaStreamNonBlocking));
   DTFE_CUDA_CHECK(cudaStreamCreateWithFlags(&h->back, cudaStreamNonBlocking));
   *out = h;
   return 0;
@@ -1027,13 +1031,11 @@ DTFE_API int dtfe_hostfeed_create(int B, int D, int steps_per_launch, void** out
 DTFE_API int dtfe_hostfeed_destroy(void* handle) {
   HostFeed* h = static_cast<HostFeed*>(handle);
   if (!h) return 0;
-  for (int i = 0; i < 2; ++i) {
+  for (int i = 0; i < kFeedRing; ++i) {
     cudaFree(h->xs[i]); cudaFree(h->ys[i]); cudaFree(h->out[i]); cudaFreeHost(h->ypin[i]);
-    cudaEventDestroy(h->copied[i]); cudaEventDestroy(h->copied2[i]);
-    cudaEventDestroy(h->done[i]); cudaEventDestroy(h->readback[i]);
+    cudaEventDestroy(h->copied[i]); cudaEventDestroy(h->done[i]); cudaEventDestroy(h->readback[i]);
   }
   cudaStreamDestroy(h->copy);
-  cudaStreamDestroy(h->copy2);
   cudaStreamDestroy(h->back);
   delete h;
   return 0;
@@ -1042,10 +1044,7 @@ DTFE_API int dtfe_hostfeed_destroy(void* handle) {
 // launch: B/D/H/C/ks, parameter pointers, workspace, lr, atomic, train, remote are used; X/labels/
 // batch_idx/nsteps are supplied from the host batches.  Every step's batch is copied H2D from its own
 // pinned buffer (x_host[i], y_host[i]) and every step's loss is copied back D2H into loss_host[i]
-// (pinned); up to `steps_per_launch` consecutive steps share one kernel launch.  Three streams keep the
-// copies off the kernels' critical path: the H2D copies of the next group run under the current group's
-// kernel, and the D2H read of a group's losses runs under the next group's kernel.  On return the
-// caller's stream waits for the last read-back, so synchronising it makes every loss_host[i] valid.
+// (pinned).  The call returns after the last read-back has completed, so every loss_host[i] is valid.
 DTFE_API int dtfe_mlp2_train_host(void* handle, const dtfe_mlp2_launch* launch, const float* const* x_host,
                                   const int* const* y_host, int nsteps, float* loss_host, void* stream) {
   HostFeed* h = static_cast<HostFeed*>(handle);
@@ -1061,27 +1060,18 @@ DTFE_API int dtfe_mlp2_train_host(void* handle, const dtfe_mlp2_launch* launch, 
   struct timespec ts0, ts1;
   if (feed_timing) clock_gettime(CLOCK_MONOTONIC, &ts0);
   for (int i = 0; i < nsteps; i += h->S, ++group) {
-    const int s = group & 1;
+    const int s = group % kFeedRing;
     const int n = nsteps - i < h->S ? nsteps - i : h->S;
-    // H2D: the staging slot is free once the launch that last read it has finished
-    DTFE_CUDA_CHECK(cudaStreamWaitEvent(h->copy, h->done[s], 0));
-    DTFE_CUDA_CHECK(cudaStreamWaitEvent(h->copy2, h->done[s], 0));
-    // A copy costs its engine ~4 us before the first byte moves (measured, scripts/h2d_probe.py), which
-    // is a third of a step: the 400-byte label vectors of the group are gathered on the host and go up in
-    // one copy; every image batch keeps its own copy, alternating between the two copy streams.
-    DTFE_CUDA_CHECK(cudaEventSynchronize(h->copied2[s]));      // the copy that last read this ypin slot is done
+    // The slot is free once the launch that last read it has finished and its losses have been read back
+    // (kFeedRing groups ago: these return at once unless the host runs that far ahead of the GPU).
+    DTFE_CUDA_CHECK(cudaEventSynchronize(h->done[s]));
+    DTFE_CUDA_CHECK(cudaEventSynchronize(h->readback[s]));
     for (int j = 0; j < n; ++j) memcpy(h->ypin[s] + (size_t)j * h->B, y_host[i + j], ybytes);
-    for (int j = 0; j < n; ++j) {
-      cudaStream_t cx = (j & 1) ? h->copy2 : h->copy;
-      DTFE_CUDA_CHECK(cudaMemcpyAsync(h->xs[s] + (size_t)j * h->B * h->D, x_host[i + j], xbytes, cudaMemcpyHostToDevice, cx));
-    }
-    DTFE_CUDA_CHECK(cudaMemcpyAsync(h->ys[s], h->ypin[s], (size_t)n * ybytes, cudaMemcpyHostToDevice, h->copy2));
+    DTFE_CUDA_CHECK(cudaMemcpyAsync(h->ys[s], h->ypin[s], (size_t)n * ybytes, cudaMemcpyHostToDevice, h->copy));
+    for (int j = 0; j < n; ++j)
+      DTFE_CUDA_CHECK(cudaMemcpyAsync(h->xs[s] + (size_t)j * h->B * h->D, x_host[i + j], xbytes, cudaMemcpyHostToDevice, h->copy));
     DTFE_CUDA_CHECK(cudaEventRecord(h->copied[s], h->copy));
-    DTFE_CUDA_CHECK(cudaEventRecord(h->copied2[s], h->copy2));
-    // steps: need their batches, and the slot's outputs must have been read back
     DTFE_CUDA_CHECK(cudaStreamWaitEvent(st, h->copied[s], 0));
-    DTFE_CUDA_CHECK(cudaStreamWaitEvent(st, h->copied2[s], 0));
-    DTFE_CUDA_CHECK(cudaStreamWaitEvent(st, h->readback[s], 0));
     L.X = h->xs[s]; L.labels = h->ys[s]; L.nsteps = n;
     L.loss_out = h->out[s]; L.acc_out = h->out[s] + kFeedMaxSteps;
     L.step_out = reinterpret_cast<int*>(h->out[s] + 2 * kFeedMaxSteps);
@@ -1102,13 +1092,12 @@ DTFE_API int dtfe_mlp2_train_host(void* handle, const dtfe_mlp2_launch* launch, 
             ((ts1.tv_sec - ts0.tv_sec) * 1e9 + (ts1.tv_nsec - ts0.tv_nsec)) * 1e-3 / nsteps);
   }
   if (nsteps > 0) {
-    DTFE_CUDA_CHECK(cudaStreamWaitEvent(st, h->readback[0], 0));
-    DTFE_CUDA_CHECK(cudaStreamWaitEvent(st, h->readback[1], 0));
     // keep the caller-visible output views (launch->loss_out etc.) in step with the last step
     const float* o = h->out[last_slot];
     DTFE_CUDA_CHECK(cudaMemcpyAsync(launch->loss_out, o + last_n - 1, sizeof(float), cudaMemcpyDeviceToDevice, st));
     DTFE_CUDA_CHECK(cudaMemcpyAsync(launch->acc_out, o + kFeedMaxSteps + last_n - 1, sizeof(float), cudaMemcpyDeviceToDevice, st));
     DTFE_CUDA_CHECK(cudaMemcpyAsync(launch->step_out, o + 2 * kFeedMaxSteps + last_n - 1, sizeof(int), cudaMemcpyDeviceToDevice, st));
+    for (int k = 0; k < kFeedRing; ++k) DTFE_CUDA_CHECK(cudaEventSynchronize(h->readback[k]));
   }
   return 0;
 }

@@ -372,14 +372,27 @@ class Mlp2Step:
                 check(lib().dtfe_hostfeed_create(self.B, self.D, steps_per_launch, ctypes.byref(h)), "dtfe_hostfeed_create")
             self._feed, self._feed_spl = h, steps_per_launch
         n = len(x_host)
-        for x, y in zip(x_host, y_host):
-            if not (x.is_pinned() and y.is_pinned() and x.dtype == torch.float32 and y.dtype == torch.int32
-                    and x.is_contiguous() and tuple(x.shape) == (self.B, self.D)):
-                raise TypeError("host batches must be pinned, contiguous float32 [B,D] / int32 [B] tensors")
-        if not loss_host.is_pinned() or loss_host.numel() < n:
+        if len(y_host) != n:
+            raise ValueError("x_host and y_host must have one entry per step")
+        # Validate and resolve every DISTINCT tensor once (is_pinned() is a driver query of about a microsecond;
+        # a feed loop cycles through a ring of staging tensors, so per-entry checks would cost more than the
+        # driver calls of the loop itself).
+        xptr, yptr = {}, {}
+        for x in x_host:
+            if id(x) not in xptr:
+                if not (x.is_pinned() and x.dtype == torch.float32 and x.is_contiguous()
+                        and tuple(x.shape) == (self.B, self.D)):
+                    raise TypeError("host batches must be pinned, contiguous float32 [B,D] tensors")
+                xptr[id(x)] = x.data_ptr()
+        for y in y_host:
+            if id(y) not in yptr:
+                if not (y.is_pinned() and y.dtype == torch.int32 and y.is_contiguous() and y.numel() == self.B):
+                    raise TypeError("host labels must be pinned, contiguous int32 [B] tensors")
+                yptr[id(y)] = y.data_ptr()
+        if not loss_host.is_pinned() or loss_host.numel() < n or loss_host.dtype != torch.float32:
             raise TypeError("loss_host must be a pinned float32 tensor with one element per step")
-        XP = (_P * n)(*[x.data_ptr() for x in x_host])
-        YP = (_P * n)(*[y.data_ptr() for y in y_host])
+        XP = (_P * n)(*[xptr[id(x)] for x in x_host])
+        YP = (_P * n)(*[yptr[id(y)] for y in y_host])
         L = self._launch_struct(W1, b1, W2, b2, global_step, lr, atomic, True, remote)
         check(lib().dtfe_mlp2_train_host(self._feed, ctypes.byref(L), XP, YP, n, loss_host.data_ptr(), _stream()),
               "dtfe_mlp2_train_host")
