@@ -338,14 +338,25 @@ class Mlp2Step:
         words = lib().dtfe_mlp2_step_workspace_words(B, D, H, C, ks)
         self.workspace = torch.zeros(words, dtype=torch.float32, device=self.device)
         self.max_steps = max_steps
-        self.loss = torch.zeros(max_steps, dtype=torch.float32, device=self.device)
-        self.acc = torch.zeros(max_steps, dtype=torch.float32, device=self.device)
-        self.step = torch.zeros(max_steps, dtype=torch.int32, device=self.device)
+        # loss | acc | step share one buffer so a caller can bring all three to the host with one copy
+        self.out = torch.zeros(3 * max_steps, dtype=torch.float32, device=self.device)
+        self.loss = self.out[:max_steps]
+        self.acc = self.out[max_steps:2 * max_steps]
+        self.step = self.out[2 * max_steps:].view(torch.int32)
+        self._out_host = torch.zeros(3 * max_steps, dtype=torch.float32).pin_memory()
         self.slices = lib().dtfe_mlp2_step_grid(D, ks)
         with torch.cuda.device(self.device):
             self.grid = lib().dtfe_mlp2_step_ctas(B, D, H, ks)     # CTAs per launch (rows of the dbg stamp array)
         if self.grid < 0:
             check(1, "dtfe_mlp2_step_ctas")
+
+    def results_host(self, n: int):
+        """(loss[n], acc[n], step[n]) of the last launch as Python lists: one D2H copy, one synchronisation."""
+        self._out_host.copy_(self.out, non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()
+        m = self.max_steps
+        h = self._out_host
+        return h[:n].tolist(), h[m:m + n].tolist(), h[2 * m:2 * m + n].view(torch.int32).tolist()
 
     def _launch_struct(self, W1, b1, W2, b2, global_step, lr, atomic, train, remote, out_offset=0):
         L = _Mlp2Launch()

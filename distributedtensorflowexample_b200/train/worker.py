@@ -253,7 +253,10 @@ class Worker:
             if self.sync_group is not None and self.sync_group.aborted():
                 print("sync: a peer left, stopping", flush=True)
                 break
-            loss, acc, steps = loss_d.tolist(), acc_d.tolist(), step_d.tolist()   # one sync per launch
+            if tr.fused is not None and not separate_exchange:
+                loss, acc, steps = tr.fused.k.results_host(len(loss_d))            # one copy, one sync per launch
+            else:
+                loss, acc, steps = loss_d.tolist(), acc_d.tolist(), step_d.tolist()
             stop = False
             for l, a, s in zip(loss, acc, steps):
                 step = s
