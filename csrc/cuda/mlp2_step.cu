@@ -80,17 +80,21 @@ struct Mlp2Args {
   dtfe_sync_exchange sx;
 };
 
+// Release/acquire fences at GPU scope: __threadfence() is a sequentially consistent fence (MEMBAR.SC), which
+// the arrive/poll pattern does not need; fence.acq_rel is MEMBAR.ALL.
+__device__ __forceinline__ void fence_acq_rel_gpu() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
+
 __device__ __forceinline__ void grid_barrier(unsigned* ctr, unsigned& target, unsigned G) {
   __syncthreads();
   if (threadIdx.x == 0) {
     target += G;
-    __threadfence();
-    atomicAdd(ctr, 1u);
+    fence_acq_rel_gpu();
+    asm volatile("red.relaxed.gpu.global.add.u32 [%0], 1;" :: "l"(ctr) : "memory");
     unsigned v;
     do {
       asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
     } while (v < target);
-    __threadfence();
+    fence_acq_rel_gpu();
   }
   __syncthreads();
 }
