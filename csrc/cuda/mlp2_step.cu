@@ -155,8 +155,8 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
   float* dZs = red + kThreads;            // [B][C]
   float* dAs = dZs + kMaxB * kMaxC;       // [B][H]  (phase C)
   float* red_part = dAs;                  // [16][kMaxH] phase-B scratch, aliases dAs (never live together)
-  // ahead mode, bookkeeping CTA: the small parameters as fetched from the shard (cp.async destination),
-  // laid out like the delta / mirror buffers: W2 | b1 | b2, each part starting on a float4
+  // ahead mode, fetching CTAs: the quads of the small parameters this CTA fetched from the shard (cp.async
+  // destination, one slot per thread and round), republished in the mirror at the end of phase B
   float* stg = dAs + kMaxB * kMaxH;       // [kMaxH*kMaxC + kMaxH + kMaxC]
   float* dwp = stg + kMaxH * kMaxC + kMaxH + kMaxC;   // [8][KS][kMaxH] per-warp partial dW1 tiles (phase C)
 
