@@ -29,6 +29,7 @@ import numpy as np
 from ..utils import checkpoint as ckpt
 from ..utils.events import FileWriter, Summary, TAG_STEPS_PER_SEC
 from ..utils.native_io import SESSION_CHECKPOINT, SESSION_START
+from ..utils.tracing import get_tracer
 
 
 class Coordinator:
@@ -174,9 +175,12 @@ class Supervisor:
 
     # ---- services ---------------------------------------------------------------------------
     def save_checkpoint(self) -> str:
-        values = self.client.snapshot(self.saver.var_list)
+        tr = get_tracer()
+        with tr.span("checkpoint.snapshot", "checkpoint"):
+            values = self.client.snapshot(self.saver.var_list)
         step = int(np.asarray(values[self.global_step_name]).reshape(()))
-        path = self.saver.save(values, self.save_path, global_step=step)
+        with tr.span("checkpoint.write", "checkpoint", step=step):
+            path = self.saver.save(values, self.save_path, global_step=step)
         if self.summary_writer is not None:
             self.summary_writer.add_session_log(SESSION_CHECKPOINT, step, checkpoint_path=path)
         return path

@@ -30,6 +30,7 @@ from ..flags import FLAGS
 from ..models.mlp import spec_from_flags
 from ..utils.checkpoint import FastSaver
 from ..utils.events import FileWriter, training_summary
+from ..utils import tracing
 from .replica import build_replicated_model
 from .supervisor import Supervisor
 
@@ -182,7 +183,10 @@ class Worker:
                         graph_text=self.graph_text())
         self.sv = sv
         last_step = 0
-        with sv.managed_session() as sess:
+        if f.trace_file:
+            tracing.enable(process_name=f"worker:{self.task_index}")
+        self.tracer = tracing.get_tracer()
+        with self.tracer.span("managed_session", "session"), sv.managed_session() as sess:
             if sv.restored_from:
                 print(f"restored from {sv.restored_from}", flush=True)
             self._begin_time = time.time()
@@ -199,12 +203,16 @@ class Worker:
                     except Exception:
                         pass
         self.summary_writer.close()
+        if f.trace_file:
+            path = self.tracer.save(tracing.trace_path_for_task(f.trace_file, "worker", self.task_index))
+            print(f"trace written to {path}", flush=True)
         return last_step
 
     def _after_step(self, step: int, cost: float, acc: float, eval_fn) -> bool:
         """Summary + cadence rules of reference worker.py:139-159. Returns True to stop."""
         f = self.flags
-        self.summary_writer.add_summary(training_summary(cost, acc), step)
+        with self.tracer.span("summary", "host"):
+            self.summary_writer.add_summary(training_summary(cost, acc), step)
         if "kill_worker" in self.faults and self.faults["kill_worker"][0] == self.task_index \
                 and step >= self.faults["kill_worker"][1]:
             print(f"fault injection: worker {self.task_index} dies at step {step}", flush=True)
@@ -217,17 +225,22 @@ class Worker:
             self._start_time = time.time()
             self._start_step = step
         if step % f.eval_every == 0:
-            print("test accuracy: {}".format(eval_fn()), flush=True)
+            with self.tracer.span("eval", "host", step=step):
+                print("test accuracy: {}".format(eval_fn()), flush=True)
         return step >= f.training_steps
 
     def _loop_cpu(self, sv: Supervisor, dataset) -> int:
         eng, f = self.engine, self.flags
         step = 0
         while not sv.should_stop():
-            eng.sync_op()                                                        # reference :131
+            tr = self.tracer
+            with tr.span("sync_op(pull)", "step"):
+                eng.sync_op()                                                    # reference :131
             batch_x, batch_y = dataset.train.next_batch(f.batch_size)           # :133
-            cost, acc, step = eng.train_op(batch_x, batch_y)                     # :135-137
-            eng.counter_op()                                                     # :141 (summary :139 is in _after_step)
+            with tr.span("train_op(fwd/bwd/push)", "step"):
+                cost, acc, step = eng.train_op(batch_x, batch_y)                 # :135-137
+            with tr.span("counter_op", "step"):
+                eng.counter_op()                                                 # :141 (summary :139 is in _after_step)
             if self._after_step(step, cost, acc, lambda: eng.accuracy(dataset.test.images, dataset.test.labels)):
                 break
         return step
@@ -235,7 +248,7 @@ class Worker:
     def _loop_cuda(self, sv: Supervisor, dataset) -> int:
         import torch
         from .gpu_step import DeviceDataset
-        f, tr = self.flags, self.trainer
+        f, tr, tc = self.flags, self.trainer, self.tracer
         dev = tr.device
         seed = None if f.seed < 0 else f.seed + 1000 * self.task_index
         train = DeviceDataset(dataset.train.images, dataset.train.label_ids, dev, seed=seed)
@@ -246,17 +259,20 @@ class Worker:
         n = 1 if separate_exchange else max(1, f.steps_per_launch)
         step = 0
         while not sv.should_stop():
-            loss_d, acc_d, step_d = tr.train_device_steps(train, n)
+            with tc.span("launch", "step", steps=n), tc.device_span("step_kernel", steps=n):
+                loss_d, acc_d, step_d = tr.train_device_steps(train, n)
             if separate_exchange:
-                self.sync_group.reduce_scatter_apply(f.learning_rate)
+                with tc.span("sync_exchange", "step"):
+                    self.sync_group.reduce_scatter_apply(f.learning_rate)
                 step_d = self.store.tensor(self.global_step.name)[:1] - 1      # the aggregated update just applied
             if self.sync_group is not None and self.sync_group.aborted():
                 print("sync: a peer left, stopping", flush=True)
                 break
-            if tr.fused is not None and not separate_exchange:
-                loss, acc, steps = tr.fused.k.results_host(len(loss_d))            # one copy, one sync per launch
-            else:
-                loss, acc, steps = loss_d.tolist(), acc_d.tolist(), step_d.tolist()
+            with tc.span("results_d2h", "step"):
+                if tr.fused is not None and not separate_exchange:
+                    loss, acc, steps = tr.fused.k.results_host(len(loss_d))        # one copy, one sync per launch
+                else:
+                    loss, acc, steps = loss_d.tolist(), acc_d.tolist(), step_d.tolist()
             stop = False
             for l, a, s in zip(loss, acc, steps):
                 step = s

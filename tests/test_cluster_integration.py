@@ -110,3 +110,27 @@ def test_sigterm_exit_code_and_non_chief_crash_is_harmless(tmp_path):
     assert cl.procs["worker0"].wait(timeout=60) == 128 + signal.SIGTERM        # reference main.py:51-52
     cl.signal_all(signal.SIGINT, jobs=("ps",))
     assert cl.procs["ps"].wait(timeout=60) == 128 + signal.SIGINT
+
+
+def test_trace_file_from_a_real_cluster(tmp_path):
+    """--trace_file: every worker writes a Chrome trace with the three per-step ops of the reference loop
+    (pull / train / counter), the per-step summary and the chief's checkpoint spans."""
+    import json
+    trace = str(tmp_path / "run.json")
+    cl, logdir = _cluster(tmp_path, extra=["--training_steps", "120", "--learning_rate", "0.05", "--trace_file", trace])
+    cl.start()
+    codes = cl.wait(timeout=240)
+    assert all(c == 0 for c in codes.values()), (codes, cl.lines)
+    assert any(l.startswith("trace written to ") for l in cl.lines["worker0"])
+    names, nsteps = {}, 0
+    for task in (0, 1):
+        doc = json.load(open(str(tmp_path / f"run.worker{task}.json")))
+        evs = [e for e in doc["traceEvents"] if e.get("ph") == "X"]
+        names[task] = {e["name"] for e in evs}
+        steps = [e for e in evs if e["name"] == "train_op(fwd/bwd/push)"]
+        assert len(steps) >= 1 and all(e["dur"] > 0 for e in steps)      # a late worker may only see the last steps
+        nsteps += len(steps)
+        assert {"sync_op(pull)", "counter_op", "summary", "managed_session"} <= names[task]
+    assert nsteps >= 120
+    assert {"checkpoint.snapshot", "checkpoint.write"} <= names[0]          # only the chief saves
+    assert "checkpoint.write" not in names[1]

@@ -331,3 +331,31 @@ def test_fused_step_with_in_kernel_sync_exchange_single_rank():
     torch.cuda.synchronize()
     assert store.read("global/global_step").item() == nsteps + 1 and sg.aborted() == 0
     sg.close(); store.close()
+
+
+def test_tracer_device_spans_time_the_step_kernel():
+    """utils.tracing on a GPU: a device span is a CUDA-event pair on the launching stream (plus an NVTX range
+    for the host span); its duration must be the kernel's, not the host call's."""
+    from distributedtensorflowexample_b200.train.gpu_step import FusedMlp2Stepper
+    from distributedtensorflowexample_b200.utils import tracing
+    spec = reference_mlp_spec()
+    model, store, names = _store(spec)
+    x, y = _data()
+    X = torch.tensor(x, device="cuda"); Y = torch.tensor(y, device="cuda")
+    nsteps = 50
+    st = FusedMlp2Stepper(spec, 100, [store.tensor(n) for n in names], store.tensor("global/global_step"), 0.01,
+                          "cuda:0", max_steps_per_launch=nsteps)
+    idx = torch.randint(0, x.shape[0], (nsteps * 100,), device="cuda", dtype=torch.int32)
+    st.run(X, Y, nsteps=nsteps, batch_idx=idx)            # warm-up
+    torch.cuda.synchronize()
+    tr = tracing.Tracer(True, process_name="gpu-test")
+    with tr.span("launch", "step", steps=nsteps), tr.device_span("step_kernel", steps=nsteps):
+        st.run(X, Y, nsteps=nsteps, batch_idx=idx)
+    evs = tr.events()
+    dev = [e for e in evs if e["cat"] == "device"]
+    host = [e for e in evs if e["name"] == "launch"]
+    assert len(dev) == 1 and len(host) == 1
+    per_step = dev[0]["dur"] / nsteps
+    assert 5.0 < per_step < 200.0, per_step              # microseconds per training step, measured on the device
+    assert dev[0]["args"] == {"steps": nsteps}
+    store.close()
