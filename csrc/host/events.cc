@@ -95,6 +95,15 @@ DTFE_HOST_API int dtfe_events_write_scalars(void* h, double wall_time, int64_t s
   return WriteRecord(static_cast<EventWriter*>(h), e);
 }
 
+// n events at once (one per training step of a multi-step kernel launch): step[i] with the `ntags` scalars
+// values[i*ntags .. ], all stamped `wall_time`.  Same bytes as n calls of dtfe_events_write_scalars.
+DTFE_HOST_API int dtfe_events_write_scalars_batch(void* h, double wall_time, const int64_t* steps,
+                                                  const char* const* tags, const float* values, int n, int ntags) {
+  for (int i = 0; i < n; ++i)
+    if (int rc = dtfe_events_write_scalars(h, wall_time, steps[i], tags, values + (size_t)i * ntags, ntags)) return rc;
+  return 0;
+}
+
 // Event{wall_time, step, session_log{status, checkpoint_path, msg}}; status: 1 START, 2 STOP, 3 CHECKPOINT
 DTFE_HOST_API int dtfe_events_write_session_log(void* h, double wall_time, int64_t step, int status,
                                                 const char* checkpoint_path, const char* msg) {

@@ -208,11 +208,12 @@ class Worker:
             print(f"trace written to {path}", flush=True)
         return last_step
 
-    def _after_step(self, step: int, cost: float, acc: float, eval_fn) -> bool:
+    def _after_step(self, step: int, cost: float, acc: float, eval_fn, write_summary: bool = True) -> bool:
         """Summary + cadence rules of reference worker.py:139-159. Returns True to stop."""
         f = self.flags
-        with self.tracer.span("summary", "host"):
-            self.summary_writer.add_summary(training_summary(cost, acc), step)
+        if write_summary:
+            with self.tracer.span("summary", "host"):
+                self.summary_writer.add_summary(training_summary(cost, acc), step)
         if "kill_worker" in self.faults and self.faults["kill_worker"][0] == self.task_index \
                 and step >= self.faults["kill_worker"][1]:
             print(f"fault injection: worker {self.task_index} dies at step {step}", flush=True)
@@ -273,10 +274,14 @@ class Worker:
                     loss, acc, steps = tr.fused.k.results_host(len(loss_d))        # one copy, one sync per launch
                 else:
                     loss, acc, steps = loss_d.tolist(), acc_d.tolist(), step_d.tolist()
+            # per-step summaries of the whole launch in one native call, up to the step that ends training
+            m = next((i + 1 for i, s in enumerate(steps) if s >= f.training_steps), len(steps))
+            with tc.span("summary", "host", steps=m):
+                self.summary_writer.add_training_summaries(steps[:m], loss[:m], acc[:m])
             stop = False
-            for l, a, s in zip(loss, acc, steps):
+            for l, a, s in zip(loss[:m], acc[:m], steps[:m]):
                 step = s
-                if self._after_step(s, l, a, eval_fn):
+                if self._after_step(s, l, a, eval_fn, write_summary=False):
                     stop = True
                     break
             if stop:

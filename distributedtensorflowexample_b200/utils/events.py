@@ -67,6 +67,12 @@ class FileWriter:
         vals = [v for _, v in summary.values]
         self._f.write_scalars(time.time() if wall_time is None else wall_time, int(global_step), tags, vals)
 
+    def add_training_summaries(self, global_steps, losses, accuracies, wall_time: Optional[float] = None) -> None:
+        """The per-step loss/accuracy summaries (reference worker.py:92-95,139) of a whole multi-step launch in
+        one native call; byte-identical to calling ``add_summary(training_summary(l, a), s)`` per step."""
+        self._f.write_scalars_batch(time.time() if wall_time is None else wall_time, list(global_steps),
+                                    [TAG_LOSS, TAG_ACCURACY], list(zip(losses, accuracies)))
+
     def add_session_log(self, status: int, global_step: int = 0, checkpoint_path: str = "", msg: str = "") -> None:
         self._f.write_session_log(time.time(), int(global_step), status, checkpoint_path, msg)
 

@@ -45,6 +45,8 @@ def _lib():
         L.dtfe_events_open.argtypes = [c_char_p]; L.dtfe_events_open.restype = c_void_p
         L.dtfe_events_write_version.argtypes = [c_void_p, c_double]
         L.dtfe_events_write_scalars.argtypes = [c_void_p, c_double, c_int64, POINTER(c_char_p), POINTER(c_float), c_int]
+        L.dtfe_events_write_scalars_batch.argtypes = [c_void_p, c_double, POINTER(c_int64), POINTER(c_char_p),
+                                                      POINTER(c_float), c_int, c_int]
         L.dtfe_events_write_session_log.argtypes = [c_void_p, c_double, c_int64, c_int, c_char_p, c_char_p]
         L.dtfe_events_write_graph.argtypes = [c_void_p, c_double, c_void_p, c_size_t]
         L.dtfe_events_flush.argtypes = [c_void_p]
@@ -180,6 +182,16 @@ class EventsFile:
         T = (c_char_p * n)(*[t.encode() for t in tags])
         V = (c_float * n)(*[float(v) for v in values])
         check_host(self._L.dtfe_events_write_scalars(self._h, wall_time, int(step), T, V, n), "events scalars")
+
+    def write_scalars_batch(self, wall_time: float, steps: Sequence[int], tags: Sequence[str], rows) -> None:
+        """One event per step: ``rows[i]`` holds the ``len(tags)`` scalar values of ``steps[i]``."""
+        n, nt = len(steps), len(tags)
+        if n == 0:
+            return
+        T = (c_char_p * nt)(*[t.encode() for t in tags])
+        S = (c_int64 * n)(*[int(x) for x in steps])
+        V = (c_float * (n * nt))(*[float(v) for row in rows for v in row])
+        check_host(self._L.dtfe_events_write_scalars_batch(self._h, wall_time, S, T, V, n, nt), "events scalars batch")
 
     def write_session_log(self, wall_time: float, step: int, status: int, checkpoint_path: str = "", msg: str = "") -> None:
         check_host(self._L.dtfe_events_write_session_log(self._h, wall_time, int(step), status,

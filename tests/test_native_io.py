@@ -154,3 +154,20 @@ def test_idx_rejects_garbage(tmp_path):
         f.write(struct.pack(">II", 0x801, 10) + b"abc")
     with pytest.raises(Exception):
         nio.read_idx(str(p2))
+
+
+def test_events_batch_is_bytewise_the_per_step_writes(tmp_path):
+    from distributedtensorflowexample_b200.utils.events import FileWriter, training_summary
+    a = FileWriter(str(tmp_path / "a")); b = FileWriter(str(tmp_path / "b"))
+    steps, losses, accs = [5, 6, 9], [1.5, 0.25, 3.0], [0.1, 0.5, 1.0]
+    for s, l, ac in zip(steps, losses, accs):
+        a.add_summary(training_summary(l, ac), s, wall_time=123.5)
+    b.add_training_summaries(steps, losses, accs, wall_time=123.5)
+    a.close(); b.close()
+    da, db = open(a.path, "rb").read(), open(b.path, "rb").read()
+    # the first record (file version) carries each writer's own creation time; everything after must match
+    def tail(d):
+        import struct
+        n = struct.unpack("<Q", d[:8])[0]
+        return d[8 + 4 + n + 4:]
+    assert tail(da) == tail(db) and len(tail(da)) > 100
