@@ -386,6 +386,11 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
       const bool vec_reduce = (H & 3) == 0;
       const int nq4 = vec_reduce ? (H >> 2) : 1;      // float4 columns per row (25)
       const int nqg = min(kThreads / nq4, 16);        // partial groups (10)
+      // After the reduction, hidden unit tu belongs to lane `lane` of warp `warp` (per = ceil(H/8) <= 16 units
+      // per warp): its activation stays in that thread's register through logits and dA.
+      const int per = (H + 7) / 8;
+      const int tu = warp * per + lane;
+      const bool own = lane < per && tu < H;
       if (vec_reduce) {
         // Cooperative float4 reduction of the G split-K partials of row r: thread = (column quad, partial
         // group); every thread sums ~G/nqg float4 loads in registers, the nqg group sums meet in smem.
@@ -410,16 +415,14 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
         add_batch();
         for (unsigned q0 = qg + 10 * nqg; q0 < G; q0 += 10 * nqg) { load_batch(q0); add_batch(); }
         if (mine) reinterpret_cast<float4*>(red_part + qg * kMaxH)[c4] = acc;
-      } else {
-        if (t < H) {
-        const float* P = a.part + (long)r * H + t;
+      } else if (own) {
+        const float* P = a.part + (long)r * H + tu;
         const long gs = (long)B * H;
         float z0 = 0.f, z1 = 0.f;
         unsigned q = 0;
         for (; q + 2 <= G; q += 2) { z0 += __ldcg(P + (long)q * gs); z1 += __ldcg(P + (long)(q + 1) * gs); }
         if (q < G) z0 += __ldcg(P + (long)q * gs);
         z = z0 + z1;
-        }
       }
       DBG_STAMP(8);
       if (first_round) {
@@ -447,35 +450,31 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
         }
       }
       __syncthreads();
+      // Activation of the owned unit, then this warp's share of the logits straight out of registers:
+      // lane = class, the warp's activations are broadcast with shuffles (no smem round trip, no barrier).
       float h = 0.f;
-      if (t < H) {
+      if (own) {
         if (vec_reduce)
-          for (int qg = 0; qg < nqg; ++qg) z += red_part[qg * kMaxH + t];
-        h = dtfe::sigmoidf_fast(z + b1s[t]);
-        hs[t] = h;
-        __stcg(a.Hbuf + (long)r * H + t, h);
+          for (int qg = 0; qg < nqg; ++qg) z += red_part[qg * kMaxH + tu];
+        h = dtfe::sigmoidf_fast(z + b1s[tu]);
+        __stcg(a.Hbuf + (long)r * H + tu, h);
       }
-      __syncthreads();
-      DBG_STAMP(9);
       {
-        // Logits: lane = class + C*group in every warp; warp w covers hidden units [w*per, (w+1)*per), its
-        // groups interleave inside that range; groups fold with shuffles, warps meet in smem (zs).
-        const int ngrp = 32 / C;                      // C <= 16 -> at least 2 groups
-        const int cls = lane % C, grp = lane / C;
-        const int per = (H + 7) / 8;
-        const int ubeg = warp * per, uend = min(H, ubeg + per);
         float p = 0.f;
-        if (grp < ngrp)
-          for (int u = ubeg + grp; u < uend; u += ngrp) p = fmaf(hs[u], W2s[u * C + cls], p);
-        for (int gsh = 1; gsh < ngrp; ++gsh) {        // fold group gsh into group 0
-          float other = __shfl_down_sync(0xffffffffu, p, gsh * C);
-          if (grp == 0) p += other;
+        for (int u = 0; u < per; ++u) {
+          const float hu = __shfl_sync(0xffffffffu, h, u);       // 0 for units beyond H
+          const int uu = warp * per + u;
+          if (lane < C && uu < H) p = fmaf(hu, W2s[uu * C + lane], p);
         }
         if (lane < C) zs[warp * kMaxC + lane] = p;
       }
       __syncthreads();
+      DBG_STAMP(9);
       DBG_STAMP(10);
-      if (warp == 0) {
+      // Softmax cross-entropy of the row, computed by EVERY warp (same latency as by one, and dz stays in the
+      // lanes 0..C-1 of each warp for the dA product below); warp 0 publishes dZ / loss / correct.
+      float dz = 0.f;
+      {
         float zc = -INFINITY;
         if (lane < C) {
           float p = b2s[lane];
@@ -498,24 +497,25 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
           y = a.labels[row];
         }
         float zy = __shfl_sync(0xffffffffu, zc, y);
-        if (lane < C) {
-          float dz = (ex / se - (lane == y ? 1.f : 0.f)) * invB;
-          dzs[lane] = dz;
-          __stcg(a.dZ + (long)r * C + lane, dz);
-        }
-        if (lane == 0) {
-          __stcg(a.rowloss + r, mx + __logf(se) - zy);
-          __stcg(a.rowcorrect + r, (am == y) ? 1 : 0);
+        if (lane < C) dz = (ex / se - (lane == y ? 1.f : 0.f)) * invB;
+        if (warp == 0) {
+          if (lane < C) __stcg(a.dZ + (long)r * C + lane, dz);
+          if (lane == 0) {
+            __stcg(a.rowloss + r, mx + __logf(se) - zy);
+            __stcg(a.rowcorrect + r, (am == y) ? 1 : 0);
+          }
         }
       }
-      __syncthreads();
       DBG_STAMP(11);
-      if (t < H) {
+      {
         float dh = 0.f;
-        for (int c = 0; c < C; ++c) dh = fmaf(dzs[c], W2s[t * C + c], dh);
-        __stcg(a.dA + (long)r * H + t, dh * h * (1.f - h));
+        for (int c = 0; c < C; ++c) {
+          const float dzc = __shfl_sync(0xffffffffu, dz, c);
+          if (own) dh = fmaf(dzc, W2s[tu * C + c], dh);
+        }
+        if (own) __stcg(a.dA + (long)r * H + tu, dh * h * (1.f - h));
       }
-      __syncthreads();
+      if (r + (int)NC < B) __syncthreads();  // another round reuses red_part / zs
     }
     if (fetches) {
       // The fetch for the next step has landed before anyone pushes (phase C starts behind barrier 2);
