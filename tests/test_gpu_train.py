@@ -78,7 +78,8 @@ def test_fused_step_matches_oracle(ks, atomic):
     store.close()
 
 
-@pytest.mark.parametrize("dims,B,ks", [((50, 30, 7), 33, 8), ((100, 128, 16), 128, 8), ((130, 20, 3), 5, 16)])
+@pytest.mark.parametrize("dims,B,ks", [((50, 30, 7), 33, 8), ((100, 128, 16), 128, 8), ((130, 20, 3), 5, 16),
+                                       ((64, 30, 7), 33, 8), ((96, 64, 10), 50, 8)])
 def test_fused_step_odd_shapes_match_oracle(dims, B, ks):
     """Shapes that are not whole float4s / whole K slices: partial cp.async quads, the scalar split-K
     reduction, a short last W1 slice, grids with and without helper CTAs."""
