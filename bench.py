@@ -17,7 +17,6 @@ import json
 import os
 import sys
 import threading
-import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
@@ -122,7 +121,6 @@ def main():
         _reference_unavailable()
         return 0
 
-    import numpy as np
     import torch
     import torch.distributed as dist
 

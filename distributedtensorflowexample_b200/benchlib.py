@@ -2,9 +2,7 @@
 from __future__ import annotations
 
 import json
-import os
 import time
-from typing import Optional
 
 import numpy as np
 import torch

@@ -2,7 +2,7 @@
 main.py:47-48; TF1 tf.train.ClusterSpec - SURVEY C3/T1)."""
 from __future__ import annotations
 
-from typing import Dict, Iterable, List, Mapping, Tuple
+from typing import Dict, List, Tuple
 
 LOCALHOST = "127.0.0.1"
 BASE_PORT = 12222

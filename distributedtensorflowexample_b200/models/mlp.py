@@ -8,7 +8,7 @@ The "wide" benchmark family (784-8192-8192-10) is the same builder with more lay
 from __future__ import annotations
 
 from dataclasses import dataclass
-from typing import List, Sequence, Tuple
+from typing import List, Tuple
 
 from ..variables import VariableDef, VariableStore, random_normal_initializer, zeros_initializer
 

@@ -12,7 +12,7 @@ from typing import Optional, Sequence
 
 import torch
 
-from ._lib import cuda_lib, check, NativeError
+from ._lib import cuda_lib, check
 
 _P = c_void_p
 

@@ -13,7 +13,7 @@ import torch
 import torch.distributed as dist
 
 from ..models.mlp import MLPSpec
-from ..train.replica import ReplicatedModel, build_replicated_model
+from ..train.replica import build_replicated_model
 from .ps import PeerParamStore
 
 

@@ -11,7 +11,7 @@ parameters from the owners' shards anyway (the fused pull).  One rank per GPU.
 """
 from __future__ import annotations
 
-from typing import Dict, List, Optional, Sequence
+from typing import Dict, List, Sequence
 
 import torch
 import torch.distributed as dist

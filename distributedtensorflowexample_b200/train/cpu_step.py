@@ -12,7 +12,7 @@ Math is plain torch on CPU without autograd (the CPU stand-in for ``allow_soft_p
 from __future__ import annotations
 
 import time
-from typing import Dict, List, Tuple
+from typing import Dict, Tuple
 
 import numpy as np
 import torch

@@ -22,7 +22,7 @@ import os
 import threading
 import time
 import traceback
-from typing import Callable, Dict, List, Optional
+from typing import Callable, List, Optional
 
 import numpy as np
 

@@ -20,9 +20,7 @@ rules are then evaluated for every step of the launch after it returns.
 from __future__ import annotations
 
 import os
-import sys
 import time
-from typing import Optional
 
 import numpy as np
 

@@ -12,7 +12,7 @@ import os
 import socket
 import threading
 import time
-from typing import Dict, Optional, Sequence, Tuple
+from typing import Optional, Sequence, Tuple
 
 from . import native_io
 

@@ -2,7 +2,6 @@
 """Host->device copy rate from pinned memory: one large copy vs a stream of batch-sized copies
 (314 KB fp32 / 78 KB uint8 MNIST batches).  Explains the end-to-end bound of the host-fed loop."""
 import json
-import sys
 import time
 
 import torch

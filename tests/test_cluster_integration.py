@@ -6,8 +6,6 @@ import os
 import re
 import signal
 import socket
-import subprocess
-import sys
 import time
 
 import numpy as np

@@ -1,5 +1,4 @@
 """CPU unit tests: flags, cluster spec, placement, variable scopes, memory fraction, launchers."""
-import math
 import os
 import subprocess
 import sys

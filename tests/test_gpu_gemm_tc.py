@@ -73,7 +73,6 @@ def test_dense_layer_ops_tc(B_, din, dout):
 def test_push_epilogue_through_tma_reduce(M, N, K, parts):
     """dW push of the 2-CTA kernel: bf16 target, whole tiles added with cp.reduce.async.bulk.tensor; must
     agree with the per-thread red.add path and with fp32 math, also when the target is row-partitioned."""
-    import os
     from distributedtensorflowexample_b200.ops import gemm_tc as G
     if parts and M % (parts * 128):
         pytest.skip("row blocks must be multiples of 128 rows for the TMA path (others fall back)")

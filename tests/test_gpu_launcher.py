@@ -1,6 +1,5 @@
 """GPU: the reference's process model on real hardware - a ps process owning an HBM shard plus worker
 processes that map it over CUDA IPC (run_single_gpu.sh topology: 2 workers sharing GPU 0)."""
-import os
 import re
 import socket
 

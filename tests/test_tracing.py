@@ -1,6 +1,5 @@
 """Tracing subsystem: spans, counters, Chrome-trace output, disabled-by-default cost."""
 import json
-import os
 import threading
 import time
 
