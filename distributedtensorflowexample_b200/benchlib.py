@@ -97,7 +97,16 @@ def run_mnist(args, rank: int, world: int, dev, ClockSampler) -> int:
         t1 = time.perf_counter()
         sec = _max_over_ranks(t1 - t0, world, dev)
         assert np.isfinite(loss_host[:Ke].numpy()).all()
+        # the same loop with ONE step per kernel launch (every step: its own launch, H2D copies, D2H read)
+        K1 = min(Ke, 1000)
+        tr.train_host_batches(xl[:W], yl[:W], loss_host, steps_per_launch=1)
+        _barrier(world)
+        t0 = time.perf_counter()
+        tr.train_host_batches(xl[:K1], yl[:K1], loss_host, steps_per_launch=1)
+        torch.cuda.synchronize()
+        sec1 = _max_over_ranks(time.perf_counter() - t0, world, dev)
         e2e = {"value": world * B * Ke / sec, "unit": "examples/sec", "steps": Ke,
+               "value_one_step_per_launch": world * B * K1 / sec1,
                "h2d_bytes_per_step": tr.h2d_bytes_per_step(), "d2h_bytes_per_step": tr.d2h_bytes_per_step(),
                "steps_per_launch": espl,
                "timing": "host wall clock around GpuTrainer.train_host_batches (every step: H2D copy of its batch from "
