@@ -21,6 +21,14 @@ DTFE_API const char* dtfe_last_error() { return g_err; }
 
 DTFE_API int dtfe_abi_version() { return 1; }
 
+// sizeof of the structs that cross the C ABI, so a binding can verify its mirror of the layout:
+// out[0] = dtfe_mlp2_launch, out[1] = dtfe_sync_exchange, out[2] = dtfe_gemm_tc.
+DTFE_API int dtfe_struct_sizes(size_t* out, int n) {
+  const size_t sizes[3] = {sizeof(dtfe_mlp2_launch), sizeof(dtfe_sync_exchange), sizeof(dtfe_gemm_tc)};
+  for (int i = 0; i < n && i < 3; ++i) out[i] = sizes[i];
+  return 3;
+}
+
 DTFE_API int dtfe_device_count(int* n) {
   DTFE_CUDA_CHECK(cudaGetDeviceCount(n));
   return 0;

@@ -18,6 +18,7 @@ _P = c_void_p
 
 _SIGS = {
     "dtfe_abi_version": ([], c_int),
+    "dtfe_struct_sizes": ([POINTER(c_size_t), c_int], c_int),
     "dtfe_device_count": ([POINTER(c_int)], c_int),
     "dtfe_device_info": ([c_int, POINTER(c_int)], c_int),
     "dtfe_shard_alloc": ([c_size_t, POINTER(_P)], c_int),

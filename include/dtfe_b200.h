@@ -21,6 +21,7 @@ extern "C" {
 /* ---- runtime ------------------------------------------------------------------------------ */
 const char* dtfe_last_error(void);
 int dtfe_abi_version(void);
+int dtfe_struct_sizes(size_t* out, int n);   /* sizeof {dtfe_mlp2_launch, dtfe_sync_exchange, dtfe_gemm_tc}; returns 3 */
 int dtfe_device_count(int* n);
 /* out[6] = {cc major, cc minor, SM count, max opt-in smem/CTA, L2 bytes, cooperative launch} */
 int dtfe_device_info(int dev, int* out);

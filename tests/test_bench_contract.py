@@ -48,3 +48,15 @@ def test_graft_entry_build_produces_loadable_libraries():
     assert len(names) > 25
     for n in sorted(names):
         assert hasattr(lib, n), f"{n} is declared in include/dtfe_b200.h but not exported"
+
+
+def test_ctypes_struct_mirrors_match_the_c_layout():
+    """The ctypes mirrors of the launch structs must have the C compiler's size (field order/padding drift
+    between include/dtfe_b200.h and the bindings would otherwise corrupt arguments silently)."""
+    import ctypes
+    from distributedtensorflowexample_b200.ops import cuda_ops, gemm_tc
+    sizes = (ctypes.c_size_t * 3)()
+    assert cuda_ops.lib().dtfe_struct_sizes(sizes, 3) == 3
+    assert ctypes.sizeof(cuda_ops._Mlp2Launch) == sizes[0]
+    assert ctypes.sizeof(cuda_ops.SyncExchange) == sizes[1]
+    assert ctypes.sizeof(gemm_tc._GemmTc) == sizes[2]
