@@ -835,6 +835,7 @@ static int mlp2_fill(const Mlp2Launch& L, Mlp2Args& a) {
   DTFE_REQUIRE(L.H >= 1 && L.H <= kMaxH, "mlp2_step: hidden %d outside [1,%d]", L.H, kMaxH);
   DTFE_REQUIRE(L.C >= 1 && L.C <= kMaxC, "mlp2_step: classes %d outside [1,%d]", L.C, kMaxC);
   DTFE_REQUIRE(L.ks == 8 || L.ks == 16, "mlp2_step: ks must be 8 or 16");
+  DTFE_REQUIRE(L.nsteps >= 1, "mlp2_step: nsteps must be at least 1 (got %d)", L.nsteps);
   DTFE_REQUIRE(((uintptr_t)L.workspace % 16) == 0, "mlp2_step: workspace must be 16-byte aligned");
   size_t G = (size_t)((L.D + L.ks - 1) / L.ks);
   DTFE_REQUIRE(G <= 148, "mlp2_step: D/ks = %zu CTAs exceeds one wave (148); use ks=16 or the layer path", G);
