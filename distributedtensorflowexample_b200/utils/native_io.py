@@ -63,6 +63,11 @@ def crc32c(data: bytes) -> int:
     return int(_lib().dtfe_crc32c(data, len(data)))
 
 
+def crc32c_extend(crc: int, data: bytes) -> int:
+    """crc32c of (already-summed prefix + data): ``crc32c(a + b) == crc32c_extend(crc32c(a), b)``."""
+    return int(_lib().dtfe_crc32c_extend(crc, data, len(data)))
+
+
 def crc32c_masked(data: bytes) -> int:
     return int(_lib().dtfe_crc32c_masked(data, len(data)))
 

@@ -174,3 +174,31 @@ def test_shard_layout_offsets_pitch_and_partitioning():
     assert all(any(x.name == "global/dense/kernel" for x in lay.shard_entries(k)) for k in range(4))
     with pytest.raises(ValueError):
         ShardLayout(wide.local_all, 4)                   # local/* variables are not on the ps job
+
+
+# ---- property tests ------------------------------------------------------------------------------------------
+from hypothesis import given, settings, strategies as st
+
+
+@settings(max_examples=60, deadline=None)
+@given(num_workers=st.integers(1, 32), num_ps=st.integers(1, 8), base=st.integers(1024, 60000))
+def test_cluster_spec_property(num_workers, num_ps, base):
+    from distributedtensorflowexample_b200.cluster import cluster_spec
+    spec = cluster_spec(num_workers, num_ps, base_port=base)
+    hosts = spec["ps"] + spec["worker"]
+    assert len(spec["ps"]) == num_ps and len(spec["worker"]) == num_workers
+    ports = [int(h.rsplit(":", 1)[1]) for h in hosts]
+    assert ports == list(range(base, base + num_ps + num_workers))          # consecutive, ps first
+    assert all(h.startswith("127.0.0.1:") for h in hosts)
+
+
+@settings(max_examples=60, deadline=None)
+@given(num_workers=st.integers(1, 64), num_gpus=st.integers(1, 8))
+def test_memory_fraction_property(num_workers, num_gpus):
+    import math
+    from distributedtensorflowexample_b200.utils.memory import per_process_gpu_memory_fraction as gpu_memory_fraction
+    if num_gpus > num_workers:
+        num_gpus = num_workers
+    f = gpu_memory_fraction(num_workers, num_gpus)
+    per_gpu = math.ceil(num_workers / num_gpus)
+    assert f == 0.9 / per_gpu and f * per_gpu <= 0.9 + 1e-12                 # the workers of one GPU never exceed 90 %

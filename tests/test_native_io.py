@@ -171,3 +171,48 @@ def test_events_batch_is_bytewise_the_per_step_writes(tmp_path):
         n = struct.unpack("<Q", d[:8])[0]
         return d[8 + 4 + n + 4:]
     assert tail(da) == tail(db) and len(tail(da)) > 100
+
+
+# ---- property tests (hypothesis): arbitrary contents must round-trip through the native formats -------------
+from hypothesis import HealthCheck, given, settings, strategies as st
+
+_SLOW_OK = settings(max_examples=40, deadline=None, suppress_health_check=[HealthCheck.function_scoped_fixture])
+
+
+@_SLOW_OK
+@given(items=st.dictionaries(st.binary(min_size=1, max_size=40), st.binary(max_size=300), max_size=60),
+       block=st.sampled_from([64, 256, 4096]))
+def test_sstable_roundtrip_property(tmp_path, items, block):
+    pairs = sorted(items.items())
+    p = str(tmp_path / "p.sst")
+    nio.sstable_write(p, pairs, block_size=block)
+    assert nio.sstable_read(p) == pairs
+
+
+_NAME = st.text(alphabet="abcdefghijklmnopqrstuvwxyz_/0123456789", min_size=1, max_size=24)
+_DTYPE = st.sampled_from([np.float32, np.float64, np.int32, np.int64])
+_SHAPE = st.lists(st.integers(min_value=0, max_value=7), min_size=0, max_size=4)
+
+
+@_SLOW_OK
+@given(spec=st.dictionaries(_NAME, st.tuples(_DTYPE, _SHAPE), min_size=1, max_size=8), seed=st.integers(0, 2 ** 31 - 1))
+def test_bundle_roundtrip_property(tmp_path, spec, seed):
+    rng = np.random.default_rng(seed)
+    tensors = {}
+    for name, (dt, shape) in spec.items():
+        a = rng.integers(-1000, 1000, size=shape) if np.issubdtype(dt, np.integer) else rng.normal(size=shape)
+        tensors[name] = np.asarray(a, dtype=dt)
+    prefix = str(tmp_path / "b")
+    nio.bundle_write(prefix, tensors)
+    back = nio.bundle_read(prefix)
+    assert set(back) == set(tensors)
+    for k, v in tensors.items():
+        assert back[k].dtype == v.dtype and back[k].shape == v.shape
+        np.testing.assert_array_equal(back[k], v)
+
+
+@_SLOW_OK
+@given(data=st.binary(max_size=5000))
+def test_crc32c_incremental_equals_one_shot(data):
+    cut = len(data) // 3
+    assert nio.crc32c(data) == nio.crc32c_extend(nio.crc32c(data[:cut]), data[cut:])
