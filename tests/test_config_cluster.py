@@ -202,3 +202,38 @@ def test_memory_fraction_property(num_workers, num_gpus):
     f = gpu_memory_fraction(num_workers, num_gpus)
     per_gpu = math.ceil(num_workers / num_gpus)
     assert f == 0.9 / per_gpu and f * per_gpu <= 0.9 + 1e-12                 # the workers of one GPU never exceed 90 %
+
+
+@settings(max_examples=80, deadline=None)
+@given(dims=st.lists(st.integers(1, 300), min_size=2, max_size=5), num_ps=st.integers(1, 6),
+       dtype=st.sampled_from(["float32", "bfloat16"]), part_kb=st.sampled_from([0, 1, 16, 256]),
+       strategy=st.sampled_from(["round_robin", "greedy_bytes"]))
+def test_shard_layout_property(dims, num_ps, dtype, part_kb, strategy):
+    """No two variables (or parts) overlap inside a shard, everything is 256-byte aligned and inside the shard,
+    a partitioned variable has exactly one equally sized part on every shard."""
+    from distributedtensorflowexample_b200.models.mlp import MLPSpec
+    from distributedtensorflowexample_b200.parallel.layout import ShardLayout, HEADER_BYTES, ALIGN
+    from distributedtensorflowexample_b200.train.replica import build_replicated_model
+    m = build_replicated_model(MLPSpec(tuple(dims), param_dtype=dtype), num_ps=num_ps, ps_strategy=strategy)
+    lay = ShardLayout(m.global_all, num_ps, partition_min_bytes=part_kb << 10)
+    assert sorted(lay.names()) == sorted(v.name for v in m.global_all)
+    spans = {k: [] for k in range(num_ps)}
+    for name in lay.names():
+        e = lay[name]
+        if e.parts:
+            assert e.shard == -1 and [pk for pk, _ in e.parts] == list(range(num_ps)) and e.nbytes % num_ps == 0
+            for pk, off in e.parts:
+                spans[pk].append((off, off + e.nbytes // num_ps, name))
+        else:
+            assert 0 <= e.shard < num_ps
+            spans[e.shard].append((e.offset, e.offset + e.nbytes, name))
+        item = 2 if e.dtype == "bfloat16" else 4
+        rows, pitch = (e.shape[0], e.pitch or e.shape[1]) if len(e.shape) == 2 else (1, int(__import__('math').prod(e.shape)))
+        assert e.nbytes == rows * pitch * item
+        if e.dtype == "bfloat16" and len(e.shape) == 2:
+            assert (pitch * item) % 16 == 0                                   # TMA row pitch
+    for k, sp in spans.items():
+        sp.sort()
+        assert all(a % ALIGN == 0 and a >= HEADER_BYTES and b <= lay.shard_bytes[k] for a, b, _ in sp)
+        assert all(sp[i][1] <= sp[i + 1][0] for i in range(len(sp) - 1)), sp
+        assert lay.shard_bytes[k] % ALIGN == 0
