@@ -237,3 +237,23 @@ def test_shard_layout_property(dims, num_ps, dtype, part_kb, strategy):
         assert all(a % ALIGN == 0 and a >= HEADER_BYTES and b <= lay.shard_bytes[k] for a, b, _ in sp)
         assert all(sp[i][1] <= sp[i + 1][0] for i in range(len(sp) - 1)), sp
         assert lay.shard_bytes[k] % ALIGN == 0
+
+
+@settings(max_examples=100, deadline=None)
+@given(bs=st.integers(1, 10 ** 6), lr=st.floats(1e-6, 10.0, allow_nan=False), logdir=st.text(alphabet="abc/._-XYZ019", min_size=1, max_size=20),
+       job=st.sampled_from(["ps", "worker"]), eq=st.lists(st.booleans(), min_size=4, max_size=4),
+       noise=st.lists(st.sampled_from(["--unknown_a=1", "--unknown_b", "stray"]), max_size=3), order=st.permutations(range(4)))
+def test_flag_parser_property(bs, lr, logdir, job, eq, noise, order):
+    """Both spellings (`--k v`, `--k=v`), any order, unknown arguments in between: every known flag gets its
+    value, every unknown argument comes back untouched and in order."""
+    fv = _flags()
+    known = [("batch_size", str(bs)), ("learning_rate", repr(lr)), ("logdir", logdir), ("job_name", job)]
+    argv = []
+    for i in order:
+        k, v = known[i]
+        argv += [f"--{k}={v}"] if eq[i] else [f"--{k}", v]
+        if noise and i % 2 == 0:
+            argv.append(noise[i % len(noise)])
+    rest = fv.parse(list(argv))
+    assert fv.batch_size == bs and fv.learning_rate == lr and fv.logdir == logdir and fv.job_name == job
+    assert rest == [a for a in argv if a in ("--unknown_a=1", "--unknown_b", "stray")]
