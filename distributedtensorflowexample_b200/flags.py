@@ -215,5 +215,7 @@ def define_framework_flags(flag_values: FlagValues = FLAGS) -> FlagValues:
     DEFINE_string("fault", "", "Test-only fault injection, e.g. 'kill_worker:1@50' or 'delay_push:0.01'", flag_values)
     DEFINE_string("trace_file", "", "Write a Chrome-trace JSON of this task's host spans and CUDA-event device spans "
                   "(job and task index are appended to the name); also emits NVTX ranges", flag_values)
+    DEFINE_float("sync_timeout_secs", 30, "Synchronous mode: give up on a round (and stop) after waiting this long "
+                 "for the other workers", flag_values)
     DEFINE_float("recovery_wait_secs", 30, "Non-chief poll period while waiting for the chief's init (TF1: 30)", flag_values)
     return flag_values

@@ -7,9 +7,16 @@ This reproduces the reference's *message pattern* literally: per step a worker d
 ``var -= lr*grad``, no locking across workers), a read of global_step, and a separate increment
 (reference worker.py:131,135-137,141).  The ps is a passive server loop, like TF1's worker service.
 
-Wire protocol (all tensors CPU): a request is an int64[4] header {op, a0, a1, a2} sent to the ps
+Wire protocol (all tensors CPU): a request is an int64[4] header {op, a0, seq, a3} sent to the ps
 rank, optionally followed by a payload; the ps answers on the same pair.  Each ps task owns the
 variables the placement function gave it, stored as one flat float32 vector + int32 global_step.
+
+Beyond the reference (which has plain asynchronous SGD only), ``OP_PUSH_OPT`` carries the two optional modes
+the CUDA path has, so that the plumbing configuration covers the same flags:
+  * Adam: the moments are ordinary ps variables (TF1 slot names ``<var>/Adam``, ``<var>/Adam_1``, placed with
+    their variable), the ps applies ``m, v, var`` updates per push and counts ``global/adam_t``;
+  * synchronous SGD/Adam: the ps accumulates the pushes of all workers, applies the MEAN once, bumps
+    ``global_step`` once and only then answers the waiting workers (TF1's SyncReplicasOptimizer semantics).
 """
 from __future__ import annotations
 
@@ -29,7 +36,14 @@ from ..variables import VariableDef
 from .client import ParamClient
 
 OP_PULL, OP_PUSH, OP_STEP_READ, OP_STEP_INC, OP_ASSIGN, OP_IS_READY, OP_SET_READY, OP_SHUTDOWN, OP_STOP_REQ, \
-    OP_STOP_QUERY, OP_ALLOC = range(1, 12)
+    OP_STOP_QUERY, OP_ALLOC, OP_PUSH_OPT, OP_ADAM_T_READ = range(1, 14)
+
+F_ADAM, F_SYNC = 1, 2            # OP_PUSH_OPT flag bits (header word 3: flags | nvars << 8)
+SYNC_ABORTED = -1                # reply of a synchronous push that was released without an update
+
+
+class SyncAborted(RuntimeError):
+    """A synchronous round could not complete (a peer left, stop was requested, or the wait timed out)."""
 
 
 _SHUTDOWN_SIGNALS = {signal.SIGHUP, signal.SIGINT, signal.SIGTERM}
@@ -51,17 +65,34 @@ class _TaskLayout:
         self.float_vars: List[VariableDef] = []
         self.offsets: Dict[str, int] = {}
         self.has_step = False
+        self.has_adam_t = False
         n = 0
         for v in variables:
             if v.device.job != "ps" or v.device.task != task:
                 continue
-            if v.dtype == "int32":
-                self.has_step = True
+            if v.dtype == "int32":               # counters live outside the flat float vector
+                if v.name.endswith("adam_t"):
+                    self.has_adam_t = True
+                else:
+                    self.has_step = True
                 continue
             self.float_vars.append(v)
             self.offsets[v.name] = n
             n += v.numel
         self.numel = n
+        self.trainable = [v for v in self.float_vars if v.trainable]
+
+    def push_descriptor(self, adam: bool) -> List[int]:
+        """Per trainable variable of this task: offset of the variable, of its two moments (-1 without Adam)
+        and its element count - everything the model-agnostic ps needs to apply a compact gradient vector."""
+        d: List[int] = []
+        for v in self.trainable:
+            m = self.offsets.get(v.name + "/Adam", -1) if adam else -1
+            w = self.offsets.get(v.name + "/Adam_1", -1) if adam else -1
+            if adam and (m < 0 or w < 0):
+                raise ValueError(f"{v.name}: the model was built without Adam slots")
+            d += [self.offsets[v.name], m, w, v.numel]
+        return d
 
 
 def init_gloo(cluster: ClusterSpec, job: str, task: int, timeout_s: float = 600.0) -> int:
@@ -85,6 +116,9 @@ class GlooParamServer:
         self.numel = _TaskLayout(variables, task).numel if variables is not None else 0
         self.flat = torch.zeros(max(self.numel, 1), dtype=torch.float32)
         self.step = torch.zeros(1, dtype=torch.int64)
+        self.adam_t = 0
+        self.sync_sum: Optional[torch.Tensor] = None       # running sum of this round's gradient vectors
+        self.sync_waiting: List[int] = []                   # ranks waiting for this round's answer
         self.ready = False
         self.stop_requested = False
         self.num_workers = num_workers
@@ -103,6 +137,30 @@ class GlooParamServer:
             self.dead.add(dst)
             print(f"ps:{self.task}: dropping reply to rank {dst} (op {op}): {str(e).splitlines()[0]}", flush=True)
 
+    def _apply(self, desc: List[int], grads: torch.Tensor, lr: float, adam: bool, hyper) -> None:
+        """var -= lr*g (TF1 ApplyGradientDescent) or the TF1 ApplyAdam update, per descriptor entry."""
+        if adam:
+            b1, b2, eps = hyper
+            self.adam_t += 1
+            lr_t = lr * (1.0 - b2 ** self.adam_t) ** 0.5 / (1.0 - b1 ** self.adam_t)
+        c = 0
+        for i in range(0, len(desc), 4):
+            vo, mo, wo, n = desc[i:i + 4]
+            g = grads[c:c + n]
+            c += n
+            if adam:
+                m, w = self.flat[mo:mo + n], self.flat[wo:wo + n]
+                m.mul_(b1).add_(g, alpha=1.0 - b1)
+                w.mul_(b2).addcmul_(g, g, value=1.0 - b2)
+                self.flat[vo:vo + n].addcdiv_(m, w.sqrt().add_(eps), value=-lr_t)
+            else:
+                self.flat[vo:vo + n].add_(g, alpha=-lr)
+
+    def _release_sync(self, value: int, op: int) -> None:
+        waiting, self.sync_waiting, self.sync_sum = self.sync_waiting, [], None
+        for r in waiting:
+            self._reply(torch.tensor([value], dtype=torch.int64), r, op)
+
     def serve_forever(self) -> None:
         hdr = torch.zeros(4, dtype=torch.int64)
         done_workers = 0
@@ -117,7 +175,7 @@ class GlooParamServer:
                 self.peer_errors += 1
                 time.sleep(0.01)
                 continue
-            op, a0, seq = int(hdr[0]), int(hdr[1]), int(hdr[2])
+            op, a0, seq, a3 = int(hdr[0]), int(hdr[1]), int(hdr[2]), int(hdr[3])
             # every request carries a per-client sequence number; anything else (an all-zero header or a
             # replay from a connection that went away) is not a request
             if op == 0 or src in self.dead or seq != last_seq.get(src, 0) + 1:
@@ -138,6 +196,29 @@ class GlooParamServer:
                 dist.recv(buf, src=src)
                 # ApplyGradientDescent on the ps: var -= lr * grad (TF1 T10); unsynchronised across workers
                 self.flat.add_(buf, alpha=-_bits_to_float(a0))
+            elif op == OP_PUSH_OPT:
+                flags, nv = a3 & 0xff, a3 >> 8
+                desc_t = torch.empty(max(4 * nv, 1), dtype=torch.int64)
+                dist.recv(desc_t, src=src)
+                desc = [int(x) for x in desc_t[:4 * nv]]
+                total = sum(desc[3::4])
+                payload = torch.empty(3 + total, dtype=torch.float32)
+                dist.recv(payload, src=src)
+                hyper = (float(payload[0]), float(payload[1]), float(payload[2]))
+                grads, lr, adam = payload[3:], _bits_to_float(a0), bool(flags & F_ADAM)
+                if not flags & F_SYNC:
+                    self._apply(desc, grads, lr, adam, hyper)             # asynchronous: apply at once
+                elif self.stop_requested:
+                    self._reply(torch.tensor([SYNC_ABORTED], dtype=torch.int64), src, op)
+                else:
+                    self.sync_sum = grads.clone() if self.sync_sum is None else self.sync_sum.add_(grads)
+                    self.sync_waiting.append(src)
+                    if len(self.sync_waiting) >= self.num_workers:        # the round is complete: one mean update
+                        self._apply(desc, self.sync_sum.div_(self.num_workers), lr, adam, hyper)
+                        self.step += 1
+                        self._release_sync(int(self.step.item()), op)
+            elif op == OP_ADAM_T_READ:
+                self._reply(torch.tensor([self.adam_t], dtype=torch.int64), src, op)
             elif op == OP_STEP_READ:
                 self._reply(self.step, src, op)
             elif op == OP_STEP_INC:
@@ -150,12 +231,15 @@ class GlooParamServer:
                 self.flat.copy_(buf[:max(n, 1)])
                 if a0 >= 0:
                     self.step[0] = a0
+                if a3 >= 0:
+                    self.adam_t = a3
             elif op == OP_IS_READY:
                 self._reply(torch.tensor([1 if self.ready else 0], dtype=torch.int64), src, op)
             elif op == OP_SET_READY:
                 self.ready = True
             elif op == OP_STOP_REQ:
                 self.stop_requested = True
+                self._release_sync(SYNC_ABORTED, op)      # nobody may be left waiting for a round that cannot complete
             elif op == OP_STOP_QUERY:
                 self._reply(torch.tensor([1 if self.stop_requested else 0], dtype=torch.int64), src, op)
             elif op == OP_SHUTDOWN:
@@ -186,6 +270,8 @@ def _locked(fn):
 
 
 class GlooParamClient(ParamClient):
+    adam_t_name = "global/adam_t"
+
     def __init__(self, variables: Sequence[VariableDef], cluster: ClusterSpec):
         self._lock = threading.RLock()
         self.variables = [v for v in variables if v.device.job == "ps"]
@@ -200,9 +286,9 @@ class GlooParamClient(ParamClient):
     def _rank(self, k: int) -> int:
         return self.cluster.global_rank("ps", k)
 
-    def _send_hdr(self, k: int, op: int, a0: int = 0) -> None:
+    def _send_hdr(self, k: int, op: int, a0: int = 0, a3: int = 0) -> None:
         self._seq[k] += 1
-        self._hdr[0], self._hdr[1], self._hdr[2] = op, a0, self._seq[k]
+        self._hdr[0], self._hdr[1], self._hdr[2], self._hdr[3] = op, a0, self._seq[k], a3
         dist.send(self._hdr, dst=self._rank(k))
         self.messages += 1
 
@@ -236,6 +322,49 @@ class GlooParamClient(ParamClient):
             dist.send(buf, dst=self._rank(k))
 
     @_locked
+    def push_opt(self, grads: Dict[str, torch.Tensor], lr: float, adam: Optional[dict] = None, sync: bool = False,
+                 timeout_s: float = 60.0) -> Optional[int]:
+        """Push with the optional modes (module docstring).  Asynchronous: returns None.  Synchronous: blocks
+        until every worker's push of this round has been applied as one mean update and returns the global
+        step AFTER it; raises ``SyncAborted`` if the round was released without an update or timed out."""
+        import datetime
+        use_adam = adam is not None
+        hyper = [adam.get("beta1", 0.9), adam.get("beta2", 0.999), adam.get("eps", 1e-8)] if use_adam else [0.0, 0.0, 0.0]
+        flags = (F_ADAM if use_adam else 0) | (F_SYNC if sync else 0)
+        active = []
+        for k, lay in enumerate(self.layouts):
+            if not lay.trainable and not (sync and lay.has_step):
+                continue
+            desc = lay.push_descriptor(use_adam)
+            nv = len(desc) // 4
+            payload = torch.empty(3 + sum(desc[3::4]), dtype=torch.float32)
+            payload[0], payload[1], payload[2] = hyper
+            c = 3
+            for v in lay.trainable:
+                payload[c:c + v.numel] = grads[v.name].reshape(-1)
+                c += v.numel
+            self._send_hdr(k, OP_PUSH_OPT, _float_to_bits(lr), flags | (nv << 8))
+            dist.send(torch.tensor(desc if desc else [0], dtype=torch.int64), dst=self._rank(k))
+            dist.send(payload, dst=self._rank(k))
+            active.append(k)
+        if not sync:
+            return None
+        new_step, aborted = None, False
+        for k in active:
+            t = torch.zeros(1, dtype=torch.int64)
+            try:
+                dist.irecv(t, src=self._rank(k)).wait(timeout=datetime.timedelta(seconds=timeout_s))
+            except RuntimeError as e:
+                raise SyncAborted(f"no answer from ps:{k} within {timeout_s:.0f} s: {str(e).splitlines()[0]}")
+            if int(t.item()) == SYNC_ABORTED:
+                aborted = True
+            elif k == self.step_task:
+                new_step = int(t.item())
+        if aborted or new_step is None:
+            raise SyncAborted("the round was released without an update (a peer left or stop was requested)")
+        return new_step
+
+    @_locked
     def read_step(self) -> int:
         self._send_hdr(self.step_task, OP_STEP_READ)
         t = torch.zeros(1, dtype=torch.int64)
@@ -265,7 +394,9 @@ class GlooParamClient(ParamClient):
                 o = lay.offsets[v.name]
                 buf[o:o + v.numel] = torch.from_numpy(np.ascontiguousarray(values[v.name], dtype=np.float32).reshape(-1))
             s = int(np.asarray(step).reshape(())) if (lay.has_step and step is not None) else -1
-            self._send_hdr(k, OP_ASSIGN, s)
+            # every task keeps its own Adam step count (each sees every push once): restore it everywhere
+            adam_t = values.get(self.adam_t_name)
+            self._send_hdr(k, OP_ASSIGN, s, int(np.asarray(adam_t).reshape(())) if adam_t is not None else -1)
             dist.send(buf, dst=self._rank(k))
 
     @_locked
@@ -273,6 +404,11 @@ class GlooParamClient(ParamClient):
         pulled = self.pull()
         out = {n: t.numpy().copy() for n, t in pulled.items()}
         out[self.global_step_name] = np.array(self.read_step(), dtype=np.int32)
+        if any(lay.has_adam_t for lay in self.layouts):
+            self._send_hdr(self.step_task, OP_ADAM_T_READ)
+            t = torch.zeros(1, dtype=torch.int64)
+            dist.recv(t, src=self._rank(self.step_task))
+            out[self.adam_t_name] = np.array(int(t.item()), dtype=np.int32)
         return {n: out[n] for n in names} if names is not None else out
 
     @_locked

@@ -8,6 +8,10 @@
   counter_op: global_step += 1                                    (separate message)
 
 Math is plain torch on CPU without autograd (the CPU stand-in for ``allow_soft_placement``).
+
+``optimizer="adam"`` and ``sync=True`` select the ps-side modes of ``parallel/gloo_ps.py`` (not in the
+reference): the worker's side of the step is unchanged except that a synchronous push blocks until the
+round's mean update has been applied and returns the step, so ``counter_op`` has nothing left to do.
 """
 from __future__ import annotations
 
@@ -22,8 +26,11 @@ from .replica import ReplicatedModel
 
 
 class CpuStepEngine:
-    def __init__(self, model: ReplicatedModel, client: GlooParamClient, lr: float, push_delay_s: float = 0.0):
+    def __init__(self, model: ReplicatedModel, client: GlooParamClient, lr: float, push_delay_s: float = 0.0,
+                 optimizer: str = "sgd", sync: bool = False, sync_timeout_s: float = 30.0):
         self.model, self.client, self.lr = model, client, lr
+        self.adam = {} if optimizer == "adam" else None      # default betas/eps of tf.train.AdamOptimizer
+        self.sync, self.sync_timeout_s = sync, sync_timeout_s
         self.pairs = model.sync_pairs()
         self.local: Dict[str, torch.Tensor] = {}
         self.push_delay_s = push_delay_s
@@ -74,11 +81,21 @@ class CpuStepEngine:
                 d = (d @ self.local[names_local[2 * l]].t()) * h_in * (1 - h_in)
         if self.push_delay_s:
             time.sleep(self.push_delay_s)
-        self.client.push(grads, self.lr)
-        step = self.client.read_step()
+        if self.sync:
+            # the answer is the global step after this round's single mean update: the step this worker's
+            # gradients were computed for is the one before it
+            step = self.client.push_opt(grads, self.lr, adam=self.adam, sync=True, timeout_s=self.sync_timeout_s) - 1
+        else:
+            if self.adam is not None:
+                self.client.push_opt(grads, self.lr, adam=self.adam)
+            else:
+                self.client.push(grads, self.lr)
+            step = self.client.read_step()
         return float(loss), float(acc), step
 
     def counter_op(self) -> int:
+        if self.sync:
+            return -1        # the ps counted the aggregated update when it applied it
         return self.client.increment_step(1)
 
     def accuracy(self, images: np.ndarray, labels: np.ndarray) -> float:

@@ -29,6 +29,7 @@ from ..models.mlp import spec_from_flags
 from ..utils.checkpoint import FastSaver
 from ..utils.events import FileWriter, training_summary
 from ..utils import tracing
+from ..parallel.gloo_ps import SyncAborted
 from .replica import build_replicated_model
 from .supervisor import Supervisor
 
@@ -63,11 +64,7 @@ class Worker:
         self.spec = spec_from_flags(flags.hidden, dtype=flags.dtype if server.backend == "cuda" else "float32")
         # C8: two copies of the net, global on the ps job, local on this worker
         self.model = build_replicated_model(self.spec, job_name, task_index, num_ps=server.num_ps,
-                                            ps_strategy=flags.ps_strategy,
-                                            optimizer=flags.optimizer if server.backend == "cuda" else "sgd")
-        if server.backend != "cuda" and (flags.sync or flags.optimizer != "sgd"):
-            raise ValueError("--sync and --optimizer adam are implemented on the CUDA path (the gloo "
-                             "configuration reproduces the reference's async SGD only)")
+                                            ps_strategy=flags.ps_strategy, optimizer=flags.optimizer)
         self.global_step = self.model.global_step
         if flags.log_device_placement:
             for v in self.model.store.all_variables():
@@ -85,7 +82,9 @@ class Worker:
         from .cpu_step import CpuStepEngine
         self.client = GlooParamClient(self.model.global_all, self.server.cluster)
         self.engine = CpuStepEngine(self.model, self.client, self.flags.learning_rate,
-                                    push_delay_s=self.faults.get("delay_push", 0.0))
+                                    push_delay_s=self.faults.get("delay_push", 0.0),
+                                    optimizer=self.flags.optimizer, sync=self.flags.sync,
+                                    sync_timeout_s=self.flags.sync_timeout_secs)
         self.trainer = None
 
     def _build_cuda(self) -> None:
@@ -194,8 +193,9 @@ class Worker:
             try:
                 last_step = run(sv, dataset)
             finally:
-                if getattr(self, "sync_group", None) is not None:
-                    # tell the peers' spinning sync kernels that this rank is gone (they skip the update)
+                if getattr(self, "sync_group", None) is not None or (self.trainer is None and f.sync):
+                    # tell the peers' spinning sync kernels (CUDA) / the ps holding their round (gloo) that this
+                    # rank is gone, so nobody waits for a round that cannot complete
                     try:
                         self.client.request_stop()
                     except Exception:
@@ -236,8 +236,12 @@ class Worker:
             with tr.span("sync_op(pull)", "step"):
                 eng.sync_op()                                                    # reference :131
             batch_x, batch_y = dataset.train.next_batch(f.batch_size)           # :133
-            with tr.span("train_op(fwd/bwd/push)", "step"):
-                cost, acc, step = eng.train_op(batch_x, batch_y)                 # :135-137
+            try:
+                with tr.span("train_op(fwd/bwd/push)", "step"):
+                    cost, acc, step = eng.train_op(batch_x, batch_y)             # :135-137
+            except SyncAborted as e:
+                print(f"sync: a peer left, stopping ({e})", flush=True)
+                break
             with tr.span("counter_op", "step"):
                 eng.counter_op()                                                 # :141 (summary :139 is in _after_step)
             if self._after_step(step, cost, acc, lambda: eng.accuracy(dataset.test.images, dataset.test.labels)):

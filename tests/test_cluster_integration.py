@@ -132,3 +132,52 @@ def test_trace_file_from_a_real_cluster(tmp_path):
     assert nsteps >= 120
     assert {"checkpoint.snapshot", "checkpoint.write"} <= names[0]          # only the chief saves
     assert "checkpoint.write" not in names[1]
+
+
+def _losses(logdir, task):
+    return [(e.step, v.simple_value) for e in _events(f"{logdir}_{task}") for v in e.summary.value if v.tag == "local/loss"]
+
+
+def test_cpu_sync_mode_rounds_are_shared_by_all_workers(tmp_path):
+    """--sync on the gloo configuration: one mean update and one global_step increment per round, and every
+    worker observes every step exactly once."""
+    cl, logdir = _cluster(tmp_path, extra=["--training_steps", "40", "--learning_rate", "0.05", "--sync"])
+    cl.start()
+    codes = cl.wait(timeout=240)
+    assert all(c == 0 for c in codes.values()), (codes, cl.lines)
+    l0, l1 = _losses(logdir, 0), _losses(logdir, 1)
+    assert [s for s, _ in l0] == list(range(41)) and [s for s, _ in l1] == list(range(41))    # steps 0..40, both workers
+    vals = ckpt.FastSaver(["global/global_step"]).restore(ckpt.latest_checkpoint(logdir))
+    assert int(vals["global/global_step"]) <= 41
+    assert np.mean([v for _, v in l0[-5:]]) < np.mean([v for _, v in l0[:5]])                   # it trains
+
+
+def test_cpu_adam_and_sync_adam(tmp_path):
+    cl, logdir = _cluster(tmp_path, extra=["--training_steps", "150", "--learning_rate", "0.01", "--optimizer", "adam"])
+    cl.start()
+    codes = cl.wait(timeout=240)
+    assert all(c == 0 for c in codes.values()), (codes, cl.lines)
+    names = ["global/dense/kernel", "global/dense/kernel/Adam", "global/dense/kernel/Adam_1", "global/adam_t",
+             "global/global_step"]
+    vals = ckpt.FastSaver(names).restore(ckpt.latest_checkpoint(logdir))
+    assert vals["global/dense/kernel/Adam"].shape == (784, 100) and np.abs(vals["global/dense/kernel/Adam"]).max() > 0
+    assert vals["global/dense/kernel/Adam_1"].min() >= 0 and vals["global/dense/kernel/Adam_1"].max() > 0
+    assert 0 < int(vals["global/adam_t"]) <= int(vals["global/global_step"]) + 2      # one Adam step per push
+    l0 = _losses(logdir, 0)
+    assert np.mean([v for _, v in l0[-10:]]) < np.mean([v for _, v in l0[:10]])
+    # synchronous Adam: the two modes compose
+    cl, logdir2 = _cluster(tmp_path / "s", extra=["--training_steps", "30", "--learning_rate", "0.01", "--optimizer",
+                                                 "adam", "--sync"])
+    cl.start()
+    codes = cl.wait(timeout=240)
+    assert all(c == 0 for c in codes.values()), (codes, cl.lines)
+    assert [s for s, _ in _losses(logdir2, 1)] == list(range(31))
+
+
+def test_cpu_sync_survivor_stops_when_a_peer_dies(tmp_path):
+    cl, logdir = _cluster(tmp_path, extra=["--training_steps", "100000", "--sync", "--fault", "kill_worker:1@15",
+                                           "--sync_timeout_secs", "3"])
+    cl.start()
+    codes = cl.wait(timeout=240)
+    assert codes["worker1"] == 17 and codes["worker0"] == 0, (codes, cl.lines)
+    assert any(l.startswith("sync: a peer left, stopping") for l in cl.lines["worker0"])

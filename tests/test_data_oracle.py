@@ -81,3 +81,35 @@ def test_reference_init_loss_and_sgd_progress():
     assert np.mean(losses[-20:]) < 0.5 * np.mean(losses[:20])
     f = oracle.flops_per_step((784, 100, 10), 100)
     assert f["fwd"] == pytest.approx(15.88e6, rel=1e-3) and f["step"] == pytest.approx(31.96e6, rel=1e-3)
+
+
+def test_gloo_ps_apply_matches_oracle_sgd_and_adam():
+    """The ps-side update rules of the gloo configuration (parallel/gloo_ps.py::_apply) against the numpy oracle:
+    TF1 ApplyGradientDescent and ApplyAdam on a flat vector holding var | m | v."""
+    import torch
+    from distributedtensorflowexample_b200.models import oracle
+    from distributedtensorflowexample_b200.parallel.gloo_ps import GlooParamServer
+    rng = np.random.default_rng(0)
+    n = 37
+    w0 = rng.normal(size=n).astype(np.float32)
+    grads = [rng.normal(size=n).astype(np.float32) for _ in range(4)]
+    # SGD
+    ps = GlooParamServer(0, 1)
+    ps.flat = torch.from_numpy(w0.copy())
+    ref = [w0.astype(np.float64).copy()]
+    for g in grads:
+        ps._apply([0, -1, -1, n], torch.from_numpy(g), 0.05, False, (0.0, 0.0, 0.0))
+        ref[0] -= 0.05 * g
+    np.testing.assert_allclose(ps.flat.numpy(), ref[0], rtol=1e-5, atol=1e-6)
+    # Adam: moments live in the same flat vector, after the variable
+    ps = GlooParamServer(0, 1)
+    ps.flat = torch.cat([torch.from_numpy(w0.copy()), torch.zeros(2 * n)])
+    ref = [w0.astype(np.float64).copy()]
+    st = oracle.AdamState(ref)
+    for g in grads:
+        ps._apply([0, n, 2 * n, n], torch.from_numpy(g), 0.01, True, (0.9, 0.999, 1e-8))
+        st.apply(ref, [g.astype(np.float64)], 0.01)
+    assert ps.adam_t == 4
+    np.testing.assert_allclose(ps.flat[:n].numpy(), ref[0], rtol=1e-4, atol=1e-6)
+    np.testing.assert_allclose(ps.flat[n:2 * n].numpy(), st.m[0], rtol=1e-4, atol=1e-7)
+    np.testing.assert_allclose(ps.flat[2 * n:].numpy(), st.v[0], rtol=1e-4, atol=1e-8)
