@@ -181,3 +181,18 @@ def test_cpu_sync_survivor_stops_when_a_peer_dies(tmp_path):
     codes = cl.wait(timeout=240)
     assert codes["worker1"] == 17 and codes["worker0"] == 0, (codes, cl.lines)
     assert any(l.startswith("sync: a peer left, stopping") for l in cl.lines["worker0"])
+
+
+def test_cpu_sync_adam_with_two_ps_tasks(tmp_path):
+    """Synchronous Adam with the variables spread over two ps tasks: every task runs its own round barrier,
+    only the task that owns global_step counts, and every task keeps the same Adam step count."""
+    cl, logdir = _cluster(tmp_path, num_ps=2, extra=["--training_steps", "25", "--learning_rate", "0.01",
+                                                     "--optimizer", "adam", "--sync"])
+    cl.start()
+    codes = cl.wait(timeout=240)
+    assert all(c == 0 for c in codes.values()), (codes, cl.lines)
+    assert [s for s, _ in _losses(logdir, 0)] == list(range(26)) == [s for s, _ in _losses(logdir, 1)]
+    vals = ckpt.FastSaver(["global/dense/bias/Adam_1", "global/dense_1/kernel/Adam_1", "global/adam_t",
+                           "global/global_step"]).restore(ckpt.latest_checkpoint(logdir))
+    assert vals["global/dense/bias/Adam_1"].max() > 0 and vals["global/dense_1/kernel/Adam_1"].max() > 0   # both tasks applied
+    assert int(vals["global/adam_t"]) == int(vals["global/global_step"])                                  # one per round
