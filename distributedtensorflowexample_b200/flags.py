@@ -13,6 +13,7 @@ eight keep their names and defaults.
 """
 from __future__ import annotations
 
+import os
 import sys
 from typing import Any, Callable, Dict, List, Optional
 
@@ -63,6 +64,11 @@ class FlagValues:
             if not tok.startswith("-") or tok in ("-", "--"):
                 rest.append(tok)
                 continue
+            if tok in ("-h", "--help", "--helpfull", "--helpshort"):
+                # tf.app.flags is argparse underneath: asking for help prints the flags and exits 0
+                # (without this, `python main.py --help` would start the default role - a ps that never returns)
+                print(f"usage: {os.path.basename(sys.argv[0] or 'main.py')} [flags]\n\nflags:\n{self.usage()}")
+                raise SystemExit(0)
             body = tok.lstrip("-")
             if "=" in body:
                 name, text = body.split("=", 1)

@@ -257,3 +257,15 @@ def test_flag_parser_property(bs, lr, logdir, job, eq, noise, order):
     rest = fv.parse(list(argv))
     assert fv.batch_size == bs and fv.learning_rate == lr and fv.logdir == logdir and fv.job_name == job
     assert rest == [a for a in argv if a in ("--unknown_a=1", "--unknown_b", "stray")]
+
+
+def test_help_prints_flags_and_exits_zero(capsys):
+    fv = _flags()
+    with pytest.raises(SystemExit) as e:
+        fv.parse(["--job_name", "worker", "--help"])
+    assert e.value.code == 0
+    out = capsys.readouterr().out
+    assert "--learning_rate (float, default 0.001)" in out and "--job_name (string, default 'ps')" in out
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "main.py", "--help"], cwd=root, capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0 and "--training_steps" in r.stdout        # and does not start the default ps role
