@@ -27,10 +27,15 @@ from .replica import ReplicatedModel
 
 class CpuStepEngine:
     def __init__(self, model: ReplicatedModel, client: GlooParamClient, lr: float, push_delay_s: float = 0.0,
-                 optimizer: str = "sgd", sync: bool = False, sync_timeout_s: float = 30.0):
+                 optimizer: str = "sgd", sync: bool = False, sync_timeout_s: float = 30.0,
+                 first_round_grace_s: float = 0.0):
         self.model, self.client, self.lr = model, client, lr
         self.adam = {} if optimizer == "adam" else None      # default betas/eps of tf.train.AdamOptimizer
         self.sync, self.sync_timeout_s = sync, sync_timeout_s
+        # The first round also has to wait for workers that are still polling for the chief's initialisation
+        # (every recovery_wait_secs, 30 s by default like TF1): they join up to one poll period late.
+        self._first_round_grace_s = first_round_grace_s
+        self._rounds = 0
         self.pairs = model.sync_pairs()
         self.local: Dict[str, torch.Tensor] = {}
         self.push_delay_s = push_delay_s
@@ -84,7 +89,9 @@ class CpuStepEngine:
         if self.sync:
             # the answer is the global step after this round's single mean update: the step this worker's
             # gradients were computed for is the one before it
-            step = self.client.push_opt(grads, self.lr, adam=self.adam, sync=True, timeout_s=self.sync_timeout_s) - 1
+            timeout = self.sync_timeout_s + (self._first_round_grace_s if self._rounds == 0 else 0.0)
+            step = self.client.push_opt(grads, self.lr, adam=self.adam, sync=True, timeout_s=timeout) - 1
+            self._rounds += 1
         else:
             if self.adam is not None:
                 self.client.push_opt(grads, self.lr, adam=self.adam)

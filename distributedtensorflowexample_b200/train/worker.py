@@ -84,7 +84,8 @@ class Worker:
         self.engine = CpuStepEngine(self.model, self.client, self.flags.learning_rate,
                                     push_delay_s=self.faults.get("delay_push", 0.0),
                                     optimizer=self.flags.optimizer, sync=self.flags.sync,
-                                    sync_timeout_s=self.flags.sync_timeout_secs)
+                                    sync_timeout_s=self.flags.sync_timeout_secs,
+                                    first_round_grace_s=2.0 * self.flags.recovery_wait_secs)
         self.trainer = None
 
     def _build_cuda(self) -> None:
