@@ -121,7 +121,9 @@ class Worker:
                     kv.set(f"sync/{me}", pickle.dumps(blob))
                     return [pickle.loads(kv.get(f"sync/{r}")) for r in range(W)]
                 # variable on ps shard k is reduced by worker (k mod W)
-                self.sync_group = SyncGroup(store, names, me, W, exchange=exchange)
+                # a round may have to wait for workers that are still polling for the chief's initialisation
+                self.sync_group = SyncGroup(store, names, me, W, exchange=exchange,
+                                            timeout_s=f.sync_timeout_secs + 2.0 * f.recovery_wait_secs)
                 kw["grad_buffers"] = self.sync_group.grad_views({n: tuple(store.tensor(n).shape) for n in names})
             else:
                 kw["adam"] = dict(slots=[store.tensor(n + "/grad_slot") for n in names],
