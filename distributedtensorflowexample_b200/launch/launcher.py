@@ -191,6 +191,7 @@ def main(argv: Optional[Sequence[str]] = None) -> int:
     ap.add_argument("--log_dir", default=None)
     ap.add_argument("--no-attach", action="store_true")
     args, extra = ap.parse_known_args(argv)
+    extra = [a for a in extra if a != "--"]      # `launcher ... -- --training_steps 200`: the separator is not a flag
     gpu_ids = [g for g in args.gpu_id.replace(",", " ").split() if g]
     tasks = task_commands(args.num_workers, args.num_gpus, gpu_ids, args.num_ps, args.device, extra)
     if args.mode == "print":

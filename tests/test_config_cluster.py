@@ -269,3 +269,30 @@ def test_help_prints_flags_and_exits_zero(capsys):
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     r = subprocess.run([sys.executable, "main.py", "--help"], cwd=root, capture_output=True, text=True, timeout=120)
     assert r.returncode == 0 and "--training_steps" in r.stdout        # and does not start the default ps role
+
+
+def test_shutdown_signal_ends_a_task_stuck_in_native_code(tmp_path):
+    """SIGTERM while the main thread cannot run Python handlers (signals masked, like during a gloo exchange, or
+    a native rendezvous that never returns): the watchdog exits with the handler's code after the grace period."""
+    import signal as sig
+    import time
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = ("import signal, time, sys\n"
+            f"sys.path.insert(0, {root!r})\n"
+            "from distributedtensorflowexample_b200.utils.signals import install_shutdown_handlers, HANDLED\n"
+            "install_shutdown_handlers(grace_s=1.0)\n"
+            "signal.pthread_sigmask(signal.SIG_BLOCK, set(HANDLED))\n"
+            "print('ready', flush=True)\n"
+            "time.sleep(120)\n")
+    p = subprocess.Popen([sys.executable, "-c", code], stdout=subprocess.PIPE, text=True)
+    assert p.stdout.readline().strip() == "ready"
+    t0 = time.time()
+    p.send_signal(sig.SIGTERM)
+    assert p.wait(timeout=30) == 143 and time.time() - t0 < 15
+    # and the ordinary path is unchanged: an interruptible main thread leaves through SystemExit at once
+    code2 = code.replace("signal.pthread_sigmask(signal.SIG_BLOCK, set(HANDLED))\n", "")
+    p = subprocess.Popen([sys.executable, "-c", code2], stdout=subprocess.PIPE, text=True)
+    assert p.stdout.readline().strip() == "ready"
+    t0 = time.time()
+    p.send_signal(sig.SIGINT)
+    assert p.wait(timeout=30) == 130 and time.time() - t0 < 0.9
