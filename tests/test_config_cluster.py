@@ -296,3 +296,10 @@ def test_shutdown_signal_ends_a_task_stuck_in_native_code(tmp_path):
     t0 = time.time()
     p.send_signal(sig.SIGINT)
     assert p.wait(timeout=30) == 130 and time.time() - t0 < 0.9
+
+
+def test_launcher_cli_forwards_flags_after_a_double_dash(capsys):
+    from distributedtensorflowexample_b200.launch import launcher
+    assert launcher.main(["--mode", "print", "--num_workers", "2", "--device", "cpu", "--", "--training_steps", "7"]) == 0
+    out = capsys.readouterr().out
+    assert "--training_steps 7" in out and " -- " not in out         # a bare '--' would end flag parsing in every task
