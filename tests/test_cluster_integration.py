@@ -196,3 +196,15 @@ def test_cpu_sync_adam_with_two_ps_tasks(tmp_path):
                            "global/global_step"]).restore(ckpt.latest_checkpoint(logdir))
     assert vals["global/dense/bias/Adam_1"].max() > 0 and vals["global/dense_1/kernel/Adam_1"].max() > 0   # both tasks applied
     assert int(vals["global/adam_t"]) == int(vals["global/global_step"])                                  # one per round
+
+
+def test_ps_crash_takes_the_workers_down(tmp_path):
+    """a ps crash loses the state; the workers' next exchange raises and they exit (non-zero),
+    nothing restarts anything.  --fault kill_ps:<seconds> is the injection hook."""
+    cl, logdir = _cluster(tmp_path, extra=["--training_steps", "100000000", "--fault", "kill_ps:4"])
+    cl.start()
+    t0 = time.time()
+    codes = cl.wait(timeout=240)
+    assert codes["ps"] == 19 and codes["worker0"] not in (0, None) and codes["worker1"] not in (0, None), codes
+    assert time.time() - t0 < 120
+    assert any("fault injection: ps dies" in l for l in cl.lines["ps"])
