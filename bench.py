@@ -41,6 +41,15 @@ def parse_args():
     ap.add_argument("--e2e-steps-per-launch", type=int, default=8,
                     help="host-fed steps that share one kernel launch in the end-to-end measurement (1..16)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--repeats", type=int, default=25, help="timed samples of K steps each (median is reported)")
+    ap.add_argument("--no-baseline", dest="no_baseline", action="store_true",
+                    help="skip the in-run NCCL baseline (vs_baseline stays null)")
+    ap.add_argument("--no-entry", dest="no_entry", action="store_true",
+                    help="skip the launcher-path (main.py) measurement")
+    ap.add_argument("--entry-steps", dest="entry_steps", type=int, default=0,
+                    help="training steps per worker of the launcher-path measurement (0 = 300000)")
+    ap.add_argument("--entry-multi", dest="entry_multi", action="store_true",
+                    help="with 4 GPUs also run the reference's 16 workers / 4 GPUs topology")
     return ap.parse_args()
 
 

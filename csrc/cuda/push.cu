@@ -77,8 +77,8 @@ __global__ void __launch_bounds__(256) k_adam_apply(float* __restrict__ p, float
   size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   size_t stride = (size_t)gridDim.x * blockDim.x;
   for (; i < n; i += stride) {
-    float g = dtfe::ld_relaxed_sys(slot + i) * gscale;
-    slot[i] = 0.f;
+    // swap the mailbox out in ONE atomic: a push that lands between a separate load and store would be lost
+    float g = atomicExch_system(slot + i, 0.f) * gscale;
     float mi = b1 * m[i] + (1.f - b1) * g;
     float vi = b2 * v[i] + (1.f - b2) * g * g;
     m[i] = mi; v[i] = vi;

@@ -104,6 +104,19 @@ DTFE_HOST_API int dtfe_events_write_scalars_batch(void* h, double wall_time, con
   return 0;
 }
 
+// The per-step loss/accuracy summaries of one multi-step kernel launch, read straight from the arrays the GPU
+// results were copied into (int32 observed global step, fp32 loss, fp32 accuracy per step): no per-value
+// marshalling on the Python side.  Same bytes as dtfe_events_write_scalars(step[i], {tag0: loss[i], tag1: acc[i]}).
+DTFE_HOST_API int dtfe_events_write_pairs_i32(void* h, double wall_time, const int32_t* steps, const float* v0,
+                                              const float* v1, int n, const char* tag0, const char* tag1) {
+  const char* tags[2] = {tag0, tag1};
+  for (int i = 0; i < n; ++i) {
+    const float vals[2] = {v0[i], v1[i]};
+    if (int rc = dtfe_events_write_scalars(h, wall_time, steps[i], tags, vals, 2)) return rc;
+  }
+  return 0;
+}
+
 // Event{wall_time, step, session_log{status, checkpoint_path, msg}}; status: 1 START, 2 STOP, 3 CHECKPOINT
 DTFE_HOST_API int dtfe_events_write_session_log(void* h, double wall_time, int64_t step, int status,
                                                 const char* checkpoint_path, const char* msg) {

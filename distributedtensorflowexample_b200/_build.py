@@ -3,7 +3,7 @@
 * ``_lib/libdtfe_cuda.so``  - every CUDA kernel, compiled for sm_100a only
   (``-gencode arch=compute_100a,code=sm_100a -lineinfo``), C ABI (``include/dtfe_b200.h``).
 * ``_lib/libdtfe_host.so``  - the C++ runtime pieces that need no GPU: crc32c, SSTable,
-  TF1 tensor-bundle checkpoints, tfevents, idx/gzip reader, TCP rendezvous.
+  TF1 tensor-bundle checkpoints, tfevents, idx/gzip reader (the rendezvous is torch's TCPStore, train/server.py).
 
 The reference ships no native code at all; these replace the parts of the TF1
 runtime it leans on.  Both libraries are loaded with ctypes, so the built ``.so`` files

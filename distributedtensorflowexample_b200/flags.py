@@ -210,7 +210,9 @@ def define_framework_flags(flag_values: FlagValues = FLAGS) -> FlagValues:
     DEFINE_float("save_summaries_secs", 30, "Chief global_step/sec summary period (reference: 30)", flag_values)
     DEFINE_integer("log_every", 100, "Print step/cost/speed when global step %% this == 0 (reference: 100)", flag_values)
     DEFINE_integer("eval_every", 10000, "Test-set accuracy when global step %% this == 0 (reference: 10000)", flag_values)
-    DEFINE_integer("steps_per_launch", 1, "Training steps fused into one persistent kernel launch", flag_values)
+    DEFINE_integer("steps_per_launch", 0, "Training steps fused into one persistent kernel launch; 0 = adaptive (up to "
+                   "256, shrinking towards evaluation steps and training_steps), 1 = one launch per step like one "
+                   "sess.run per step", flag_values)
     DEFINE_string("ps_strategy", "round_robin", "round_robin | greedy_bytes variable placement", flag_values)
     DEFINE_boolean("log_device_placement", False, "Print where every variable was placed (TF1 ConfigProto option; "
                    "the reference sets it to False)", flag_values)

@@ -2,7 +2,10 @@
 
 Keeps the reference's knobs - ``name`` (tmux session), ``num_workers``, ``num_gpus``, ``GPU_ID`` array -
 and its process model: one ps process per ps task + one worker process per worker task on localhost,
-worker ``i`` pinned to ``GPU_ID[i % num_gpus]`` through ``CUDA_VISIBLE_DEVICES``.
+worker ``i`` pinned to ``GPU_ID[i % num_gpus]`` through ``CUDA_VISIBLE_DEVICES``: that GPU comes FIRST in
+the task's list, so ``gpu:0`` is the task's own GPU exactly as in the reference, and the cluster's other
+GPUs follow it.  They are listed only so that the task can map the parameter shards that live there:
+CUDA IPC (``cudaIpcOpenMemHandle``) cannot open memory of a GPU the opening process does not see.
 
 Two modes:
   * ``--mode tmux``     : one tmux session, one window per task, like the reference (attach with
@@ -42,13 +45,18 @@ def task_commands(num_workers: int, num_gpus: int, gpu_ids: Sequence[str], num_p
               "--device", device, *extra]
     cpu_only = device == "cpu"
     tasks = []
+
+    def visible(j: int) -> str:
+        """Own GPU first (= cuda:0 of the task), then the other GPUs of the cluster for peer mapping."""
+        own = str(gpu_ids[j % num_gpus])
+        return ",".join([own] + [str(g) for g in gpu_ids[:num_gpus] if str(g) != own])
     for k in range(num_ps):
-        vis = "" if cpu_only else str(gpu_ids[k % num_gpus])
+        vis = "" if cpu_only else visible(k)
         tasks.append(dict(name=f"ps{k}" if num_ps > 1 else "ps", job="ps", index=k,
                           env={"CUDA_VISIBLE_DEVICES": vis},
                           argv=[python, MAIN, *common, "--job_name", "ps", f"--task_index={k}"]))
     for i in range(num_workers):
-        vis = "" if cpu_only else str(gpu_ids[i % num_gpus])          # ID=$((i % num_gpus)), reference :20
+        vis = "" if cpu_only else visible(i)                          # ID=$((i % num_gpus)), reference :20
         tasks.append(dict(name=f"worker{i}", job="worker", index=i, env={"CUDA_VISIBLE_DEVICES": vis},
                           argv=[python, MAIN, *common, "--job_name", "worker", "--task_index", str(i)]))
     return tasks

@@ -418,8 +418,10 @@ class Mlp2Step:
 
     def run(self, W1, b1, W2, b2, global_step, X, labels, lr: float, nsteps: int = 1, batch_idx=None,
             rows_per_step: int = 0, atomic: bool = True, train: bool = True, out_offset: int = 0,
-            remote: bool = True, dbg=None, grads=None, cursor=None, sync_exchange=None):
-        assert nsteps + out_offset <= self.max_steps
+            remote: bool = True, dbg=None, grads=None, cursor=None, sync_exchange=None, outs=None):
+        """``outs``: (loss, acc, step) device tensors (float32, float32, int32; >= nsteps elements each) that receive
+        the per-step results instead of this object's own ring."""
+        assert outs is not None or nsteps + out_offset <= self.max_steps
         L = _Mlp2Launch()
         L.B, L.D, L.H, L.C, L.ks = self.B, self.D, self.H, self.C, self.ks
         L.W1, L.b1, L.W2, L.b2 = W1.data_ptr(), b1.data_ptr(), W2.data_ptr(), b2.data_ptr()
@@ -432,6 +434,10 @@ class Mlp2Step:
         L.loss_out = self.loss.data_ptr() + 4 * out_offset
         L.acc_out = self.acc.data_ptr() + 4 * out_offset
         L.step_out = self.step.data_ptr() + 4 * out_offset
+        if outs is not None:
+            lo, ao, so = outs
+            assert lo.numel() >= nsteps and ao.numel() >= nsteps and so.numel() >= nsteps and so.dtype == torch.int32
+            L.loss_out, L.acc_out, L.step_out = lo.data_ptr(), ao.data_ptr(), so.data_ptr()
         L.lr, L.nsteps, L.atomic, L.train = lr, nsteps, int(atomic), int(train)
         L.remote = int(remote)
         L.dbg = _ptr(dbg)

@@ -428,7 +428,8 @@ class GlooParamClient(ParamClient):
 
     @_locked
     def request_stop(self):
-        self._send_hdr(0, OP_STOP_REQ)
+        for k in range(self.num_ps):      # every ps task runs its own round barrier in synchronous mode
+            self._send_hdr(k, OP_STOP_REQ)
 
     @_locked
     def stop_requested(self) -> bool:

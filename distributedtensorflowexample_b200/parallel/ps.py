@@ -204,5 +204,12 @@ class PeerParamStore:
         for k in range(self.num_shards):
             self.header(k)[H_STOP] = 1
 
+    def clear_stop(self) -> None:
+        """A new generation of workers starts against shards that outlived the previous one (the reference's
+        recovery model: restart the workers, the ps stays up): forget the old generation's stop request."""
+        for k in range(self.num_shards):
+            self.header(k)[H_STOP] = 0
+        torch.cuda.synchronize(self.device)
+
     def stop_requested(self) -> bool:
         return any(int(self.header(k)[H_STOP].item()) != 0 for k in range(self.num_shards))

@@ -79,12 +79,13 @@ class FusedMlp2Stepper:
                 and spec.dims[2] <= 16 and (spec.dims[0] + 7) // 8 <= 148)
 
     def run(self, X: torch.Tensor, labels: torch.Tensor, nsteps: int = 1, batch_idx: Optional[torch.Tensor] = None,
-            rows_per_step: int = 0, train: bool = True, out_offset: int = 0) -> None:
-        """Results land in ``self.k.loss/acc/step[out_offset : out_offset+nsteps]`` (device)."""
+            rows_per_step: int = 0, train: bool = True, out_offset: int = 0, outs=None) -> None:
+        """Results land in ``self.k.loss/acc/step[out_offset : out_offset+nsteps]`` (device), or in the three
+        tensors ``outs`` when given."""
         self.k.run(self.W1, self.b1, self.W2, self.b2, self.global_step, X, labels, self.lr, nsteps=nsteps,
                    batch_idx=batch_idx, rows_per_step=rows_per_step, atomic=self.atomic, train=train,
                    out_offset=out_offset, remote=self.remote, dbg=self.dbg, grads=self.grad_buffers,
-                   cursor=self.cursor, sync_exchange=self.sync_exchange)
+                   cursor=self.cursor, sync_exchange=self.sync_exchange, outs=outs)
 
     @property
     def loss(self): return self.k.loss
@@ -110,7 +111,7 @@ class LayerwiseStepper:
         are pushed (red.add, unscaled) into the owner-side slots; the rank with ``apply=True`` (the chief)
         then runs the owner-side Adam kernel over every variable, consuming and clearing the slots."""
         self.adam = adam
-        self._adam_t = 0
+        self._adam_t = None        # read from adam['t'] (the global/adam_t shard variable) at the first apply
         self.tf32 = tf32
         if tf32:
             from ..ops import gemm_tc
@@ -191,12 +192,17 @@ class LayerwiseStepper:
             d = d_prev
         if self.adam is not None and self.adam.get("apply", True):
             import math
+            t_var = self.adam.get("t")
+            if self._adam_t is None:     # after the chief's init-or-restore: continue the restored count
+                self._adam_t = int(t_var.item()) if t_var is not None else 0
             self._adam_t += 1
             b1, b2, eps = self.adam.get("beta1", 0.9), self.adam.get("beta2", 0.999), self.adam.get("eps", 1e-8)
             lr_t = self.lr * math.sqrt(1.0 - b2 ** self._adam_t) / (1.0 - b1 ** self._adam_t)
             for i, p in enumerate(self.params):
                 ops.adam_apply(p.view(-1), self.adam["m"][i].view(-1), self.adam["v"][i].view(-1),
                                self.adam["slots"][i].view(-1), lr_t, b1, b2, eps)
+            if t_var is not None:       # checkpointed next to m and v (TF1 keeps beta powers; the gloo ps keeps this count)
+                ops.global_step_add(t_var, 1)
         if self.grad_buffers is None:
             ops.global_step_add(self.global_step, 1, self.step)
 

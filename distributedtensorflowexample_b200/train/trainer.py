@@ -19,6 +19,13 @@ from ..models.mlp import MLPSpec
 from .gpu_step import DeviceDataset, FusedMlp2Stepper, LayerwiseStepper, TcStepper
 
 
+class LaunchTicket:
+    __slots__ = ("slot", "nsteps", "event")
+
+    def __init__(self, slot: int, nsteps: int, event):
+        self.slot, self.nsteps, self.event = slot, nsteps, event
+
+
 class GpuTrainer:
     def __init__(self, spec: MLPSpec, batch: int, lr: float, params: Sequence[torch.Tensor],
                  global_step: torch.Tensor, device, steps_per_launch: int = 1, atomic: bool = True,
@@ -53,6 +60,7 @@ class GpuTrainer:
         self._stage: List[Tuple[torch.Tensor, torch.Tensor, torch.cuda.Event, torch.cuda.Event]] = []
         self._host_out: Optional[torch.Tensor] = None
         self._slot = 0
+        self._ring_dev = None
 
     # ---- device-resident data ---------------------------------------------------------
     def train_device_steps(self, dataset: DeviceDataset, nsteps: int) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
@@ -75,6 +83,49 @@ class GpuTrainer:
                 last = (self.layer.loss, self.layer.acc, self.layer.step)
             done += n
         return last
+
+    # ---- pipelined launches (what Worker.learn drives) --------------------------------------
+    def launch_async(self, dataset: DeviceDataset, nsteps: int, ring_depth: int = 3, ring_cap: int = 512) -> "LaunchTicket":
+        """Enqueue ``nsteps`` (<= ``ring_cap``) training steps as ONE launch group plus the device->host copy of
+        their per-step (loss, accuracy, observed global step), and return without waiting.  ``collect(ticket)``
+        waits for that group only, so a caller that keeps two tickets in flight never lets the GPU idle while the
+        host logs, writes summaries or checks its stop conditions.  At most ``ring_depth`` tickets may be
+        outstanding (their results live in a ring of that many slots)."""
+        if self._ring_dev is None:
+            self._ring_cap, self._ring_depth = ring_cap, ring_depth
+            self._ring_dev = torch.zeros(ring_depth, 3, ring_cap, dtype=torch.float32, device=self.device)
+            self._ring_host = torch.zeros(ring_depth, 3, ring_cap, dtype=torch.float32).pin_memory()
+            self._ring_np = self._ring_host.numpy()
+            self._ring_events = [torch.cuda.Event() for _ in range(ring_depth)]
+            self._ring_next = 0
+        if not 1 <= nsteps <= self._ring_cap:
+            raise ValueError(f"nsteps must be in [1, {self._ring_cap}]")
+        slot = self._ring_next
+        self._ring_next = (slot + 1) % self._ring_depth
+        dev = self._ring_dev[slot]
+        lo, ao, so = dev[0], dev[1], dev[2].view(torch.int32)
+        idx = dataset.next_indices(self.batch, nsteps)
+        if self.fused is not None:
+            self.fused.run(dataset.images, dataset.labels, nsteps=nsteps, batch_idx=idx, outs=(lo, ao, so))
+            self.launch_count += 1
+        else:
+            for i in range(nsteps):
+                rows = idx[i * self.batch:(i + 1) * self.batch].long()
+                self.layer.run(dataset.images.index_select(0, rows), dataset.labels.index_select(0, rows))
+                lo[i:i + 1].copy_(self.layer.loss); ao[i:i + 1].copy_(self.layer.acc); so[i:i + 1].copy_(self.layer.step)
+                self.launch_count += self.layer.launches_per_call
+        self._ring_host[slot].copy_(dev, non_blocking=True)
+        ev = self._ring_events[slot]
+        ev.record(torch.cuda.current_stream(self.device))
+        return LaunchTicket(slot, nsteps, ev)
+
+    def collect(self, ticket: "LaunchTicket"):
+        """Wait for one launch group; returns numpy views (valid until ``ring_depth`` more launches) of
+        loss[n] float32, accuracy[n] float32, step[n] int32."""
+        ticket.event.synchronize()
+        r = self._ring_np[ticket.slot]
+        n = ticket.nsteps
+        return r[0, :n], r[1, :n], r[2, :n].view(np.int32)
 
     def run_indices(self, dataset: DeviceDataset, idx: torch.Tensor, nsteps: int) -> None:
         """Fused engine only: run exactly ``nsteps`` steps over precomputed batch indices."""
@@ -155,12 +206,20 @@ class GpuTrainer:
     # ---- evaluation ------------------------------------------------------------------
     def evaluate(self, X: torch.Tensor, labels: torch.Tensor) -> float:
         if isinstance(self.layer, TcStepper):
-            correct = total = 0
-            B = self.batch
-            for s in range(0, X.shape[0] - B + 1, B):           # whole batches (buffers are batch-sized)
-                self.layer.run(X[s:s + B].to(torch.bfloat16), labels[s:s + B], train=False)
-                correct += int(round(self.layer.acc.item() * B)); total += B
-            return correct / max(total, 1)
+            # buffers are batch-sized: whole batches, then the tail rows in a zero-padded batch whose padding rows
+            # are not counted (reference worker.py:152-153 evaluates ALL test images)
+            B, N = self.batch, X.shape[0]
+            correct = torch.zeros((), device=X.device, dtype=torch.int64)
+            for s in range(0, N, B):
+                m = min(B, N - s)
+                xb, yb = X[s:s + m].to(torch.bfloat16), labels[s:s + m]
+                if m < B:
+                    xp = torch.zeros(B, X.shape[1], device=X.device, dtype=torch.bfloat16); xp[:m] = xb
+                    yp = torch.zeros(B, device=X.device, dtype=labels.dtype); yp[:m] = yb
+                    xb, yb = xp, yp
+                self.layer.run(xb, yb, train=False)
+                correct += self.layer.rowcorrect[:m].sum()
+            return float(correct.item()) / max(N, 1)
         correct, total = self.layer.eval_counts(X, labels)
         return float(correct.item()) / float(total)
 

@@ -14,8 +14,10 @@ Observable behaviour kept from the reference:
   * a loss/accuracy summary per step, keyed by the observed global step, in ``<logdir>_<task>``
     (worker.py:96,139);
   * stop when ``step >= training_steps`` (a bound on the global step, worker.py:158-159).
-On the GPU path ``steps_per_launch > 1`` fuses several steps into one kernel launch; the cadence
-rules are then evaluated for every step of the launch after it returns.
+On the GPU path several steps are fused into one kernel launch (``--steps_per_launch``, adaptive by default);
+the cadence rules are evaluated for every step of a launch when it returns, launch sizes are planned so that
+evaluation and the end of training fall on launch boundaries (``plan_launch_steps``), two launches are kept in
+flight, and the per-step summaries are written by a helper thread.
 """
 from __future__ import annotations
 
@@ -52,6 +54,37 @@ def _parse_fault(text: str):
         else:
             raise ValueError(f"unknown fault {part!r}")
     return out
+
+
+AUTO_STEPS_PER_LAUNCH = 256     # --steps_per_launch 0: cap of the adaptive launch size
+PIPELINE_DEPTH = 2              # launch groups in flight: the GPU runs one while the host digests the previous one
+
+
+def plan_launch_steps(next_step_lb: int, training_steps: int, eval_every: int, num_workers: int, cap: int,
+                      nothing_in_flight: bool) -> int:
+    """How many steps the next kernel launch of a worker should fuse (0: enqueue nothing, wait for results).
+
+    ``next_step_lb`` is a lower bound on the global step the next step of this worker will observe (last observed
+    step + 1 + this worker's steps in flight; other workers can only add to it).  The reference checks its
+    cadence rules after every single step (worker.py:143-159); a multi-step launch checks them when it returns,
+    so its size is chosen such that, counting on this worker's own steps alone,
+      * the step that observes ``training_steps`` (the last one the reference would run) is the last of a launch,
+      * so is a step that observes a multiple of ``eval_every`` (the evaluation then sees the parameters right
+        after that step's update),
+    and with ``num_workers`` workers racing - the global step then advances about ``num_workers`` times faster than
+    this worker's own count - launches shrink geometrically towards those boundaries instead of running over them.
+    """
+    W = max(1, num_workers)
+    rem = training_steps - next_step_lb + 1            # own steps until one observes >= training_steps, inclusive
+    if rem <= 0:
+        # every step enqueued from now on would observe >= training_steps: only the reference's "one more step,
+        # then notice" remains, and only if no step in flight is going to notice first
+        return 1 if nothing_in_flight else 0
+    n = min(cap, -(-rem // W))
+    if eval_every > 0:
+        boundary = -(-next_step_lb // eval_every) * eval_every
+        n = min(n, -(-(boundary - next_step_lb + 1) // W))
+    return max(1, n)
 
 
 class Worker:
@@ -116,10 +149,17 @@ class Worker:
                 from ..parallel.sync import SyncGroup
                 W, me = self.server.num_workers, self.task_index
 
+                # Workers may be restarted against a ps that stayed up: key the handle exchange by generation
+                # (every W joins start a new one) so that nobody opens a dead process's IPC handles, and let the
+                # generation's chief clear the stop word its predecessors raised on their way out.
+                gen = (kv.add("sync/joined", 1) - 1) // W
+
                 def exchange(blob):
                     import pickle
-                    kv.set(f"sync/{me}", pickle.dumps(blob))
-                    return [pickle.loads(kv.get(f"sync/{r}")) for r in range(W)]
+                    if me == 0:
+                        store.clear_stop()
+                    kv.set(f"sync/{gen}/{me}", pickle.dumps(blob))
+                    return [pickle.loads(kv.get(f"sync/{gen}/{r}")) for r in range(W)]
                 # variable on ps shard k is reduced by worker (k mod W)
                 # a round may have to wait for workers that are still polling for the chief's initialisation
                 self.sync_group = SyncGroup(store, names, me, W, exchange=exchange,
@@ -128,7 +168,8 @@ class Worker:
             else:
                 kw["adam"] = dict(slots=[store.tensor(n + "/grad_slot") for n in names],
                                   m=[store.tensor(n + "/Adam") for n in names],
-                                  v=[store.tensor(n + "/Adam_1") for n in names], apply=self.is_chief)
+                                  v=[store.tensor(n + "/Adam_1") for n in names],
+                                  t=store.tensor("global/adam_t"), apply=self.is_chief)
             fused_ok = (f.sync and f.optimizer == "sgd" and f.engine in ("auto", "fused")
                         and FusedMlp2Stepper.supports(self.spec, f.batch_size))
             tr = GpuTrainer(self.spec, f.batch_size, f.learning_rate, [store.tensor(n) for n in names],
@@ -146,7 +187,7 @@ class Worker:
             self.trainer = tr
         else:
             self.trainer = GpuTrainer(self.spec, f.batch_size, f.learning_rate,
-                                      [store.tensor(n) for n in names], store.tensor(self.global_step.name), dev,
+                                      [store.param_handle(n) for n in names], store.tensor(self.global_step.name), dev,
                                       steps_per_launch=f.steps_per_launch, engine=f.engine,
                                       atomic=not f.unlocked_apply, remote=True, tf32=f.tf32)
         self.engine = None
@@ -209,8 +250,10 @@ class Worker:
             print(f"trace written to {path}", flush=True)
         return last_step
 
-    def _after_step(self, step: int, cost: float, acc: float, eval_fn, write_summary: bool = True) -> bool:
-        """Summary + cadence rules of reference worker.py:139-159. Returns True to stop."""
+    def _after_step(self, step: int, cost: float, acc: float, eval_fn, write_summary: bool = True,
+                    now: float = None) -> bool:
+        """Summary + cadence rules of reference worker.py:139-159. Returns True to stop.  ``now``: when the step
+        finished (steps of a multi-step launch are stamped by interpolation over the launch)."""
         f = self.flags
         if write_summary:
             with self.tracer.span("summary", "host"):
@@ -218,13 +261,16 @@ class Worker:
         if "kill_worker" in self.faults and self.faults["kill_worker"][0] == self.task_index \
                 and step >= self.faults["kill_worker"][1]:
             print(f"fault injection: worker {self.task_index} dies at step {step}", flush=True)
+            if getattr(self, "_summary_thread", None) is not None:
+                self._summary_thread.drain()
             self.summary_writer.flush()
             os._exit(17)
         if step % f.log_every == 0 and step != 0:
-            elapsed = time.time() - self._start_time
+            now = time.time() if now is None else now
+            elapsed = now - self._start_time
             print("step: {}\t| cost: {}\t| speed: {}step/sec".format(
                 step, cost, float((step - self._start_step) / max(elapsed, 1e-9))), flush=True)
-            self._start_time = time.time()
+            self._start_time = now
             self._start_step = step
         if step % f.eval_every == 0:
             with self.tracer.span("eval", "host", step=step):
@@ -257,38 +303,142 @@ class Worker:
         f, tr, tc = self.flags, self.trainer, self.tracer
         dev = tr.device
         seed = None if f.seed < 0 else f.seed + 1000 * self.task_index
-        train = DeviceDataset(dataset.train.images, dataset.train.label_ids, dev, seed=seed)
-        test_x = torch.as_tensor(dataset.test.images, dtype=torch.float32).to(dev)
+        train = DeviceDataset(dataset.train.images, dataset.train.label_ids, dev, seed=seed, dtype=tr.input_dtype)
+        test_x = torch.as_tensor(dataset.test.images, dtype=torch.float32).to(dev).to(tr.input_dtype)
         test_y = torch.as_tensor(dataset.test.label_ids, dtype=torch.int32).to(dev)
         eval_fn = lambda: tr.evaluate(test_x, test_y)
-        separate_exchange = self.sync_group is not None and not self._sync_in_kernel
-        n = 1 if separate_exchange else max(1, f.steps_per_launch)
+        if self.sync_group is not None and not self._sync_in_kernel:
+            return self._loop_cuda_separate_exchange(sv, train, eval_fn)
+        # One launch = up to `cap` steps of the persistent kernel (fused engine) or of the per-layer kernels; two
+        # launches are kept in flight so the GPU never waits for this loop.  --steps_per_launch N pins the cap
+        # (1 = the reference's one sess.run per step, at ~10x the cost per step); 0 adapts it.
+        cap = f.steps_per_launch if f.steps_per_launch > 0 else AUTO_STEPS_PER_LAUNCH
+        if tr.fused is None:
+            cap = min(cap, 16)          # per-layer engines launch every step's kernels from this thread anyway
+        W = 1 if self.sync_group is not None else self.server.num_workers   # sync: every worker observes every step
+        from collections import deque
+        pending = deque()
+        in_flight = 0
+        next_lb = self.client.read_step()       # restored runs continue from the checkpoint's step
+        writer = _SummaryThread(self.summary_writer)
+        self._summary_thread = writer
+        step, stop, hold = 0, False, False
+        t_prev = time.time()
+        try:
+            while not stop and not sv.should_stop():
+                while len(pending) < PIPELINE_DEPTH and not hold:
+                    lb = next_lb + in_flight
+                    n = plan_launch_steps(lb, f.training_steps, f.eval_every, W, cap, not pending)
+                    if n == 0:
+                        break
+                    # a launch that reaches an evaluation step is digested before anything else is queued, so the
+                    # evaluation reads the parameters right after that step, not a launch later
+                    hold = f.eval_every > 0 and lb + n - 1 >= -(-lb // f.eval_every) * f.eval_every
+                    with tc.span("launch", "step", steps=n), tc.device_span("step_kernel", steps=n):
+                        pending.append(tr.launch_async(train, n, ring_depth=PIPELINE_DEPTH + 1,
+                                                       ring_cap=max(cap, AUTO_STEPS_PER_LAUNCH)))
+                    in_flight += n
+                tk = pending.popleft()
+                with tc.span("results_d2h", "step"):
+                    loss, acc, steps = tr.collect(tk)
+                t_now = time.time()
+                in_flight -= tk.nsteps
+                if self.sync_group is not None and self.sync_group.aborted():
+                    print("sync: a peer left, stopping", flush=True)
+                    break
+                step, stop = self._digest_launch(loss, acc, steps, t_prev, t_now, eval_fn, writer)
+                next_lb = max(next_lb, step + 1)
+                t_prev = t_now
+                if not pending:
+                    hold = False
+        finally:
+            # launches already queued run to completion on the GPU (they cannot be recalled); their steps were
+            # applied and counted, but like a reference worker that was told to stop, nobody logs them
+            writer.close()
+        return step
+
+    def _digest_launch(self, loss, acc, steps, t0: float, t1: float, eval_fn, writer):
+        """Per-step summaries and cadence rules (reference worker.py:139-159) for all steps of one launch, touching
+        only the steps that print, evaluate or end training.  Returns (last step handled, stop)."""
+        f = self.flags
+        n = len(steps)
+        over = np.nonzero(steps >= f.training_steps)[0]
+        m = int(over[0]) + 1 if len(over) else n          # the step that ends training is the last one handled
+        with self.tracer.span("summary", "host", steps=m):
+            writer.submit(steps[:m], loss[:m], acc[:m])
+        hot = (steps[:m] % f.log_every == 0) | (steps[:m] % f.eval_every == 0)
+        hot[m - 1] = True
+        if "kill_worker" in self.faults and self.faults["kill_worker"][0] == self.task_index:
+            hot |= steps[:m] >= self.faults["kill_worker"][1]
+        stop = False
+        for i in np.nonzero(hot)[0]:
+            now = t0 + (t1 - t0) * (i + 1) / n
+            if self._after_step(int(steps[i]), float(loss[i]), float(acc[i]), eval_fn, write_summary=False, now=now):
+                stop = True
+                break
+        return int(steps[m - 1]), stop
+
+    def _loop_cuda_separate_exchange(self, sv: Supervisor, train, eval_fn) -> int:
+        """Synchronous mode of the per-layer engines: one step, then the stand-alone exchange kernel."""
+        f, tr, tc = self.flags, self.trainer, self.tracer
         step = 0
         while not sv.should_stop():
-            with tc.span("launch", "step", steps=n), tc.device_span("step_kernel", steps=n):
-                loss_d, acc_d, step_d = tr.train_device_steps(train, n)
-            if separate_exchange:
-                with tc.span("sync_exchange", "step"):
-                    self.sync_group.reduce_scatter_apply(f.learning_rate)
-                step_d = self.store.tensor(self.global_step.name)[:1] - 1      # the aggregated update just applied
-            if self.sync_group is not None and self.sync_group.aborted():
+            with tc.span("launch", "step", steps=1), tc.device_span("step_kernel", steps=1):
+                loss_d, acc_d, _ = tr.train_device_steps(train, 1)
+            with tc.span("sync_exchange", "step"):
+                self.sync_group.reduce_scatter_apply(f.learning_rate)
+            step_d = self.store.tensor(self.global_step.name)[:1] - 1      # the aggregated update just applied
+            if self.sync_group.aborted():
                 print("sync: a peer left, stopping", flush=True)
                 break
             with tc.span("results_d2h", "step"):
-                if tr.fused is not None and not separate_exchange:
-                    loss, acc, steps = tr.fused.k.results_host(len(loss_d))        # one copy, one sync per launch
-                else:
-                    loss, acc, steps = loss_d.tolist(), acc_d.tolist(), step_d.tolist()
-            # per-step summaries of the whole launch in one native call, up to the step that ends training
-            m = next((i + 1 for i, s in enumerate(steps) if s >= f.training_steps), len(steps))
-            with tc.span("summary", "host", steps=m):
-                self.summary_writer.add_training_summaries(steps[:m], loss[:m], acc[:m])
-            stop = False
-            for l, a, s in zip(loss[:m], acc[:m], steps[:m]):
-                step = s
-                if self._after_step(s, l, a, eval_fn, write_summary=False):
-                    stop = True
-                    break
-            if stop:
+                l, a, step = loss_d.item(), acc_d.item(), int(step_d.item())
+            if self._after_step(step, l, a, eval_fn):
                 break
         return step
+
+
+class _SummaryThread:
+    """Per-step summaries are written by a helper thread (the native writer releases the GIL): the training
+    thread only hands over copies of a launch's result arrays, in order."""
+
+    def __init__(self, file_writer):
+        import queue
+        import threading
+        self._w = file_writer
+        self._q = queue.Queue()
+        self._err = None
+        self._t = threading.Thread(target=self._run, name="summary-writer", daemon=True)
+        self._t.start()
+
+    def _run(self) -> None:
+        while True:
+            item = self._q.get()
+            if item is None:
+                return
+            try:
+                if callable(item):
+                    item()
+                else:
+                    self._w.add_training_arrays(*item)
+            except BaseException as e:      # surfaced by the next submit/close on the training thread
+                self._err = e
+
+    def submit(self, steps, loss, acc) -> None:
+        if self._err is not None:
+            raise self._err
+        self._q.put((np.ascontiguousarray(steps).copy(), np.ascontiguousarray(loss).copy(),
+                     np.ascontiguousarray(acc).copy()))
+
+    def drain(self) -> None:
+        import threading
+        done = threading.Event()
+        self._q.put(done.set)
+        done.wait(30)
+
+    def close(self) -> None:
+        if self._t.is_alive():
+            self._q.put(None)
+            self._t.join(30)
+        if self._err is not None:
+            raise self._err

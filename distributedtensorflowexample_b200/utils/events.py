@@ -73,6 +73,12 @@ class FileWriter:
         self._f.write_scalars_batch(time.time() if wall_time is None else wall_time, list(global_steps),
                                     [TAG_LOSS, TAG_ACCURACY], list(zip(losses, accuracies)))
 
+    def add_training_arrays(self, global_steps, losses, accuracies, wall_time: Optional[float] = None) -> None:
+        """``add_training_summaries`` for numpy arrays (int32 steps, float32 loss/accuracy), written by the native
+        library straight from the arrays."""
+        self._f.write_pairs_i32(time.time() if wall_time is None else wall_time, global_steps, losses, accuracies,
+                                TAG_LOSS, TAG_ACCURACY)
+
     def add_session_log(self, status: int, global_step: int = 0, checkpoint_path: str = "", msg: str = "") -> None:
         self._f.write_session_log(time.time(), int(global_step), status, checkpoint_path, msg)
 

@@ -47,6 +47,7 @@ def _lib():
         L.dtfe_events_write_scalars.argtypes = [c_void_p, c_double, c_int64, POINTER(c_char_p), POINTER(c_float), c_int]
         L.dtfe_events_write_scalars_batch.argtypes = [c_void_p, c_double, POINTER(c_int64), POINTER(c_char_p),
                                                       POINTER(c_float), c_int, c_int]
+        L.dtfe_events_write_pairs_i32.argtypes = [c_void_p, c_double, c_void_p, c_void_p, c_void_p, c_int, c_char_p, c_char_p]
         L.dtfe_events_write_session_log.argtypes = [c_void_p, c_double, c_int64, c_int, c_char_p, c_char_p]
         L.dtfe_events_write_graph.argtypes = [c_void_p, c_double, c_void_p, c_size_t]
         L.dtfe_events_flush.argtypes = [c_void_p]
@@ -197,6 +198,17 @@ class EventsFile:
         S = (c_int64 * n)(*[int(x) for x in steps])
         V = (c_float * (n * nt))(*[float(v) for row in rows for v in row])
         check_host(self._L.dtfe_events_write_scalars_batch(self._h, wall_time, S, T, V, n, nt), "events scalars batch")
+
+    def write_pairs_i32(self, wall_time: float, steps: np.ndarray, v0: np.ndarray, v1: np.ndarray, tag0: str, tag1: str) -> None:
+        """One event per step with two scalars, from contiguous int32 / float32 / float32 arrays (no per-value
+        marshalling; the call releases the GIL)."""
+        n = int(steps.shape[0])
+        if n == 0:
+            return
+        assert steps.dtype == np.int32 and v0.dtype == np.float32 and v1.dtype == np.float32
+        assert steps.flags.c_contiguous and v0.flags.c_contiguous and v1.flags.c_contiguous and len(v0) == n == len(v1)
+        check_host(self._L.dtfe_events_write_pairs_i32(self._h, wall_time, steps.ctypes.data, v0.ctypes.data,
+                                                       v1.ctypes.data, n, tag0.encode(), tag1.encode()), "events pairs")
 
     def write_session_log(self, wall_time: float, step: int, status: int, checkpoint_path: str = "", msg: str = "") -> None:
         check_host(self._L.dtfe_events_write_session_log(self._h, wall_time, int(step), status,

@@ -129,7 +129,12 @@ def test_launcher_task_commands_modulo_mapping():
     from distributedtensorflowexample_b200.launch import launcher
     tasks = launcher.task_commands(16, 4, ["0", "1", "2", "3"])
     assert [t["name"] for t in tasks][:3] == ["ps", "worker0", "worker1"] and len(tasks) == 17
-    assert [t["env"]["CUDA_VISIBLE_DEVICES"] for t in tasks[1:]] == [str(i % 4) for i in range(16)]
+    # the task's own GPU is GPU_ID[i % num_gpus] and comes first (= its cuda:0, like the reference's gpu:0); the
+    # cluster's other GPUs follow so that shards living there can be mapped (CUDA IPC needs the device visible)
+    vis = [t["env"]["CUDA_VISIBLE_DEVICES"].split(",") for t in tasks[1:]]
+    assert [v[0] for v in vis] == [str(i % 4) for i in range(16)]
+    assert all(sorted(v) == ["0", "1", "2", "3"] for v in vis)
+    assert launcher.task_commands(2, 1, ["5"])[1]["env"]["CUDA_VISIBLE_DEVICES"] == "5"
     w5 = tasks[6]["argv"]
     assert w5[w5.index("--job_name") + 1] == "worker" and w5[w5.index("--task_index") + 1] == "5"
     assert "--task_index=0" in tasks[0]["argv"]
@@ -148,7 +153,7 @@ def test_shell_launchers_keep_reference_knobs():
     out = subprocess.run(["bash", os.path.join(root, "run_multi_gpu.sh"), "--mode", "print"], capture_output=True,
                          text=True, env={**os.environ, "MODE": "print"}, timeout=60).stdout
     assert out.count("new-window") == 16 and "--num_workers 16 --num_gpus 4" in out
-    assert "CUDA_VISIBLE_DEVICES=3" in out and "--task_index 15" in out
+    assert "CUDA_VISIBLE_DEVICES=3,0,1,2" in out and "--task_index 15" in out
     out = subprocess.run(["bash", os.path.join(root, "run_single_gpu.sh")], capture_output=True, text=True,
                          env={**os.environ, "MODE": "print"}, timeout=60).stdout
     assert out.count("new-window") == 2 and "--num_workers 2 --num_gpus 1" in out

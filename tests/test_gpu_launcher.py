@@ -56,6 +56,28 @@ def test_adam_and_unlocked_apply_modes(tmp_path):
     assert codes["worker0"] == 0 and codes["worker1"] == 0, (codes, cl.lines)
 
 
+def test_bfloat16_worker_trains_on_the_tensor_core_engine(tmp_path):
+    """--dtype bfloat16 selects the tcgen05 engine: data set, test set and parameter handles must all follow."""
+    cl, codes, logdir = _run(tmp_path, ["--training_steps", "300", "--dtype", "bfloat16", "--hidden", "104",
+                                        "--learning_rate", "0.05", "--eval_every", "200"], num_workers=1)
+    assert codes["worker0"] == 0, (codes, cl.lines)
+    assert sum(l.startswith("test accuracy: ") for l in cl.lines["worker0"]) >= 2        # steps 0 and 200
+
+
+def test_default_flags_reach_training_steps_exactly_with_one_worker(tmp_path):
+    """Adaptive launch sizes: a lone worker runs exactly training_steps + 1 steps (the reference's count) and the
+    evaluation steps end their launches."""
+    cl, codes, logdir = _run(tmp_path, ["--training_steps", "2500", "--learning_rate", "0.05", "--eval_every", "1000"],
+                             num_workers=1)
+    assert codes["worker0"] == 0, (codes, cl.lines)
+    w0 = cl.lines["worker0"]
+    assert sum(l.startswith("test accuracy: ") for l in w0) == 3                          # steps 0, 1000, 2000
+    pat = re.compile(r"^step: (\d+)\t")
+    assert [int(m.group(1)) for l in w0 if (m := pat.match(l))] == list(range(100, 2501, 100))
+    from distributedtensorflowexample_b200.utils.events_reader import scalars
+    assert [s for s, _, _, _ in scalars(logdir + "_0", "local/loss")] == list(range(2501))
+
+
 @pytest.mark.multigpu
 def test_sync_mode_two_gpus_two_ps(tmp_path):
     cl, codes, logdir = _run(tmp_path, ["--training_steps", "400", "--sync", "--learning_rate", "0.05"],

@@ -241,6 +241,42 @@ def test_trainer_device_and_host_paths_agree():
     assert outs[0][-1].item() == 10
 
 
+@pytest.mark.parametrize("engine", ["fused", "layerwise"])
+def test_pipelined_launches_equal_the_blocking_path(engine):
+    """launch_async/collect (what Worker.learn drives): two launch groups in flight give the same parameters and the
+    same per-step metrics as the blocking calls, for every step of every group."""
+    from distributedtensorflowexample_b200.train.gpu_step import DeviceDataset
+    from distributedtensorflowexample_b200.train.trainer import GpuTrainer
+    spec = reference_mlp_spec()
+    x, y = _data(3000)
+    res = []
+    for mode in ("blocking", "pipelined"):
+        model, store, names = _store(spec, seed=3)
+        tr = GpuTrainer(spec, 100, 0.02, [store.tensor(n) for n in names], store.tensor("global/global_step"),
+                        "cuda:0", steps_per_launch=1 if mode == "blocking" else 8, engine=engine)
+        ds = DeviceDataset(x, y, "cuda:0", seed=9)
+        losses, steps = [], []
+        if mode == "blocking":
+            for _ in range(19):
+                l, a, s = tr.train_device_steps(ds, 1)
+                losses.append(float(l[0].item())); steps.append(int(s[0].item()))
+        else:
+            sizes, tickets = [8, 8, 3], []
+            for n in sizes:
+                tickets.append(tr.launch_async(ds, n, ring_depth=3, ring_cap=8))
+            for tk in tickets:
+                l, a, s = tr.collect(tk)
+                assert len(l) == tk.nsteps
+                losses += l.tolist(); steps += s.tolist()
+        torch.cuda.synchronize()
+        res.append((losses, steps, [store.read(n) for n in names]))
+        store.close()
+    assert res[0][1] == res[1][1] == list(range(19))
+    np.testing.assert_allclose(res[0][0], res[1][0], rtol=1e-5, atol=1e-6)
+    for a, b in zip(res[0][2], res[1][2]):
+        np.testing.assert_allclose(a, b, rtol=1e-5, atol=1e-6)
+
+
 def test_layerwise_adam_matches_oracle():
     """Optional Adam (north star): workers push raw gradients into owner-side slots, the owner applies."""
     from distributedtensorflowexample_b200.parallel.ps import PeerParamStore

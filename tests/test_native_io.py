@@ -173,6 +173,24 @@ def test_events_batch_is_bytewise_the_per_step_writes(tmp_path):
     assert tail(da) == tail(db) and len(tail(da)) > 100
 
 
+def test_events_array_writer_is_bytewise_the_per_step_writes(tmp_path):
+    """The worker loop hands the summary thread numpy arrays (int32 steps, fp32 loss/accuracy of one launch)."""
+    from distributedtensorflowexample_b200.utils.events import FileWriter, training_summary
+    a = FileWriter(str(tmp_path / "a")); b = FileWriter(str(tmp_path / "b"))
+    steps = np.array([5, 6, 9, 70000], np.int32)
+    losses = np.array([1.5, 0.25, 3.0, 1e-3], np.float32); accs = np.array([0.1, 0.5, 1.0, 0.0], np.float32)
+    for s, l, ac in zip(steps, losses, accs):
+        a.add_summary(training_summary(float(l), float(ac)), int(s), wall_time=123.5)
+    b.add_training_arrays(steps, losses, accs, wall_time=123.5)
+    a.close(); b.close()
+    import struct
+    def tail(d):
+        n = struct.unpack("<Q", d[:8])[0]
+        return d[8 + 4 + n + 4:]
+    da, db = open(a.path, "rb").read(), open(b.path, "rb").read()
+    assert tail(da) == tail(db) and len(tail(da)) > 100
+
+
 # ---- property tests (hypothesis): arbitrary contents must round-trip through the native formats -------------
 from hypothesis import HealthCheck, given, settings, strategies as st
 
