@@ -123,6 +123,12 @@ __device__ __forceinline__ void emit_small(float* shard, float* gbuf, float* del
   emit(shard, gbuf, i, g, nlr, atomic);
 }
 
+__device__ __forceinline__ void st_relaxed_sys_u32(unsigned* p, unsigned v) {
+  asm volatile("st.relaxed.sys.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
+constexpr int kCtaFlagPitch = 160;      // per-CTA arrival words per rank (dtfe_sync_exchange.cta_flags)
+constexpr unsigned kSxAbort = 0xffffffffu;
+
 // Wait for a peer's flag; gives up (returns false) when the stop word is raised or the timeout expires, so a
 // rank that left can never hang this GPU.
 __device__ __forceinline__ bool sx_wait(const unsigned* flag, unsigned epoch, const dtfe_sync_exchange& sx,
@@ -243,12 +249,18 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
     n = C - (e - dOffB2);
     return a.b2 + (e - dOffB2);
   };
-  if (ahead) {
+  // Synchronous all-reduce mode: the parameters this kernel is given are this rank's own copies; the W1 slice
+  // stays in shared memory for the whole launch and is updated in place in phase D.
+  const bool sx1 = a.has_sx && a.sx.mode == 1;
+  if (ahead || sx1) {
     dtfe::cta_copy_async(Ws, a.W1 + (long)k0 * H, nW1, tid, kThreads);
     dtfe::cp_async_commit();
   } else {
     fetch_w1();
   }
+  // offsets (floats) of the four gradients inside every rank's exchange buffer
+  const long sxOffW1 = sx1 ? (long)(a.gW1 - a.sx.grads[a.sx.rank]) : 0, sxOffB1 = sx1 ? (long)(a.gb1 - a.sx.grads[a.sx.rank]) : 0;
+  const long sxOffW2 = sx1 ? (long)(a.gW2 - a.sx.grads[a.sx.rank]) : 0, sxOffB2 = sx1 ? (long)(a.gb2 - a.sx.grads[a.sx.rank]) : 0;
   int pending_step = 0;                                 // book CTA / thread 0: global step observed for the previous step
   const unsigned sx_epoch0 = a.has_sx ? *reinterpret_cast<volatile unsigned*>(a.sx.epoch) : 0u;
   const unsigned long long sx_t0 = gtime();
@@ -265,14 +277,21 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
     // ------------------------------ phase A ------------------------------------
     DBG_STAMP(0);
     int ylab = 0;
+    // all-reduce mode alternates between two copies of the gradient buffer (see phase D)
+    const long goff = sx1 ? (long)((sx_epoch0 + (unsigned)s + 1u) & 1u) * (long)a.sx.grad_stride : 0;
+    float* const gW1 = a.gW1 ? a.gW1 + goff : nullptr;
+    float* const gb1 = a.gb1 ? a.gb1 + goff : nullptr;
+    float* const gW2 = a.gW2 ? a.gW2 + goff : nullptr;
+    float* const gb2 = a.gb2 ? a.gb2 + goff : nullptr;
     if (slice) {
 #pragma unroll
     for (int i = 0; i < kXPer; ++i) {
       int e = tid + i * kThreads;
       if (e < B * KS) Xs[e] = xnext[i];
     }
-    if (ahead) {
-      // W1 slice: already in Ws (fetched during the previous step's phase C, own update added there)
+    if (ahead || sx1) {
+      // W1 slice: already in Ws (fetched during the previous step's phase C, own update added there; all-reduce
+      // mode: resident for the whole launch)
       dtfe::cp_async_wait<0>();              // only the first step of a launch still has copies in flight here
     } else {
       // W1 slice: every thread re-read, right after its own pushes in the previous step's phase C (same
@@ -320,6 +339,12 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
     DBG_STAMP(1);
     grid_barrier(a.sync, bar_target, NC);
     DBG_STAMP(2);
+    if (sx1) {
+      // a CTA that gave up on its peers in the previous step said so before arriving here: stop, all CTAs alike
+      unsigned v;
+      asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(a.sync + 2) : "memory");
+      if (v == kSxAbort) break;
+    }
 
     // ------------------------------ phase B ------------------------------------
     // Next step's X slice and the rows after that: issued now, consumed a whole step later.
@@ -652,7 +677,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
               if (b < B) v = fmaf(hc[i], dZs[b * C + c], v);
             }
             v = dtfe::warp_sum(v);
-            if (lane == 0) emit_small(a.W2, a.gW2, delta, (long)tt * C + c, v, nlr, a.atomic);
+            if (lane == 0) emit_small(a.W2, gW2, delta, (long)tt * C + c, v, nlr, a.atomic);
           }
           if (warp == 5) {                        // db1[tt] = sum_b dA[b][tt]
             float v = 0.f;
@@ -660,7 +685,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
             else if (rnd == 1) v = (dacol1[0] + dacol1[1]) + (dacol1[2] + dacol1[3]);
             else for (int b = lane; b < B; b += 32) v += __ldcg(a.dA + (long)b * H + tt);
             v = dtfe::warp_sum(v);
-            if (lane == 0) emit_small(a.b1, a.gb1, delta ? delta + dOffB1 : nullptr, tt, v, nlr, a.atomic);
+            if (lane == 0) emit_small(a.b1, gb1, delta ? delta + dOffB1 : nullptr, tt, v, nlr, a.atomic);
           }
         }
         if (g == book) {                          // db2[c] = sum_b dZ[b][c], spread over the warps
@@ -668,7 +693,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
             float v = 0.f;
             for (int b = lane; b < B; b += 32) v += dZs[b * C + c];
             v = dtfe::warp_sum(v);
-            if (lane == 0) emit_small(a.b2, a.gb2, delta ? delta + dOffB2 : nullptr, c, v, nlr, a.atomic);
+            if (lane == 0) emit_small(a.b2, gb2, delta ? delta + dOffB2 : nullptr, c, v, nlr, a.atomic);
           }
         }
       }
@@ -687,8 +712,8 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
               if (wv0) g0 += pq[w * (KS * kMaxH) + wj0];
               if (kParts < 4 && wv1) g1 += pq[w * (KS * kMaxH) + wj1];
             }
-            if (wv0) emit(a.W1, a.gW1, (long)k * H + wj0, g0, nlr, a.atomic);
-            if (kParts < 4 && wv1) emit(a.W1, a.gW1, (long)k * H + wj1, g1, nlr, a.atomic);
+            if (wv0) emit(a.W1, gW1, (long)k * H + wj0, g0, nlr, a.atomic);
+            if (kParts < 4 && wv1) emit(a.W1, gW1, (long)k * H + wj1, g1, nlr, a.atomic);
             if (ahead) {        // fetched value + own update = what the shard holds (bitwise, absent other writers)
               float* w0 = Ws + (wgrp * 4 + q) * HP + wj0;
               if (wv0) *w0 = __fadd_rn(*w0, __fmul_rn(nlr, g0));
@@ -706,7 +731,83 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
       // of this step's pushes before the global_step increment that counts them.
       __syncthreads();                            // dAs / Xs are rewritten by the next step
       DBG_STAMP(7);
-      if (a.has_sx) {
+      if (sx1) {
+        // ------------------------------ phase D, all-reduce form -----------------------------------
+        // This CTA's gradients are in this rank's exchange buffer (the __syncthreads above ordered every
+        // thread's stores before thread 0's fence).  Tell the same CTA of every other rank, wait for theirs,
+        // sum exactly the elements this CTA produced over all ranks in rank order, apply to the home copy.
+        const unsigned epoch = sx_epoch0 + (unsigned)s + 1u;
+        const int W = a.sx.world, me = a.sx.rank;
+        if (tid == 0 && W > 1) {
+          __threadfence_system();
+          for (int p = 0; p < W; ++p)
+            if (p != me) st_relaxed_sys_u32(a.sx.cta_flags[p] + me * kCtaFlagPitch + g, epoch);
+        }
+        bool ok = true;
+        if (tid < W && tid != me) ok = sx_wait(a.sx.cta_flags[me] + tid * kCtaFlagPitch + g, epoch, a.sx, sx_t0);
+        ok = __syncthreads_and(ok) != 0;
+        DBG_STAMP(6);
+        if (ok) {
+          const float alpha = a.sx.alpha;
+          if (slice) {
+            const long base = sxOffW1 + goff + (long)k0 * H;
+            if ((H & 3) == 0 && (base & 3) == 0) {
+              for (int f = tid; 4 * f < nW1; f += kThreads) {
+                float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+                for (int q0 = 0; q0 < W; q0 += 8) {
+                  float4 v[8];
+#pragma unroll
+                  for (int u = 0; u < 8; ++u)
+                    if (q0 + u < W) v[u] = dtfe::ld_relaxed_sys_v4(a.sx.grads[q0 + u] + base + 4 * f);
+#pragma unroll
+                  for (int u = 0; u < 8; ++u)
+                    if (q0 + u < W) { acc.x += v[u].x; acc.y += v[u].y; acc.z += v[u].z; acc.w += v[u].w; }
+                }
+                float4 w = *reinterpret_cast<float4*>(Ws + 4 * f);
+                w.x = fmaf(alpha, acc.x, w.x); w.y = fmaf(alpha, acc.y, w.y);
+                w.z = fmaf(alpha, acc.z, w.z); w.w = fmaf(alpha, acc.w, w.w);
+                *reinterpret_cast<float4*>(Ws + 4 * f) = w;
+                __stcg(reinterpret_cast<float4*>(a.W1 + (long)k0 * H) + f, w);
+              }
+            } else {
+              for (int e = tid; e < nW1; e += kThreads) {
+                float acc = 0.f;
+                for (int q = 0; q < W; ++q) acc += dtfe::ld_relaxed_sys(a.sx.grads[q] + base + e);
+                const float w = fmaf(alpha, acc, Ws[e]);
+                Ws[e] = w;
+                __stcg(a.W1 + (long)k0 * H + e, w);
+              }
+            }
+          }
+          if (does_small) {
+            const int nrows = t0 < H ? (H - t0 + tstride - 1) / tstride : 0, per = C + 1;
+            for (int i = tid; i < nrows * per; i += kThreads) {
+              const int tt = t0 + (i / per) * tstride, c = i % per;
+              const long off = goff + (c < C ? sxOffW2 + (long)tt * C + c : sxOffB1 + tt);
+              float acc = 0.f;
+              for (int q = 0; q < W; ++q) acc += dtfe::ld_relaxed_sys(a.sx.grads[q] + off);
+              float* home = c < C ? a.W2 + (long)tt * C + c : a.b1 + tt;
+              __stcg(home, fmaf(alpha, acc, __ldcg(home)));
+            }
+            if (g == book)
+              for (int c = tid; c < C; c += kThreads) {
+                float acc = 0.f;
+                for (int q = 0; q < W; ++q) acc += dtfe::ld_relaxed_sys(a.sx.grads[q] + goff + sxOffB2 + c);
+                __stcg(a.b2 + c, fmaf(alpha, acc, __ldcg(a.b2 + c)));
+              }
+          }
+          if (g == book && tid == 0) {        // every rank counts the aggregated update in its own copy
+            const int old = *reinterpret_cast<volatile int*>(a.global_step);
+            *reinterpret_cast<volatile int*>(a.global_step) = old + 1;
+            a.step_out[s] = old;
+          }
+          ++steps_done;
+        } else if (tid == 0) {
+          a.sx.status[0] = 1u;
+          asm volatile("st.release.gpu.global.u32 [%0], %1;" :: "l"(a.sync + 2), "r"(kSxAbort) : "memory");
+        }
+        __syncthreads();                          // the updated W1 slice is in Ws for every thread
+      } else if (a.has_sx) {
         // ------------------------------ phase D (synchronous mode) -------------------------------
         // D1: every CTA's gradients are in this rank's exchange buffer
         grid_barrier(a.sync, bar_target, NC);
@@ -795,6 +896,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
     unsigned prev = atomicAdd(a.sync + 1, 1u);
     if (prev == NC - 1) {
       a.sync[0] = 0; a.sync[1] = 0;
+      if (a.has_sx && a.sx.mode == 1) a.sync[2] = 0;
       if (a.has_sx) {
         *a.sx.epoch = sx_epoch0 + (unsigned)steps_done;
       } else if (a.train && a.nsteps > 0) {
@@ -869,6 +971,15 @@ static int mlp2_fill(const Mlp2Launch& L, Mlp2Args& a) {
     DTFE_REQUIRE(a.gW1 != nullptr, "mlp2_step: sync_exchange needs the four gradient buffers (they are what is exchanged)");
     DTFE_REQUIRE(a.sx.world >= 1 && a.sx.world <= 16 && a.sx.nseg >= 0 && a.sx.nseg <= 8 && a.sx.epoch && a.sx.status,
                  "mlp2_step: malformed sync_exchange");
+    DTFE_REQUIRE(a.sx.mode == 0 || a.sx.mode == 1, "mlp2_step: sync_exchange.mode must be 0 or 1");
+    if (a.sx.mode == 1) {
+      DTFE_REQUIRE(a.sx.rank >= 0 && a.sx.rank < a.sx.world && a.sx.grad_stride > 0,
+                   "mlp2_step: all-reduce exchange needs rank < world and grad_stride");
+      for (int r = 0; r < a.sx.world; ++r)
+        DTFE_REQUIRE(a.sx.grads[r] && a.sx.cta_flags[r], "mlp2_step: all-reduce exchange: rank %d's buffers are missing", r);
+      DTFE_REQUIRE(((uintptr_t)L.W1 % 16) == 0, "mlp2_step: all-reduce exchange needs a 16-byte aligned W1 copy");
+      DTFE_REQUIRE(a.train, "mlp2_step: sync_exchange is for training launches");
+    }
   }
   DTFE_REQUIRE((a.gW1 != nullptr) == (a.gb1 != nullptr) && (a.gW1 != nullptr) == (a.gW2 != nullptr) &&
                (a.gW1 != nullptr) == (a.gb2 != nullptr), "mlp2_step: pass all four gradient buffers or none");

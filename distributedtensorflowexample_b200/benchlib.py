@@ -298,48 +298,93 @@ def run_mnist(args, rank: int, world: int, dev, ClockSampler) -> int:
 
 
 def _run_mnist_sync(args, rank, world, dev, ClockSampler, spec, model, store, names, ds, x, y, B, lr, K, W) -> int:
-    """Synchronous SGD: the fused step kernel writes its gradients to this rank's peer-visible exchange buffer
-    and, as its last phase, runs barrier + reduce-scatter + apply + barrier over peer memory - every step,
-    any number of steps per launch (parallel/sync.py, mlp2_step.cu phase D)."""
+    """Synchronous SGD inside the fused step kernel, any number of steps per launch (parallel/sync.py, mlp2_step.cu
+    phase D).  ``--sync-mode allreduce`` (default): per-CTA flag exchange, every rank sums all ranks' gradients and
+    applies them to its own copy of the parameters; ``reduce_scatter``: round 1's form (grid barrier, owners reduce
+    and apply, second flag round, pull)."""
+    from .ops import cuda_ops as ops
     from .parallel.sync import SyncGroup
     from .train.gpu_step import FusedMlp2Stepper
-    sg = SyncGroup(store, names, rank, world)
+    mode = getattr(args, "sync_mode", "allreduce")
+    sg = SyncGroup(store, names, rank, world, mode=mode)
     shapes = {n: tuple(store.tensor(n).shape) for n in names}
     spl = args.steps_per_launch or min(K, 500)
-    st = FusedMlp2Stepper(spec, B, [store.tensor(n) for n in names], store.tensor("global/global_step"), lr, dev,
-                          max_steps_per_launch=spl, remote=not store.all_local(), grad_buffers=sg.grad_views(shapes))
-    idx = ds.next_indices(B, K + W)
+    R = max(1, getattr(args, "repeats", 25))
+    if mode == "allreduce":
+        sg.refresh_replicas()
+        _barrier(world)
+        params, gstep, remote = sg.home_params(), sg.home("global/global_step"), False
+    else:
+        params, gstep, remote = [store.tensor(n) for n in names], store.tensor("global/global_step"), not store.all_local()
+    st = FusedMlp2Stepper(spec, B, params, gstep, lr, dev, max_steps_per_launch=spl, remote=remote,
+                          grad_buffers=sg.grad_views(shapes))
     st.sync_exchange = sg.exchange_struct(lr)       # phase D of the step kernel: exchange + apply, every step
 
-    def run_steps(first, n):
+    def run_steps(n):
         done = 0
         while done < n:
             m = min(spl, n - done)
-            st.run(ds.images, ds.labels, nsteps=m, batch_idx=idx[(first + done) * B:(first + done + m) * B])
+            st.run(ds.images, ds.labels, nsteps=m, batch_idx=ds.next_indices(B, m))
             done += m
         return (n + spl - 1) // spl
 
-    run_steps(0, W)
+    run_steps(W)
     _barrier(world)
+    flush = torch.empty(64 << 20, dtype=torch.int32, device=dev)
     clocks = ClockSampler(dev.index or 0)
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     clocks.start()
-    e0.record()
-    launches = run_steps(W, K)
-    e1.record()
-    torch.cuda.synchronize()
+    samples, launches = [], 0
+    for r in range(R):
+        _barrier(world)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ops.l2_flush(flush)
+        e0.record()
+        launches = run_steps(K)
+        e1.record()
+        torch.cuda.synchronize()
+        samples.append(e0.elapsed_time(e1))
     clk = clocks.stop()
     assert sg.aborted() == 0, "a rank abandoned the exchange"
-    ms = _max_over_ranks(e0.elapsed_time(e1), world, dev)
+    samples = sorted(_max_over_ranks_vec(samples, world, dev))
+    ms = samples[len(samples) // 2]
     _barrier(world)
-    out = {"metric": METRIC, "value": world * B * K / (ms * 1e-3), "unit": "examples/sec", "n_gpus": world,
+    value = world * B * K / (ms * 1e-3)
+    # replicas must still agree bit for bit (all-reduce mode): compare a checksum of this rank's copy with rank 0's
+    agree = None
+    if mode == "allreduce" and world > 1:
+        chk = torch.stack([p.double().sum() for p in params] + [gstep.double().sum()])
+        ref = chk.clone()
+        dist.broadcast(ref, src=0)
+        agree = bool(torch.equal(chk, ref))
+    baseline = None
+    if not getattr(args, "no_baseline", False):
+        import sys as _sys, os as _os
+        root = _os.path.dirname(_os.path.dirname(_os.path.abspath(__file__)))
+        if root not in _sys.path:
+            _sys.path.insert(0, root)
+        from baseline import nccl_ps
+        try:
+            m = nccl_ps.measure("mnist", B, K, W, rank, world, dev, graph=True, flat=True, repeats=min(R, 9), e2e=False)
+            baseline = {k: m[k] for k in ("value", "ms_per_step", "ms_per_step_min", "ms_per_step_max", "samples")}
+        except Exception as e:
+            baseline = {"error": f"{type(e).__name__}: {e}"[:300]}
+        _barrier(world)
+    out = {"metric": METRIC, "value": value, "unit": "examples/sec", "n_gpus": world,
            "steps": K, "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak",
            "vs_baseline": None, "dtype": "fp32", "data": "synthetic", "impl": "ours",
+           "samples": {"n": len(samples), "ms_per_step_min": samples[0] / K, "ms_per_step_median": ms / K,
+                       "ms_per_step_max": samples[-1] / K},
            "config": {"model": "MNIST MLP 784-100-10", "global_batch": B * world, "batch_per_worker": B,
-                      "parallelism": f"sync-ps dp{world}: reduce-scatter fused with apply over peer memory",
-                      "engine": "fused step kernel with the exchange (barrier, reduce-scatter, apply, barrier) as its phase D", "steps_per_launch": spl},
-           "gpu_launches": launches, "clocks": clk,
-           "global_step_after": int(store.tensor("global/global_step").item())}
+                      "parallelism": f"sync-ps dp{world}: {mode} fused with the apply over peer memory, inside the step kernel",
+                      "engine": "fused step kernel, exchange as its phase D", "steps_per_launch": spl, "sync_mode": mode,
+                      "l2": "L2 flushed (256 MB fill) before every timed sample; batch sampling inside the timed region"},
+           "gpu_launches": launches, "clocks": clk, "replicas_bit_identical": agree,
+           "global_step_after": int(gstep.item())}
+    if baseline is not None:
+        out["baseline"] = {"impl": "nccl-ps: torch ops + one NCCL all-reduce of the flat gradient per step (the same "
+                                   "synchronous algorithm), whole step CUDA-graph-captured", **baseline}
+        if baseline.get("value"):
+            out["vs_baseline"] = value / baseline["value"]
     if rank == 0:
         print(json.dumps(out), flush=True)
     sg.close(); store.close()

@@ -308,6 +308,7 @@ class SyncExchange(ctypes.Structure):
         ("epoch", _P), ("status", _P), ("abort_flag", _P),
         ("timeout_ns", ctypes.c_ulonglong),
         ("global_step", _P),
+        ("mode", c_int), ("grad_stride", c_size_t), ("cta_flags", _P * 16),
     ]
 
 

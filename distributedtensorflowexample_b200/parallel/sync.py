@@ -8,6 +8,12 @@ memory -> each owner reduces the slices of the variables it owns out of all rank
 loads over NVLink) and applies ``-lr/W * sum`` in place in its shard -> barrier.  That is a
 reduce-scatter fused with the update; there is no all-gather because the next forward reads the
 parameters from the owners' shards anyway (the fused pull).  One rank per GPU.
+
+``mode="allreduce"`` (fused MNIST step kernel only) is the low-latency form: every rank keeps its own copy of
+the parameters ("home": the shard itself where the rank owns the variable, a private replica elsewhere), each
+CTA of the step kernel exchanges per-CTA flags with the same CTA of the other ranks, sums all ranks' gradients
+for the elements it produced and applies them to its home copy - no grid barrier, no second flag round, no
+pull.  Replicas stay bit-identical because every rank sums in rank order.
 """
 from __future__ import annotations
 
@@ -22,9 +28,13 @@ from .ps import PeerParamStore
 
 class SyncGroup:
     def __init__(self, store: PeerParamStore, trainable_names: Sequence[str], rank: int, world: int,
-                 owner_of_shard=lambda k, world: k % world, exchange=None, timeout_s: float = 20.0):
+                 owner_of_shard=lambda k, world: k % world, exchange=None, timeout_s: float = 20.0,
+                 mode: str = "reduce_scatter"):
         """``exchange(blob) -> [blob of rank 0, ..., blob of rank W-1]``; default: torch.distributed
         all_gather_object (SPMD).  Launcher-mode workers pass a TCPStore-based exchange."""
+        if mode not in ("reduce_scatter", "allreduce"):
+            raise ValueError(mode)
+        self.mode = mode
         self.store, self.rank, self.world = store, rank, world
         self.device = store.device
         self.names = list(trainable_names)
@@ -37,14 +47,19 @@ class SyncGroup:
             n = (n + numel + 3) // 4 * 4
         self.total = n
         max_ranks = ops.lib().dtfe_sync_max_ranks()
+        copies = 2 if mode == "allreduce" else 1       # all-reduce mode alternates between two gradient copies
+        self.CTA_FLAG_PITCH = 160
         with torch.cuda.device(self.device):
-            self._grad_ptr = ops.shard_alloc(max(self.total, 4) * 4)
+            self._grad_ptr = ops.shard_alloc(copies * max(self.total, 4) * 4)
             self._flag_ptr = ops.shard_alloc(2 * max_ranks * 4)
-        self.gradbuf = ops.tensor_from_ptr(self._grad_ptr, (max(self.total, 4),), torch.float32, self.device, owner=self)
+            self._cta_flag_ptr = ops.shard_alloc(max_ranks * self.CTA_FLAG_PITCH * 4) if mode == "allreduce" else 0
+        self.gradbuf = ops.tensor_from_ptr(self._grad_ptr, (copies * max(self.total, 4),), torch.float32, self.device,
+                                           owner=self)
         self.local_sync = torch.zeros(4, dtype=torch.int32, device=self.device)
         self.epoch = 0
         # exchange IPC handles
-        mine = (ops.ipc_export(self._grad_ptr), ops.ipc_export(self._flag_ptr))
+        mine = (ops.ipc_export(self._grad_ptr), ops.ipc_export(self._flag_ptr),
+                ops.ipc_export(self._cta_flag_ptr) if self._cta_flag_ptr else None)
         self._opened: List[int] = []
         self.timeout_s = timeout_s
         # workers leaving (signal, crash handler) raise the stop word of shard 0; spinning peers see it
@@ -56,19 +71,24 @@ class SyncGroup:
                 dist.all_gather_object(allh, mine)
             else:
                 allh = exchange(mine)
-            self.grad_ptrs, self.flag_ptrs = [], []
+            self.grad_ptrs, self.flag_ptrs, self.cta_flag_ptrs = [], [], []
             with torch.cuda.device(self.device):
-                for r, (gh, fh) in enumerate(allh):
+                for r, (gh, fh, ch) in enumerate(allh):
                     if r == rank:
                         self.grad_ptrs.append(self._grad_ptr); self.flag_ptrs.append(self._flag_ptr)
+                        self.cta_flag_ptrs.append(self._cta_flag_ptr)
                     else:
                         g, f = ops.ipc_open(gh), ops.ipc_open(fh)
                         self._opened += [g, f]
                         self.grad_ptrs.append(g); self.flag_ptrs.append(f)
+                        if ch is not None:
+                            c = ops.ipc_open(ch)
+                            self._opened.append(c)
+                            self.cta_flag_ptrs.append(c)
             if exchange is None:
                 dist.barrier()
         else:
-            self.grad_ptrs, self.flag_ptrs = [self._grad_ptr], [self._flag_ptr]
+            self.grad_ptrs, self.flag_ptrs, self.cta_flag_ptrs = [self._grad_ptr], [self._flag_ptr], [self._cta_flag_ptr]
         # segments this rank owns
         self.segments = []
         for name in self.names:
@@ -77,6 +97,30 @@ class SyncGroup:
                 self.segments.append((store.tensor(name).view(-1), b, e))
         gs_owner = owner_of_shard(store.shard_of("global/global_step"), world)
         self.global_step = store.tensor("global/global_step") if gs_owner == rank else None
+        # all-reduce mode: this rank's own copy of every variable - the shard where it owns it, a replica elsewhere
+        self._home: Dict[str, torch.Tensor] = {}
+        if mode == "allreduce":
+            for name in self.names + ["global/global_step"]:
+                t = store.tensor(name)
+                mine_ = owner_of_shard(store.shard_of(name), world) == rank
+                self._home[name] = t if mine_ else torch.zeros(t.shape, dtype=t.dtype, device=self.device)
+
+    def home(self, name: str) -> torch.Tensor:
+        """all-reduce mode: the copy of ``name`` this rank trains on (bind the step kernel to these)."""
+        return self._home[name]
+
+    def home_params(self) -> List[torch.Tensor]:
+        return [self._home[n] for n in self.names]
+
+    def refresh_replicas(self) -> None:
+        """all-reduce mode: load this rank's private replicas from the shards.  Call once the model is ready
+        (after the chief's init or restore) and before the first step; in synchronous mode no shard changes
+        until every rank has joined the first exchange, so the copies of all ranks agree."""
+        for name, t in self._home.items():
+            src = self.store.tensor(name)
+            if t.data_ptr() != src.data_ptr():
+                t.copy_(src)
+        torch.cuda.synchronize(self.device)
 
     def grad_views(self, shapes: Dict[str, tuple]) -> List[torch.Tensor]:
         """Per-variable views into the flat gradient buffer, in ``names`` order."""
@@ -89,6 +133,8 @@ class SyncGroup:
     def reduce_scatter_apply(self, lr: float, device_epoch: bool = True) -> None:
         """``device_epoch``: the kernel numbers the exchanges itself (local_sync[3]), so this call can be
         captured in a CUDA graph and replayed."""
+        if self.mode != "reduce_scatter":
+            raise RuntimeError("the stand-alone exchange kernel is the reduce-scatter form; this group is all-reduce")
         self.epoch += 1
         ops.sync_rs_apply(self.grad_ptrs, self.flag_ptrs, self.rank, self.world, self.segments,
                           -lr / self.world, 0 if device_epoch else self.epoch, self.local_sync, self.global_step,
@@ -110,6 +156,10 @@ class SyncGroup:
         x.abort_flag = self._abort_ptr
         x.timeout_ns = int(self.timeout_s * 1e9)
         x.global_step = self.global_step.data_ptr() if self.global_step is not None else None
+        if self.mode == "allreduce":
+            x.mode, x.grad_stride = 1, max(self.total, 4)
+            for r in range(self.world):
+                x.cta_flags[r] = self.cta_flag_ptrs[r]
         self._xs = x                                       # keep the ctypes object alive
         return x
 

@@ -162,8 +162,11 @@ class Worker:
                     return [pickle.loads(kv.get(f"sync/{gen}/{r}")) for r in range(W)]
                 # variable on ps shard k is reduced by worker (k mod W)
                 # a round may have to wait for workers that are still polling for the chief's initialisation
+                fused_sync = (f.optimizer == "sgd" and f.engine in ("auto", "fused")
+                              and FusedMlp2Stepper.supports(self.spec, f.batch_size))
                 self.sync_group = SyncGroup(store, names, me, W, exchange=exchange,
-                                            timeout_s=f.sync_timeout_secs + 2.0 * f.recovery_wait_secs)
+                                            timeout_s=f.sync_timeout_secs + 2.0 * f.recovery_wait_secs,
+                                            mode="allreduce" if fused_sync else "reduce_scatter")
                 kw["grad_buffers"] = self.sync_group.grad_views({n: tuple(store.tensor(n).shape) for n in names})
             else:
                 kw["adam"] = dict(slots=[store.tensor(n + "/grad_slot") for n in names],
@@ -172,13 +175,16 @@ class Worker:
                                   t=store.tensor("global/adam_t"), apply=self.is_chief)
             fused_ok = (f.sync and f.optimizer == "sgd" and f.engine in ("auto", "fused")
                         and FusedMlp2Stepper.supports(self.spec, f.batch_size))
-            tr = GpuTrainer(self.spec, f.batch_size, f.learning_rate, [store.tensor(n) for n in names],
-                            store.tensor(self.global_step.name), dev, engine="fused" if fused_ok else "layerwise",
+            # fused synchronous mode trains on this rank's own copies (the shard where it owns the variable)
+            params = self.sync_group.home_params() if fused_ok else [store.tensor(n) for n in names]
+            gstep = self.sync_group.home(self.global_step.name) if fused_ok else store.tensor(self.global_step.name)
+            tr = GpuTrainer(self.spec, f.batch_size, f.learning_rate, params, gstep, dev,
+                            engine="fused" if fused_ok else "layerwise",
                             steps_per_launch=f.steps_per_launch if fused_ok else 1, remote=True, tf32=f.tf32)
             if fused_ok:
                 # the whole synchronous step - exchange included - is one kernel (mlp2_step.cu phase D)
                 tr.fused = FusedMlp2Stepper(self.spec, f.batch_size, tr.params, tr.global_step, f.learning_rate, dev,
-                                            max_steps_per_launch=max(1, f.steps_per_launch), remote=True, **kw)
+                                            max_steps_per_launch=max(1, f.steps_per_launch), remote=False, **kw)
                 tr.fused.sync_exchange = self.sync_group.exchange_struct(f.learning_rate)
                 self._sync_in_kernel = True
             else:
@@ -230,6 +236,8 @@ class Worker:
         with self.tracer.span("managed_session", "session"), sv.managed_session() as sess:
             if sv.restored_from:
                 print(f"restored from {sv.restored_from}", flush=True)
+            if getattr(self, "_sync_in_kernel", False):
+                self.sync_group.refresh_replicas()      # the model is ready: load this rank's copies from the shards
             self._begin_time = time.time()
             self._start_time = time.time()
             self._start_step = 0

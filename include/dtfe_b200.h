@@ -126,6 +126,19 @@ typedef struct dtfe_sync_exchange {
   const unsigned* abort_flag; /* optional peer-visible stop word */
   unsigned long long timeout_ns;
   int* global_step;           /* non-NULL on the rank that owns global_step */
+  /* mode 1 - all-reduce fused with the apply (dtfe_mlp2_step only).  Every rank keeps its own copy of the
+   * parameters and of global_step ("home": the shard itself on the rank that owns the variable, a private
+   * replica elsewhere) and passes THOSE as W1/b1/W2/b2/global_step.  After its backward pass every CTA
+   * publishes the gradients it produced, waits for the same CTA of every other rank (per-CTA flags, no grid
+   * barrier), sums all ranks' gradients for exactly the elements it produced - in rank order, so every
+   * replica stays bit-identical - and applies alpha * sum to its home copy (the W1 slice stays in shared
+   * memory across steps).  Nothing is pulled; the only peer traffic is the flag stores and the gradient
+   * loads.  The exchange buffers hold two copies of the flat gradient, grad_stride floats apart, used by
+   * alternate steps, which makes a second barrier per step unnecessary.  seg_* and global_step above are
+   * ignored. */
+  int mode;                   /* 0: reduce-scatter by the owners (default), 1: all-reduce with apply */
+  size_t grad_stride;         /* mode 1: floats between the two copies of the flat gradient */
+  unsigned* cta_flags[16];    /* mode 1: every rank's per-CTA arrival words, [16 ranks][160 CTAs] u32 */
 } dtfe_sync_exchange;
 
 /* ---- the whole reference training step in one cooperative kernel ------------------------------- */

@@ -373,6 +373,42 @@ def test_fused_step_with_in_kernel_sync_exchange_single_rank():
     sg.close(); store.close()
 
 
+@pytest.mark.parametrize("dims,B", [((784, 100, 10), 100), ((50, 30, 7), 37)])
+def test_fused_step_allreduce_exchange_single_rank(dims, B):
+    """The all-reduce form of the in-kernel exchange with world = 1: per-CTA flags, alternating gradient copies,
+    W1 slice resident in shared memory across steps and launches, apply to the home copy, local step counter.
+    Must equal plain SGD over two launches (the second starts from what the first wrote back)."""
+    from distributedtensorflowexample_b200.parallel.sync import SyncGroup
+    from distributedtensorflowexample_b200.train.gpu_step import FusedMlp2Stepper
+    spec = MLPSpec(dims)
+    model, store, names = _store(spec, num_ps=2, seed=21)
+    params_np = [store.read(n).astype(np.float64) for n in names]
+    from distributedtensorflowexample_b200.data import synthetic_arrays
+    x, y = synthetic_arrays(1000, seed=5, num_classes=dims[2], dim=dims[0])
+    y = y.astype(np.int32)
+    X = torch.tensor(x, device="cuda"); Y = torch.tensor(y, device="cuda")
+    lr, nsteps = 0.05, 4
+    sg = SyncGroup(store, names, 0, 1, timeout_s=5.0, mode="allreduce")
+    sg.refresh_replicas()
+    shapes = {n: tuple(store.tensor(n).shape) for n in names}
+    st = FusedMlp2Stepper(spec, B, sg.home_params(), sg.home("global/global_step"), lr, "cuda:0",
+                          max_steps_per_launch=nsteps, remote=False, grad_buffers=sg.grad_views(shapes))
+    st.sync_exchange = sg.exchange_struct(lr)
+    idx = torch.arange(2 * nsteps * B, device="cuda", dtype=torch.int32)
+    st.run(X, Y, nsteps=nsteps, batch_idx=idx[:nsteps * B])
+    st.run(X, Y, nsteps=nsteps, batch_idx=idx[nsteps * B:], out_offset=0)
+    torch.cuda.synchronize()
+    assert sg.aborted() == 0
+    for s in range(2 * nsteps):
+        rows = slice(s * B, (s + 1) * B)
+        oracle.sgd_step(params_np, x[rows].astype(np.float64), y[rows], lr)
+    for n, p in zip(names, params_np):
+        np.testing.assert_allclose(store.read(n), p, rtol=1e-3, atol=2e-4)     # world = 1: home IS the shard
+    assert store.read("global/global_step").item() == 2 * nsteps
+    assert st.step[:nsteps].cpu().tolist() == list(range(nsteps, 2 * nsteps))
+    sg.close(); store.close()
+
+
 def test_tracer_device_spans_time_the_step_kernel():
     """utils.tracing on a GPU: a device span is a CUDA-event pair on the launching stream (plus an NVTX range
     for the host span); its duration must be the kernel's, not the host call's."""
