@@ -36,7 +36,7 @@ def parse_args():
     ap.add_argument("--batch", type=int, default=0, help="per-worker batch (default: 100 mnist / 4096 wide)")
     ap.add_argument("--steps-per-launch", type=int, default=0,
                     help="training steps fused into one persistent-kernel launch (0 = auto)")
-    ap.add_argument("--engine", default="auto", choices=["auto", "fused", "layerwise", "tc"])
+    ap.add_argument("--engine", default="auto", choices=["auto", "fused", "fused_tc", "layerwise", "tc"])
     ap.add_argument("--e2e-steps", type=int, default=0, help="steps of the host-fed end-to-end measurement (0 = --steps)")
     ap.add_argument("--e2e-steps-per-launch", type=int, default=8,
                     help="host-fed steps that share one kernel launch in the end-to-end measurement (1..16)")

@@ -926,8 +926,9 @@ DTFE_API int dtfe_mlp2_step_grid(int D, int ks) { return (D + ks - 1) / ks; }
 // part[G*B*H] | dA[B*H] | Hbuf[B*H] | dZ[B*C] | rowloss[B] | rowcorrect[B] | delta | mirror[2] | sync[4]
 DTFE_API size_t dtfe_mlp2_step_workspace_words(int B, int D, int H, int C, int ks) {
   size_t G = (size_t)((D + ks - 1) / ks);
+  if (G < 8) G = 8;          // the tensor-core form (dtfe_mlp2_step_tc) always keeps 8 split-K partials
   size_t w = G * B * H + 2 * (size_t)B * H + (size_t)B * C + 2 * (size_t)B + 3 * ((size_t)H * C + H + C + 12) + 4;
-  return (w + 3) / 4 * 4 + 32;
+  return (w + 3) / 4 * 4 + 64;
 }
 
 using Mlp2Launch = dtfe_mlp2_launch;

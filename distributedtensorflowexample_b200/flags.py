@@ -201,7 +201,7 @@ def define_framework_flags(flag_values: FlagValues = FLAGS) -> FlagValues:
     DEFINE_string("dtype", "float32", "float32 | bfloat16 parameter/compute dtype of the GPU path", flag_values)
     DEFINE_boolean("tf32", False, "Let the fp32 layer-wise engine use tcgen05 kind::tf32 GEMMs (TMA pull from the fp32 "
                    "shards) where operand pitches allow; default is exact fp32", flag_values)
-    DEFINE_string("engine", "auto", "GPU step engine: auto | fused | layerwise | tc", flag_values)
+    DEFINE_string("engine", "auto", "GPU step engine: auto | fused (fp32 SIMT persistent kernel) | fused_tc (the same step on tcgen05 kind::tf32) | layerwise | tc", flag_values)
     DEFINE_string("data", "mnist", "mnist | synthetic", flag_values)
     DEFINE_string("data_dir", "MNIST_data", "Directory with the MNIST idx.gz files", flag_values)
     DEFINE_string("hidden", "100", "Comma-separated hidden layer widths (reference: 100)", flag_values)

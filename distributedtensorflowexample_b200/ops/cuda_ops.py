@@ -49,6 +49,8 @@ _SIGS = {
     "dtfe_mlp2_step_ctas": ([c_int, c_int, c_int, c_int], c_int),
     "dtfe_mlp2_step_workspace_words": ([c_int, c_int, c_int, c_int, c_int], c_size_t),
     "dtfe_mlp2_step": ([_P, _P], c_int),
+    "dtfe_mlp2_step_tc": ([_P, _P], c_int),
+    "dtfe_mlp2_step_tc_supported": ([c_int, c_int, c_int, c_int], c_int),
     "dtfe_hostfeed_create": ([c_int, c_int, c_int, POINTER(_P)], c_int),
     "dtfe_hostfeed_destroy": ([_P], c_int),
     "dtfe_mlp2_train_host": ([_P, _P, POINTER(_P), POINTER(_P), c_int, _P, _P], c_int),
@@ -419,8 +421,10 @@ class Mlp2Step:
 
     def run(self, W1, b1, W2, b2, global_step, X, labels, lr: float, nsteps: int = 1, batch_idx=None,
             rows_per_step: int = 0, atomic: bool = True, train: bool = True, out_offset: int = 0,
-            remote: bool = True, dbg=None, grads=None, cursor=None, sync_exchange=None, outs=None):
-        """``outs``: (loss, acc, step) device tensors (float32, float32, int32; >= nsteps elements each) that receive
+            remote: bool = True, dbg=None, grads=None, cursor=None, sync_exchange=None, outs=None, tc: bool = False):
+        """``tc``: run the tensor-core form of the step (``dtfe_mlp2_step_tc``: tcgen05 kind::tf32 on one 8-CTA
+        cluster) instead of the fp32 SIMT kernel; asynchronous lossless training only.
+        ``outs``: (loss, acc, step) device tensors (float32, float32, int32; >= nsteps elements each) that receive
         the per-step results instead of this object's own ring."""
         assert outs is not None or nsteps + out_offset <= self.max_steps
         L = _Mlp2Launch()
@@ -447,4 +451,7 @@ class Mlp2Step:
         L.cursor = _ptr(cursor)
         if sync_exchange is not None:
             L.sync_exchange = ctypes.addressof(sync_exchange)
-        check(lib().dtfe_mlp2_step(ctypes.byref(L), _stream()), "dtfe_mlp2_step")
+        if tc:
+            check(lib().dtfe_mlp2_step_tc(ctypes.byref(L), _stream()), "dtfe_mlp2_step_tc")
+        else:
+            check(lib().dtfe_mlp2_step(ctypes.byref(L), _stream()), "dtfe_mlp2_step")

@@ -56,8 +56,11 @@ class DeviceDataset:
 class FusedMlp2Stepper:
     def __init__(self, spec: MLPSpec, batch: int, params: Sequence[torch.Tensor], global_step: torch.Tensor,
                  lr: float, device, max_steps_per_launch: int = 1, atomic: bool = True, ks: int = 8,
-                 remote: bool = True, grad_buffers: Optional[Sequence[torch.Tensor]] = None):
-        """``grad_buffers``: synchronous mode - raw gradients go to these 4 buffers (this rank's exchange
+                 remote: bool = True, grad_buffers: Optional[Sequence[torch.Tensor]] = None, tc: bool = False):
+        """``tc``: training launches run on the tensor cores (``csrc/cuda/mlp2_step_tc.cu``: tcgen05 kind::tf32, one
+        8-CTA cluster, W1 pulled by TMA from the shard); evaluation launches, ``atomic=False`` and synchronous mode
+        stay on the fp32 SIMT kernel.
+        ``grad_buffers``: synchronous mode - raw gradients go to these 4 buffers (this rank's exchange
         buffer) instead of being pushed; ``parallel.sync.SyncGroup.reduce_scatter_apply`` finishes the step."""
         self.grad_buffers = list(grad_buffers) if grad_buffers is not None else None
         self.cursor = None
@@ -69,6 +72,7 @@ class FusedMlp2Stepper:
         self.W1, self.b1, self.W2, self.b2 = params
         self.global_step = global_step
         self.remote = remote      # False only when every shard is in this GPU's own HBM
+        self.tc = bool(tc) and self.supports_tc(spec, batch) and atomic and grad_buffers is None
         self.dbg = None
         self.k = ops.Mlp2Step(batch, D, H, C, device, max_steps=max_steps_per_launch, ks=ks)
         self.launches_per_call = 1
@@ -78,6 +82,13 @@ class FusedMlp2Stepper:
         return (spec.num_layers == 2 and spec.param_dtype == "float32" and batch <= 128 and spec.dims[1] <= 128
                 and spec.dims[2] <= 16 and (spec.dims[0] + 7) // 8 <= 148)
 
+    @staticmethod
+    def supports_tc(spec: MLPSpec, batch: int) -> bool:
+        if spec.num_layers != 2 or spec.param_dtype != "float32" or spec.dims[0] % 4:
+            return False
+        D, H, C = spec.dims
+        return bool(ops.lib().dtfe_mlp2_step_tc_supported(batch, D, H, C))
+
     def run(self, X: torch.Tensor, labels: torch.Tensor, nsteps: int = 1, batch_idx: Optional[torch.Tensor] = None,
             rows_per_step: int = 0, train: bool = True, out_offset: int = 0, outs=None) -> None:
         """Results land in ``self.k.loss/acc/step[out_offset : out_offset+nsteps]`` (device), or in the three
@@ -85,7 +96,8 @@ class FusedMlp2Stepper:
         self.k.run(self.W1, self.b1, self.W2, self.b2, self.global_step, X, labels, self.lr, nsteps=nsteps,
                    batch_idx=batch_idx, rows_per_step=rows_per_step, atomic=self.atomic, train=train,
                    out_offset=out_offset, remote=self.remote, dbg=self.dbg, grads=self.grad_buffers,
-                   cursor=self.cursor, sync_exchange=self.sync_exchange, outs=outs)
+                   cursor=self.cursor, sync_exchange=self.sync_exchange, outs=outs,
+                   tc=self.tc and train and self.sync_exchange is None)
 
     @property
     def loss(self): return self.k.loss

@@ -42,9 +42,10 @@ class GpuTrainer:
                 engine = "fused" if FusedMlp2Stepper.supports(spec, batch) else "layerwise"
         self.engine = engine
         self.launch_count = 0
-        if engine == "fused":
+        if engine in ("fused", "fused_tc"):
             self.fused = FusedMlp2Stepper(spec, batch, self.params, global_step, lr, self.device,
-                                          max_steps_per_launch=self.steps_per_launch, atomic=atomic, remote=remote)
+                                          max_steps_per_launch=self.steps_per_launch, atomic=atomic, remote=remote,
+                                          tc=engine == "fused_tc")
             self.layer = LayerwiseStepper(spec, batch, self.params, global_step, lr, self.device, atomic=atomic, tf32=tf32)
         elif engine == "layerwise":
             self.fused = None

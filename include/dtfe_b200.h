@@ -168,6 +168,16 @@ int dtfe_mlp2_step_ctas(int B, int D, int H, int ks);  /* CTAs per launch on the
 size_t dtfe_mlp2_step_workspace_words(int B, int D, int H, int C, int ks);
 int dtfe_mlp2_step(const dtfe_mlp2_launch* launch, void* stream);
 
+/* dtfe_mlp2_step on the tensor cores (same launch struct, workspace and results): X.W1 and X^T.dA run as
+ * tcgen05.mma kind::tf32 with fp32 accumulators in TMEM on one cluster of 8 CTAs; CTA i owns a slice of the
+ * features, pulls its slice of W1 from the shard with TMA (one step ahead, own update added in shared memory)
+ * and pushes -lr*dW1 from the TMEM epilogue with red.add.v4.  tf32 rounds X, W1 and dA to 10 mantissa bits;
+ * everything else is fp32.  Asynchronous lossless training only (train = 1, atomic = 1, no gradient buffers, no
+ * sync_exchange); `ks` is ignored.  Limits: B <= 104, D <= 832, H <= 128 with H % 4 == 0, C <= 16, 16-byte
+ * aligned parameters.  Reference: the same step, worker.py:129-141. */
+int dtfe_mlp2_step_tc_supported(int B, int D, int H, int C);
+int dtfe_mlp2_step_tc(const dtfe_mlp2_launch* launch, void* stream);
+
 /* Host-fed loop (the reference's feed_dict path, worker.py:133-137): `nsteps` steps, step i fed from the
  * pinned host buffers x_host[i] ([B,D] fp32) / y_host[i] ([B] int32) through double-buffered staging
  * and private copy streams; the loss of step i is copied back to loss_host[i] (pinned).  Up to
