@@ -6,6 +6,7 @@ asynchronous parameter-server training, examples/sec, device-timed, max over ran
     python bench.py --impl reference ...                          # the TF1 reference (unavailable here)
     python bench.py --impl nccl-ps ...                            # torch.distributed NCCL ps baseline
     python bench.py --config wide ...                             # 784-8192-8192-10, batch 4096, bf16
+    python bench.py --config bw --gpus N ...                      # ps push/pull bandwidth sweep 4 KB - 1 GB vs NCCL
 
 For N>1 the driver launches this file under torchrun (one rank per GPU).  One JSON line is
 printed by rank 0.  See DESIGN.md "Benchmark methodology" for what is inside the timed region.
@@ -31,7 +32,8 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=2000)
     ap.add_argument("--warmup", type=int, default=50)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "nccl-ps"])
-    ap.add_argument("--config", default="mnist", choices=["mnist", "wide"])
+    ap.add_argument("--config", default="mnist", choices=["mnist", "wide", "bw"])
+    ap.add_argument("--bw-max-mb", dest="bw_max_mb", type=int, default=1024, help="--config bw: largest shard in MB")
     ap.add_argument("--mode", default="async", choices=["async", "sync"])
     ap.add_argument("--batch", type=int, default=0, help="per-worker batch (default: 100 mnist / 4096 wide)")
     ap.add_argument("--steps-per-launch", type=int, default=0,
@@ -153,6 +155,9 @@ def main():
     from distributedtensorflowexample_b200 import benchlib
     if args.config == "wide":
         return benchlib.run_wide(args, rank, world, dev, ClockSampler)
+    if args.config == "bw":
+        from distributedtensorflowexample_b200 import bench_bw
+        return bench_bw.run(args, rank, world, dev)
     return benchlib.run_mnist(args, rank, world, dev, ClockSampler)
 
 

@@ -91,6 +91,13 @@ DTFE_API int dtfe_enable_peer(int dev, int peer) {
   return 0;
 }
 
+// Copy-engine pull: one asynchronous device-to-device copy (cudaMemcpyDefault: source may be a peer-mapped shard).
+// Unlike dtfe_pull_f32 it takes no SM away from the GEMMs that run next to it (reference sync_op, worker.py:81-85).
+DTFE_API int dtfe_memcpy_async(void* dst, const void* src, size_t bytes, void* stream) {
+  DTFE_CUDA_CHECK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, (cudaStream_t)stream));
+  return 0;
+}
+
 // ---- L2 flush (bench hygiene): overwrite a buffer larger than L2 ----------------
 __global__ void k_fill_u32(uint32_t* p, size_t n, uint32_t v) {
   size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;

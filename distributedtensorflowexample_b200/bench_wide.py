@@ -55,16 +55,23 @@ def run(args, rank: int, world: int, dev, ClockSampler) -> int:
     for s in range(W):
         step(s)
     _barrier(world)
+    R = max(1, min(getattr(args, "repeats", 25), 9))
     clocks = ClockSampler(dev.index or 0, period_s=0.02)
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     clocks.start()
-    e0.record()
-    for s in range(K):
-        step(s)
-    e1.record()
-    torch.cuda.synchronize()
+    samples = []
+    for r in range(R):
+        _barrier(world)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for s in range(K):
+            step(s)
+        e1.record()
+        torch.cuda.synchronize()
+        samples.append(e0.elapsed_time(e1))
     clk = clocks.stop()
-    ms = _max_over_ranks(e0.elapsed_time(e1), world, dev)
+    from .benchlib import _max_over_ranks_vec
+    samples = sorted(_max_over_ranks_vec(samples, world, dev))
+    ms = samples[len(samples) // 2]
     _barrier(world)
     value = world * B * K / (ms * 1e-3)
     flops = oracle.flops_per_step(dims, B)["step"]
@@ -100,8 +107,27 @@ def run(args, rank: int, world: int, dev, ClockSampler) -> int:
         "gpu_launches": tr.layer.launches_per_call * K, "clocks": clk,
         "tflops_per_gpu": flops / (ms / K * 1e-3) / 1e12, "final_loss": float(tr.layer.loss.item()),
     }
+    out["samples"] = {"n": len(samples), "ms_per_step_min": samples[0] / K, "ms_per_step_median": ms / K,
+                      "ms_per_step_max": samples[-1] / K}
     if e2e is not None:
         out["e2e"] = e2e
+    if not getattr(args, "no_baseline", False):
+        # same box, same run: torch ops (cuBLAS bf16 GEMMs) + one NCCL all-reduce of the flat gradient per step,
+        # whole step in a CUDA graph
+        import os as _os, sys as _sys
+        root = _os.path.dirname(_os.path.dirname(_os.path.abspath(__file__)))
+        if root not in _sys.path:
+            _sys.path.insert(0, root)
+        from baseline import nccl_ps
+        try:
+            m = nccl_ps.measure("wide", B, K, W, rank, world, dev, graph=True, flat=True, repeats=min(R, 5), e2e=False)
+            out["baseline"] = {"impl": "nccl-ps: torch/cuBLAS bf16 GEMMs + one NCCL all-reduce per step, CUDA graph",
+                               **{k: m[k] for k in ("value", "ms_per_step", "ms_per_step_min", "ms_per_step_max", "samples")}}
+            out["vs_baseline"] = value / m["value"]
+            out["vs_baseline_denominator"] = "in-run nccl-ps baseline (graph-captured)"
+        except Exception as e:
+            out["baseline"] = {"error": f"{type(e).__name__}: {e}"[:300]}
+        _barrier(world)
     if rank == 0:
         print(json.dumps(out), flush=True)
     store.close()

@@ -40,6 +40,7 @@ _SIGS = {
     "dtfe_push_sgd_f32": ([_P, _P, c_size_t, c_float, c_int, _P], c_int),
     "dtfe_push_sgd_bf16": ([_P, _P, c_size_t, c_float, _P], c_int),
     "dtfe_pull_f32": ([_P, _P, c_size_t, _P], c_int),
+    "dtfe_memcpy_async": ([_P, _P, c_size_t, _P], c_int),
     "dtfe_adam_apply_f32": ([_P, _P, _P, _P, c_size_t, c_float, c_float, c_float, c_float, c_float, _P], c_int),
     "dtfe_sync_rs_apply_f32": ([POINTER(_P), POINTER(_P), c_int, c_int, c_int, POINTER(_P), POINTER(c_size_t),
                                 POINTER(c_size_t), c_float, c_uint, _P, _P, _P, ctypes.c_double, _P], c_int),
@@ -266,6 +267,11 @@ def push_sgd(shard: torch.Tensor, grad: torch.Tensor, alpha: float, atomic: bool
 
 def pull(dst: torch.Tensor, shard: torch.Tensor):
     check(lib().dtfe_pull_f32(dst.data_ptr(), shard.data_ptr(), dst.numel(), _stream()), "dtfe_pull_f32")
+
+
+def pull_ce(dst: torch.Tensor, shard: torch.Tensor, nbytes: int) -> None:
+    """Bulk pull on a copy engine (the current stream's): ``nbytes`` from ``shard`` (possibly peer HBM) to ``dst``."""
+    check(lib().dtfe_memcpy_async(dst.data_ptr(), shard.data_ptr(), nbytes, _stream()), "dtfe_memcpy_async")
 
 
 def adam_apply(param, m, v, slot, lr_t: float, beta1: float, beta2: float, eps: float, grad_scale: float = 1.0):

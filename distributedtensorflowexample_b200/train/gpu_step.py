@@ -292,32 +292,50 @@ class TcStepper:
         self.launches_per_call = L + 2 + (L - 1) + 2 * L + 1
 
     def pull_partitioned(self) -> None:
-        """Issue this step's pulls on a side stream, one event per variable: the copy of layer l+1's
-        weights over NVLink runs under layer l's GEMM; ``_w`` makes the consumer wait for its own event."""
+        """Issue this step's pulls on side streams, one event per variable: the copy of layer l+1's weights over
+        NVLink runs under layer l's GEMM; ``_w`` makes the consumer wait for its own event.  The copies are
+        ``cudaMemcpyAsync`` calls, i.e. they run on the copy engines and leave every SM to the GEMMs (set
+        ``DTFE_PULL_SM=1`` for round 1's SM copy kernel); blocks go round-robin over a few streams so that
+        several engines and several peers' links work at once."""
         if not self.replicas:
             return
+        import os
         if self._pull_stream is None:
-            self._pull_stream = torch.cuda.Stream(device=self.loss.device)
-            self._pull_events = {i: torch.cuda.Event() for i in self.replicas}
+            dev = self.loss.device
+            self._pull_streams = [torch.cuda.Stream(device=dev) for _ in range(4)]
+            self._pull_stream = self._pull_streams[0]
+            self._pull_events = {i: [torch.cuda.Event() for _ in self._pull_streams] for i in self.replicas}
+            self._pull_sm = os.environ.get("DTFE_PULL_SM") == "1"
         main = torch.cuda.current_stream()
-        self._pull_stream.wait_stream(main)        # previous step's readers of the replicas are done
-        with torch.cuda.stream(self._pull_stream):
-            # small things first (biases, thin matrices), then the big matrices in layer order
-            order = sorted(self.replicas, key=lambda i: (self._nbytes(i) > (1 << 20), i))
-            for i in order:
-                rep = self.replicas[i]
-                blocks = self.params[i] if isinstance(self.params[i], (list, tuple)) else [self.params[i]]
-                rp = blocks[0].shape[0]
-                for k, blk in enumerate(blocks):
-                    if blk.dim() == 2:
-                        dst = rep[k * rp:(k + 1) * rp]
-                        # blocks and replica rows share the pitch, so each block is one contiguous byte range
-                        n = rp * blk.stride(0)
+        for st in self._pull_streams:
+            st.wait_stream(main)                   # previous step's readers of the replicas are done
+        # small things first (biases, thin matrices), then the big matrices in layer order
+        order = sorted(self.replicas, key=lambda i: (self._nbytes(i) > (1 << 20), i))
+        rr = 0
+        for i in order:
+            rep = self.replicas[i]
+            blocks = self.params[i] if isinstance(self.params[i], (list, tuple)) else [self.params[i]]
+            rp = blocks[0].shape[0]
+            used = set()
+            for k, blk in enumerate(blocks):
+                if blk.dim() == 2:
+                    dst = rep[k * rp:(k + 1) * rp]
+                    # blocks and replica rows share the pitch, so each block is one contiguous byte range
+                    n = rp * blk.stride(0)
+                else:
+                    dst, n = rep, (blk.numel() + 1) // 2 * 2
+                si = rr % len(self._pull_streams); rr += 1
+                used.add(si)
+                with torch.cuda.stream(self._pull_streams[si]):
+                    if self._pull_sm:
+                        ops.pull(torch.as_strided(dst, (n,), (1,)).view(torch.float32),
+                                 torch.as_strided(blk, (n,), (1,)).view(torch.float32))
                     else:
-                        dst, n = rep, (blk.numel() + 1) // 2 * 2
-                    ops.pull(torch.as_strided(dst, (n,), (1,)).view(torch.float32),
-                             torch.as_strided(blk, (n,), (1,)).view(torch.float32))
-                self._pull_events[i].record(self._pull_stream)
+                        ops.pull_ce(dst, blk, n * 2)
+            for si in used:
+                self._pull_events[i][si].record(self._pull_streams[si])
+            self._pull_used = getattr(self, "_pull_used", {})
+            self._pull_used[i] = used
         self._pending = set(self.replicas)
 
     def _nbytes(self, i) -> int:
@@ -328,7 +346,8 @@ class TcStepper:
     def _w(self, i):
         if i in self.replicas:
             if i in self._pending:
-                torch.cuda.current_stream().wait_event(self._pull_events[i])
+                for si in self._pull_used[i]:
+                    torch.cuda.current_stream().wait_event(self._pull_events[i][si])
                 self._pending.discard(i)
             return self.replicas[i]
         return self.params[i]

@@ -29,7 +29,7 @@ import numpy as np
 from ..flags import FLAGS
 from ..models.mlp import spec_from_flags
 from ..utils.checkpoint import FastSaver
-from ..utils.events import FileWriter, training_summary
+from ..utils.events import FileWriter, Summary, TAG_TEST_ACCURACY, training_summary
 from ..utils import tracing
 from ..parallel.gloo_ps import SyncAborted
 from .replica import build_replicated_model
@@ -282,7 +282,13 @@ class Worker:
             self._start_step = step
         if step % f.eval_every == 0:
             with self.tracer.span("eval", "host", step=step):
-                print("test accuracy: {}".format(eval_fn()), flush=True)
+                test_acc = eval_fn()
+                print("test accuracy: {}".format(test_acc), flush=True)
+            # additive: the evaluation also goes to the event file (the reference only prints it), so a run's
+            # time-to-accuracy can be read from its logs: wall_time of this event minus that of the first step's
+            if getattr(self, "_summary_thread", None) is not None:
+                self._summary_thread.drain()         # keep the file in step order
+            self.summary_writer.add_summary(Summary([(TAG_TEST_ACCURACY, float(test_acc))]), step)
         return step >= f.training_steps
 
     def _loop_cpu(self, sv: Supervisor, dataset) -> int:

@@ -22,6 +22,7 @@ from . import native_io
 TAG_LOSS = "local/loss"
 TAG_ACCURACY = "local/accuracy_1"
 TAG_STEPS_PER_SEC = "global/global_step/sec"
+TAG_TEST_ACCURACY = "local/test_accuracy"     # additive: the reference prints the evaluation, it does not log it
 
 
 class Summary:

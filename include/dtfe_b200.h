@@ -88,6 +88,9 @@ int dtfe_push_sgd_f32(float* shard, const float* grad, size_t n, float alpha, in
 int dtfe_push_sgd_bf16(void* shard_bf16, const float* grad, size_t n, float alpha, void* stream);
 /* dst[i] = shard[i] with L1-bypassing loads: the stand-alone pull (reference worker.py:81-85 sync_op). */
 int dtfe_pull_f32(float* dst, const float* shard, size_t n, void* stream);
+/* The same pull on a copy engine (cudaMemcpyAsync, source may be a peer-mapped shard): for bulk pulls that run
+ * next to GEMMs and must not take SMs from them (reference sync_op, worker.py:81-85). */
+int dtfe_memcpy_async(void* dst, const void* src, size_t bytes, void* stream);
 /* Adam at the owner: consumes and clears the accumulation slot workers pushed into
  * (no counterpart in the reference, which only has GradientDescentOptimizer, worker.py:71). */
 int dtfe_adam_apply_f32(float* param, float* m, float* v, float* slot, size_t n, float lr_t, float beta1,

@@ -28,7 +28,10 @@ def step(record):
     events = []
     m = mark if record else (lambda n: None)
     m("start")
-    st.pull_partitioned(); torch.cuda.current_stream().wait_stream(st._pull_stream) if st._pull_stream else None; st._pending = set(); m("pull (not overlapped here)")
+    st.pull_partitioned()
+    if st._pull_stream is not None:
+        for ps in st._pull_streams: torch.cuda.current_stream().wait_stream(ps)
+    st._pending = set(); m("pull (not overlapped here)")
     h = X
     L = 3
     for l in range(L):
