@@ -43,7 +43,7 @@ def parse_args():
     ap.add_argument("--e2e-steps-per-launch", type=int, default=8,
                     help="host-fed steps that share one kernel launch in the end-to-end measurement (1..16)")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--sync-mode", dest="sync_mode", default="allreduce", choices=["allreduce", "reduce_scatter"],
+    ap.add_argument("--sync-mode", dest="sync_mode", default="allreduce_ll", choices=["allreduce_ll", "allreduce", "reduce_scatter"],
                     help="--mode sync: form of the in-kernel exchange")
     ap.add_argument("--repeats", type=int, default=25, help="timed samples of K steps each (median is reported)")
     ap.add_argument("--no-baseline", dest="no_baseline", action="store_true",

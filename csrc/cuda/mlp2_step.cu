@@ -110,17 +110,32 @@ __device__ __forceinline__ void push1(float* p, float v, int atomic) {
   if (atomic) dtfe::red_add_sys(p, v);
   else *p = dtfe::ld_relaxed_sys(p) + v;
 }
+// Low-latency synchronous exchange (dtfe_sync_exchange mode 2): where to send a gradient element.
+struct LLSend {
+  float* const* recv;       // every rank's receive buffer
+  long slot;                // pair index of element 0 of THIS rank's area in the current copy: (copy * world + rank) * stride
+  int world;
+  unsigned epoch;
+};
+__device__ __forceinline__ void ll_send(const LLSend& ll, long idx, float g) {
+  const float tag = __uint_as_float(ll.epoch);
+  for (int p = 0; p < ll.world; ++p)       // one 8-byte store per rank (own buffer included): value + step number
+    asm volatile("st.relaxed.sys.global.v2.f32 [%0], {%1, %2};" :: "l"(ll.recv[p] + 2 * (ll.slot + idx)), "f"(g), "f"(tag) : "memory");
+}
 // Asynchronous mode: push -lr*g into the shard.  Synchronous mode: leave the raw gradient in this
-// rank's exchange buffer for the reduce-scatter kernel.
-__device__ __forceinline__ void emit(float* shard, float* gbuf, long i, float g, float nlr, int atomic) {
-  if (gbuf) __stcg(gbuf + i, g);
+// rank's exchange buffer for the reduce-scatter kernel (or send it, low-latency mode: gbuf then only
+// carries the element's offset in the flat gradient).
+__device__ __forceinline__ void emit(float* shard, float* gbuf, long i, float g, float nlr, int atomic,
+                                     const LLSend* ll = nullptr, const float* gbase = nullptr) {
+  if (ll) ll_send(*ll, (gbuf - gbase) + i, g);
+  else if (gbuf) __stcg(gbuf + i, g);
   else push1(shard + i, __fmul_rn(nlr, g), atomic);
 }
 // Small parameters in ahead mode: the update also goes to the local delta buffer every CTA reads next step.
 __device__ __forceinline__ void emit_small(float* shard, float* gbuf, float* delta, long i, float g, float nlr,
-                                           int atomic) {
+                                           int atomic, const LLSend* ll = nullptr, const float* gbase = nullptr) {
   if (delta) __stcg(delta + i, __fmul_rn(nlr, g));
-  emit(shard, gbuf, i, g, nlr, atomic);
+  emit(shard, gbuf, i, g, nlr, atomic, ll, gbase);
 }
 
 __device__ __forceinline__ void st_relaxed_sys_u32(unsigned* p, unsigned v) {
@@ -251,7 +266,8 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
   };
   // Synchronous all-reduce mode: the parameters this kernel is given are this rank's own copies; the W1 slice
   // stays in shared memory for the whole launch and is updated in place in phase D.
-  const bool sx1 = a.has_sx && a.sx.mode == 1;
+  const bool sx1 = a.has_sx && a.sx.mode >= 1;      // all-reduce forms: flags + peer loads (1) or low-latency pairs (2)
+  const bool sxll = a.has_sx && a.sx.mode == 2;
   if (ahead || sx1) {
     dtfe::cta_copy_async(Ws, a.W1 + (long)k0 * H, nW1, tid, kThreads);
     dtfe::cp_async_commit();
@@ -278,11 +294,18 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
     DBG_STAMP(0);
     int ylab = 0;
     // all-reduce mode alternates between two copies of the gradient buffer (see phase D)
-    const long goff = sx1 ? (long)((sx_epoch0 + (unsigned)s + 1u) & 1u) * (long)a.sx.grad_stride : 0;
+    const long goff = (sx1 && !sxll) ? (long)((sx_epoch0 + (unsigned)s + 1u) & 1u) * (long)a.sx.grad_stride : 0;
     float* const gW1 = a.gW1 ? a.gW1 + goff : nullptr;
     float* const gb1 = a.gb1 ? a.gb1 + goff : nullptr;
     float* const gW2 = a.gW2 ? a.gW2 + goff : nullptr;
     float* const gb2 = a.gb2 ? a.gb2 + goff : nullptr;
+    LLSend llv;
+    const LLSend* const ll = sxll ? &llv : nullptr;
+    const float* const gbase = sxll ? a.sx.grads[a.sx.rank] : nullptr;
+    if (sxll) {
+      llv.recv = a.sx.ll_recv; llv.world = a.sx.world; llv.epoch = sx_epoch0 + (unsigned)s + 1u;
+      llv.slot = ((long)(llv.epoch & 1u) * a.sx.world + a.sx.rank) * (long)a.sx.grad_stride;
+    }
     if (slice) {
 #pragma unroll
     for (int i = 0; i < kXPer; ++i) {
@@ -677,7 +700,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
               if (b < B) v = fmaf(hc[i], dZs[b * C + c], v);
             }
             v = dtfe::warp_sum(v);
-            if (lane == 0) emit_small(a.W2, gW2, delta, (long)tt * C + c, v, nlr, a.atomic);
+            if (lane == 0) emit_small(a.W2, gW2, delta, (long)tt * C + c, v, nlr, a.atomic, ll, gbase);
           }
           if (warp == 5) {                        // db1[tt] = sum_b dA[b][tt]
             float v = 0.f;
@@ -685,7 +708,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
             else if (rnd == 1) v = (dacol1[0] + dacol1[1]) + (dacol1[2] + dacol1[3]);
             else for (int b = lane; b < B; b += 32) v += __ldcg(a.dA + (long)b * H + tt);
             v = dtfe::warp_sum(v);
-            if (lane == 0) emit_small(a.b1, gb1, delta ? delta + dOffB1 : nullptr, tt, v, nlr, a.atomic);
+            if (lane == 0) emit_small(a.b1, gb1, delta ? delta + dOffB1 : nullptr, tt, v, nlr, a.atomic, ll, gbase);
           }
         }
         if (g == book) {                          // db2[c] = sum_b dZ[b][c], spread over the warps
@@ -693,7 +716,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
             float v = 0.f;
             for (int b = lane; b < B; b += 32) v += dZs[b * C + c];
             v = dtfe::warp_sum(v);
-            if (lane == 0) emit_small(a.b2, gb2, delta ? delta + dOffB2 : nullptr, c, v, nlr, a.atomic);
+            if (lane == 0) emit_small(a.b2, gb2, delta ? delta + dOffB2 : nullptr, c, v, nlr, a.atomic, ll, gbase);
           }
         }
       }
@@ -712,8 +735,8 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
               if (wv0) g0 += pq[w * (KS * kMaxH) + wj0];
               if (kParts < 4 && wv1) g1 += pq[w * (KS * kMaxH) + wj1];
             }
-            if (wv0) emit(a.W1, gW1, (long)k * H + wj0, g0, nlr, a.atomic);
-            if (kParts < 4 && wv1) emit(a.W1, gW1, (long)k * H + wj1, g1, nlr, a.atomic);
+            if (wv0) emit(a.W1, gW1, (long)k * H + wj0, g0, nlr, a.atomic, ll, gbase);
+            if (kParts < 4 && wv1) emit(a.W1, gW1, (long)k * H + wj1, g1, nlr, a.atomic, ll, gbase);
             if (ahead) {        // fetched value + own update = what the shard holds (bitwise, absent other writers)
               float* w0 = Ws + (wgrp * 4 + q) * HP + wj0;
               if (wv0) *w0 = __fadd_rn(*w0, __fmul_rn(nlr, g0));
@@ -738,20 +761,76 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
         // sum exactly the elements this CTA produced over all ranks in rank order, apply to the home copy.
         const unsigned epoch = sx_epoch0 + (unsigned)s + 1u;
         const int W = a.sx.world, me = a.sx.rank;
-        if (tid == 0 && W > 1) {
-          __threadfence_system();
-          for (int p = 0; p < W; ++p)
-            if (p != me) st_relaxed_sys_u32(a.sx.cta_flags[p] + me * kCtaFlagPitch + g, epoch);
-        }
         bool ok = true;
-        if (tid < W && tid != me) ok = sx_wait(a.sx.cta_flags[me] + tid * kCtaFlagPitch + g, epoch, a.sx, sx_t0);
-        ok = __syncthreads_and(ok) != 0;
+        if (!sxll) {
+          if (tid == 0 && W > 1) {
+            __threadfence_system();
+            for (int p = 0; p < W; ++p)
+              if (p != me) st_relaxed_sys_u32(a.sx.cta_flags[p] + me * kCtaFlagPitch + g, epoch);
+          }
+          if (tid < W && tid != me) ok = sx_wait(a.sx.cta_flags[me] + tid * kCtaFlagPitch + g, epoch, a.sx, sx_t0);
+          ok = __syncthreads_and(ok) != 0;
+        }
         DBG_STAMP(6);
+        // Source of rank q's copy of flat-gradient element i.  Modes: peer loads from q's exchange buffer (1), or
+        // this rank's own receive buffer, where every rank stored {value, step number} pairs (2).
+        const float* const llr = sxll ? a.sx.ll_recv[me] + 2 * ((long)(epoch & 1u) * W * (long)a.sx.grad_stride) : nullptr;
+        const float etag = __uint_as_float(epoch);
+        auto ll_pair = [&](int q, long i, bool& good) -> float {     // spins until rank q's element i of this step is here
+          const float* p = llr + 2 * ((long)q * (long)a.sx.grad_stride + i);
+          float v, t;
+          unsigned it = 0;
+          for (;;) {
+            asm volatile("ld.relaxed.sys.global.v2.f32 {%0, %1}, [%2];" : "=f"(v), "=f"(t) : "l"(p) : "memory");
+            if (__float_as_uint(t) == __float_as_uint(etag)) return v;
+            if ((++it & 0x3ff) == 0) {
+              if ((a.sx.abort_flag && dtfe::ld_acquire_sys(a.sx.abort_flag) != 0) ||
+                  (a.sx.timeout_ns && (unsigned long long)(gtime() - sx_t0) > a.sx.timeout_ns)) { good = false; return 0.f; }
+            }
+          }
+        };
         if (ok) {
           const float alpha = a.sx.alpha;
           if (slice) {
             const long base = sxOffW1 + goff + (long)k0 * H;
-            if ((H & 3) == 0 && (base & 3) == 0) {
+            if (sxll) {
+              // 16-byte loads carry two pairs; every pair is validated on its own (8-byte stores are atomic)
+              for (int f = tid; 4 * f < nW1; f += kThreads) {
+                float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+                const int nel = min(4, nW1 - 4 * f);
+                for (int q = 0; q < W; ++q) {
+                  const float* p = llr + 2 * ((long)q * (long)a.sx.grad_stride + base + 4 * f);
+                  float4 lo = make_float4(0.f, etag, 0.f, etag), hi = lo;
+                  const bool vec = nel == 4 && ((base & 1) == 0);
+                  if (vec) {
+                    unsigned it = 0;
+                    for (;;) {
+                      lo = dtfe::ld_relaxed_sys_v4(p); hi = dtfe::ld_relaxed_sys_v4(p + 4);
+                      if (__float_as_uint(lo.y) == epoch && __float_as_uint(lo.w) == epoch &&
+                          __float_as_uint(hi.y) == epoch && __float_as_uint(hi.w) == epoch) break;
+                      if ((++it & 0x3ff) == 0) {
+                        if ((a.sx.abort_flag && dtfe::ld_acquire_sys(a.sx.abort_flag) != 0) ||
+                            (a.sx.timeout_ns && (unsigned long long)(gtime() - sx_t0) > a.sx.timeout_ns)) { ok = false; break; }
+                      }
+                    }
+                  } else {
+                    lo.x = ll_pair(q, base + 4 * f, ok);
+                    if (nel > 1) lo.z = ll_pair(q, base + 4 * f + 1, ok);
+                    if (nel > 2) hi.x = ll_pair(q, base + 4 * f + 2, ok);
+                    if (nel > 3) hi.z = ll_pair(q, base + 4 * f + 3, ok);
+                  }
+                  if (!ok) break;
+                  acc.x += lo.x; acc.y += lo.z; acc.z += hi.x; acc.w += hi.z;
+                }
+                if (!ok) break;
+                float w4[4] = {acc.x, acc.y, acc.z, acc.w};
+                for (int j = 0; j < nel; ++j) {
+                  const float w = fmaf(alpha, w4[j], Ws[4 * f + j]);
+                  Ws[4 * f + j] = w;
+                  __stcg(a.W1 + (long)k0 * H + 4 * f + j, w);
+                }
+              }
+            } else if ((H & 3) == 0 && (base & 3) == 0) {
               for (int f = tid; 4 * f < nW1; f += kThreads) {
                 float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
                 for (int q0 = 0; q0 < W; q0 += 8) {
@@ -785,17 +864,21 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
               const int tt = t0 + (i / per) * tstride, c = i % per;
               const long off = goff + (c < C ? sxOffW2 + (long)tt * C + c : sxOffB1 + tt);
               float acc = 0.f;
-              for (int q = 0; q < W; ++q) acc += dtfe::ld_relaxed_sys(a.sx.grads[q] + off);
+              for (int q = 0; q < W && ok; ++q) acc += sxll ? ll_pair(q, off, ok) : dtfe::ld_relaxed_sys(a.sx.grads[q] + off);
               float* home = c < C ? a.W2 + (long)tt * C + c : a.b1 + tt;
-              __stcg(home, fmaf(alpha, acc, __ldcg(home)));
+              if (ok) __stcg(home, fmaf(alpha, acc, __ldcg(home)));
             }
             if (g == book)
               for (int c = tid; c < C; c += kThreads) {
                 float acc = 0.f;
-                for (int q = 0; q < W; ++q) acc += dtfe::ld_relaxed_sys(a.sx.grads[q] + goff + sxOffB2 + c);
-                __stcg(a.b2 + c, fmaf(alpha, acc, __ldcg(a.b2 + c)));
+                for (int q = 0; q < W && ok; ++q)
+                  acc += sxll ? ll_pair(q, goff + sxOffB2 + c, ok) : dtfe::ld_relaxed_sys(a.sx.grads[q] + goff + sxOffB2 + c);
+                if (ok) __stcg(a.b2 + c, fmaf(alpha, acc, __ldcg(a.b2 + c)));
               }
           }
+          if (sxll) ok = __syncthreads_and(ok) != 0;
+        }
+        if (ok) {
           if (g == book && tid == 0) {        // every rank counts the aggregated update in its own copy
             const int old = *reinterpret_cast<volatile int*>(a.global_step);
             *reinterpret_cast<volatile int*>(a.global_step) = old + 1;
@@ -896,7 +979,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
     unsigned prev = atomicAdd(a.sync + 1, 1u);
     if (prev == NC - 1) {
       a.sync[0] = 0; a.sync[1] = 0;
-      if (a.has_sx && a.sx.mode == 1) a.sync[2] = 0;
+      if (a.has_sx && a.sx.mode >= 1) a.sync[2] = 0;
       if (a.has_sx) {
         *a.sx.epoch = sx_epoch0 + (unsigned)steps_done;
       } else if (a.train && a.nsteps > 0) {
@@ -972,12 +1055,13 @@ static int mlp2_fill(const Mlp2Launch& L, Mlp2Args& a) {
     DTFE_REQUIRE(a.gW1 != nullptr, "mlp2_step: sync_exchange needs the four gradient buffers (they are what is exchanged)");
     DTFE_REQUIRE(a.sx.world >= 1 && a.sx.world <= 16 && a.sx.nseg >= 0 && a.sx.nseg <= 8 && a.sx.epoch && a.sx.status,
                  "mlp2_step: malformed sync_exchange");
-    DTFE_REQUIRE(a.sx.mode == 0 || a.sx.mode == 1, "mlp2_step: sync_exchange.mode must be 0 or 1");
-    if (a.sx.mode == 1) {
+    DTFE_REQUIRE(a.sx.mode >= 0 && a.sx.mode <= 2, "mlp2_step: sync_exchange.mode must be 0, 1 or 2");
+    if (a.sx.mode >= 1) {
       DTFE_REQUIRE(a.sx.rank >= 0 && a.sx.rank < a.sx.world && a.sx.grad_stride > 0,
                    "mlp2_step: all-reduce exchange needs rank < world and grad_stride");
       for (int r = 0; r < a.sx.world; ++r)
-        DTFE_REQUIRE(a.sx.grads[r] && a.sx.cta_flags[r], "mlp2_step: all-reduce exchange: rank %d's buffers are missing", r);
+        DTFE_REQUIRE(a.sx.grads[r] && (a.sx.mode == 1 ? (void*)a.sx.cta_flags[r] : (void*)a.sx.ll_recv[r]),
+                     "mlp2_step: all-reduce exchange: rank %d's buffers are missing", r);
       DTFE_REQUIRE(((uintptr_t)L.W1 % 16) == 0, "mlp2_step: all-reduce exchange needs a 16-byte aligned W1 copy");
       DTFE_REQUIRE(a.train, "mlp2_step: sync_exchange is for training launches");
     }

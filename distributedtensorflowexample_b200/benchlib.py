@@ -305,12 +305,12 @@ def _run_mnist_sync(args, rank, world, dev, ClockSampler, spec, model, store, na
     from .ops import cuda_ops as ops
     from .parallel.sync import SyncGroup
     from .train.gpu_step import FusedMlp2Stepper
-    mode = getattr(args, "sync_mode", "allreduce")
+    mode = getattr(args, "sync_mode", "allreduce_ll")
     sg = SyncGroup(store, names, rank, world, mode=mode)
     shapes = {n: tuple(store.tensor(n).shape) for n in names}
     spl = args.steps_per_launch or min(K, 500)
     R = max(1, getattr(args, "repeats", 25))
-    if mode == "allreduce":
+    if mode.startswith("allreduce"):
         sg.refresh_replicas()
         _barrier(world)
         params, gstep, remote = sg.home_params(), sg.home("global/global_step"), False
@@ -351,7 +351,7 @@ def _run_mnist_sync(args, rank, world, dev, ClockSampler, spec, model, store, na
     value = world * B * K / (ms * 1e-3)
     # replicas must still agree bit for bit (all-reduce mode): compare a checksum of this rank's copy with rank 0's
     agree = None
-    if mode == "allreduce" and world > 1:
+    if mode.startswith("allreduce") and world > 1:
         chk = torch.stack([p.double().sum() for p in params] + [gstep.double().sum()])
         ref = chk.clone()
         dist.broadcast(ref, src=0)

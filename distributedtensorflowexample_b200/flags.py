@@ -197,6 +197,8 @@ def define_framework_flags(flag_values: FlagValues = FLAGS) -> FlagValues:
     DEFINE_integer("num_ps", 1, "Number of parameter-server tasks (shards)", flag_values)
     DEFINE_boolean("sync", False, "Synchronous SGD (reduce-scatter fused with the update) instead of async", flag_values)
     DEFINE_string("optimizer", "sgd", "sgd | adam", flag_values)
+    DEFINE_string("sync_mode", "allreduce_ll", "--sync with the fused step kernel: allreduce_ll (gradient elements travel as "
+                  "{value, step} pairs into every rank's receive buffer) | allreduce (per-CTA flags + peer loads)", flag_values)
     DEFINE_string("device", "auto", "auto | cuda | cpu (cpu = gloo plumbing config)", flag_values)
     DEFINE_string("dtype", "float32", "float32 | bfloat16 parameter/compute dtype of the GPU path", flag_values)
     DEFINE_boolean("tf32", False, "Let the fp32 layer-wise engine use tcgen05 kind::tf32 GEMMs (TMA pull from the fp32 "

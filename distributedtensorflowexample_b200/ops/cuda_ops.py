@@ -316,7 +316,7 @@ class SyncExchange(ctypes.Structure):
         ("epoch", _P), ("status", _P), ("abort_flag", _P),
         ("timeout_ns", ctypes.c_ulonglong),
         ("global_step", _P),
-        ("mode", c_int), ("grad_stride", c_size_t), ("cta_flags", _P * 16),
+        ("mode", c_int), ("grad_stride", c_size_t), ("cta_flags", _P * 16), ("ll_recv", _P * 16),
     ]
 
 

@@ -9,7 +9,11 @@ loads over NVLink) and applies ``-lr/W * sum`` in place in its shard -> barrier.
 reduce-scatter fused with the update; there is no all-gather because the next forward reads the
 parameters from the owners' shards anyway (the fused pull).  One rank per GPU.
 
-``mode="allreduce"`` (fused MNIST step kernel only) is the low-latency form: every rank keeps its own copy of
+``mode="allreduce_ll"`` moves the same all-reduce over a low-latency transport: every gradient element is stored
+as an 8-byte {value, step number} pair straight into every rank's receive buffer by the thread that computed it, and
+consumers spin on their local buffer - no fence, no flag, no NVLink round trip on the critical path.
+
+``mode="allreduce"`` (fused MNIST step kernel only) is the flag-based form: every rank keeps its own copy of
 the parameters ("home": the shard itself where the rank owns the variable, a private replica elsewhere), each
 CTA of the step kernel exchanges per-CTA flags with the same CTA of the other ranks, sums all ranks' gradients
 for the elements it produced and applies them to its home copy - no grid barrier, no second flag round, no
@@ -32,7 +36,7 @@ class SyncGroup:
                  mode: str = "reduce_scatter"):
         """``exchange(blob) -> [blob of rank 0, ..., blob of rank W-1]``; default: torch.distributed
         all_gather_object (SPMD).  Launcher-mode workers pass a TCPStore-based exchange."""
-        if mode not in ("reduce_scatter", "allreduce"):
+        if mode not in ("reduce_scatter", "allreduce", "allreduce_ll"):
             raise ValueError(mode)
         self.mode = mode
         self.store, self.rank, self.world = store, rank, world
@@ -48,18 +52,23 @@ class SyncGroup:
         self.total = n
         max_ranks = ops.lib().dtfe_sync_max_ranks()
         copies = 2 if mode == "allreduce" else 1       # all-reduce mode alternates between two gradient copies
+        self._ll_ptr = 0
         self.CTA_FLAG_PITCH = 160
         with torch.cuda.device(self.device):
             self._grad_ptr = ops.shard_alloc(copies * max(self.total, 4) * 4)
             self._flag_ptr = ops.shard_alloc(2 * max_ranks * 4)
             self._cta_flag_ptr = ops.shard_alloc(max_ranks * self.CTA_FLAG_PITCH * 4) if mode == "allreduce" else 0
+            if mode == "allreduce_ll":
+                # receive buffer of the low-latency transport: [2 copies][world sources][total] {value, step} pairs
+                self._ll_ptr = ops.shard_alloc(2 * world * max(self.total, 4) * 8)
         self.gradbuf = ops.tensor_from_ptr(self._grad_ptr, (copies * max(self.total, 4),), torch.float32, self.device,
                                            owner=self)
         self.local_sync = torch.zeros(4, dtype=torch.int32, device=self.device)
         self.epoch = 0
         # exchange IPC handles
         mine = (ops.ipc_export(self._grad_ptr), ops.ipc_export(self._flag_ptr),
-                ops.ipc_export(self._cta_flag_ptr) if self._cta_flag_ptr else None)
+                ops.ipc_export(self._cta_flag_ptr) if self._cta_flag_ptr else None,
+                ops.ipc_export(self._ll_ptr) if self._ll_ptr else None)
         self._opened: List[int] = []
         self.timeout_s = timeout_s
         # workers leaving (signal, crash handler) raise the stop word of shard 0; spinning peers see it
@@ -71,12 +80,12 @@ class SyncGroup:
                 dist.all_gather_object(allh, mine)
             else:
                 allh = exchange(mine)
-            self.grad_ptrs, self.flag_ptrs, self.cta_flag_ptrs = [], [], []
+            self.grad_ptrs, self.flag_ptrs, self.cta_flag_ptrs, self.ll_ptrs = [], [], [], []
             with torch.cuda.device(self.device):
-                for r, (gh, fh, ch) in enumerate(allh):
+                for r, (gh, fh, ch, lh) in enumerate(allh):
                     if r == rank:
                         self.grad_ptrs.append(self._grad_ptr); self.flag_ptrs.append(self._flag_ptr)
-                        self.cta_flag_ptrs.append(self._cta_flag_ptr)
+                        self.cta_flag_ptrs.append(self._cta_flag_ptr); self.ll_ptrs.append(self._ll_ptr)
                     else:
                         g, f = ops.ipc_open(gh), ops.ipc_open(fh)
                         self._opened += [g, f]
@@ -85,10 +94,15 @@ class SyncGroup:
                             c = ops.ipc_open(ch)
                             self._opened.append(c)
                             self.cta_flag_ptrs.append(c)
+                        if lh is not None:
+                            c = ops.ipc_open(lh)
+                            self._opened.append(c)
+                            self.ll_ptrs.append(c)
             if exchange is None:
                 dist.barrier()
         else:
             self.grad_ptrs, self.flag_ptrs, self.cta_flag_ptrs = [self._grad_ptr], [self._flag_ptr], [self._cta_flag_ptr]
+            self.ll_ptrs = [self._ll_ptr]
         # segments this rank owns
         self.segments = []
         for name in self.names:
@@ -99,7 +113,7 @@ class SyncGroup:
         self.global_step = store.tensor("global/global_step") if gs_owner == rank else None
         # all-reduce mode: this rank's own copy of every variable - the shard where it owns it, a replica elsewhere
         self._home: Dict[str, torch.Tensor] = {}
-        if mode == "allreduce":
+        if mode in ("allreduce", "allreduce_ll"):
             for name in self.names + ["global/global_step"]:
                 t = store.tensor(name)
                 mine_ = owner_of_shard(store.shard_of(name), world) == rank
@@ -160,6 +174,10 @@ class SyncGroup:
             x.mode, x.grad_stride = 1, max(self.total, 4)
             for r in range(self.world):
                 x.cta_flags[r] = self.cta_flag_ptrs[r]
+        elif self.mode == "allreduce_ll":
+            x.mode, x.grad_stride = 2, max(self.total, 4)
+            for r in range(self.world):
+                x.ll_recv[r] = self.ll_ptrs[r]
         self._xs = x                                       # keep the ctypes object alive
         return x
 

@@ -166,7 +166,7 @@ class Worker:
                               and FusedMlp2Stepper.supports(self.spec, f.batch_size))
                 self.sync_group = SyncGroup(store, names, me, W, exchange=exchange,
                                             timeout_s=f.sync_timeout_secs + 2.0 * f.recovery_wait_secs,
-                                            mode="allreduce" if fused_sync else "reduce_scatter")
+                                            mode=f.sync_mode if fused_sync else "reduce_scatter")
                 kw["grad_buffers"] = self.sync_group.grad_views({n: tuple(store.tensor(n).shape) for n in names})
             else:
                 kw["adam"] = dict(slots=[store.tensor(n + "/grad_slot") for n in names],

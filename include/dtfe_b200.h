@@ -139,9 +139,16 @@ typedef struct dtfe_sync_exchange {
    * loads.  The exchange buffers hold two copies of the flat gradient, grad_stride floats apart, used by
    * alternate steps, which makes a second barrier per step unnecessary.  seg_* and global_step above are
    * ignored. */
-  int mode;                   /* 0: reduce-scatter by the owners (default), 1: all-reduce with apply */
-  size_t grad_stride;         /* mode 1: floats between the two copies of the flat gradient */
+  /* mode 2 - the same all-reduce with the apply, low-latency transport: a gradient element travels as the
+   * 8-byte pair {value, step number}, stored by the producing thread straight into EVERY rank's receive buffer
+   * (ll_recv[p], peer memory) as soon as it is computed.  The pair is the message and its own arrival flag:
+   * no fence, no flag store, no round trip - a consumer spins on its LOCAL buffer until the step number of
+   * every rank's pair matches.  Receive buffer of a rank: [2 alternating copies][world sources][grad_stride]
+   * pairs = 2 * world * grad_stride * 8 bytes, zeroed once, from dtfe_shard_alloc.  cta_flags is unused. */
+  int mode;                   /* 0: reduce-scatter by the owners (default), 1: all-reduce with apply, 2: the same, low latency */
+  size_t grad_stride;         /* modes 1, 2: floats between the two copies of the flat gradient */
   unsigned* cta_flags[16];    /* mode 1: every rank's per-CTA arrival words, [16 ranks][160 CTAs] u32 */
+  float* ll_recv[16];         /* mode 2: every rank's receive buffer */
 } dtfe_sync_exchange;
 
 /* ---- the whole reference training step in one cooperative kernel ------------------------------- */

@@ -85,32 +85,36 @@ def main():
     sg.close()
     # the all-reduce form (what --sync runs now): every rank trains on its own copy, per-CTA flag exchange,
     # every rank sums all ranks' gradients in rank order -> all copies bit-identical and equal to the oracle
-    sa = SyncGroup(store, names, rank, world, mode="allreduce")
-    sa.refresh_replicas()
-    dist.barrier()
-    fa = FusedMlp2Stepper(spec, B, sa.home_params(), sa.home("global/global_step"), lr, dev,
-                          max_steps_per_launch=nsteps, remote=False, grad_buffers=sa.grad_views(shapes))
-    fa.sync_exchange = sa.exchange_struct(lr)
-    fa.cursor = torch.full((1,), 3 * nsteps, dtype=torch.int32, device=dev)
-    na = 2                                                # 4000 rows = 20 synchronous steps of 2 x 100: 15 are used up
-    fa.run(X, Y, nsteps=na, batch_idx=order)
-    fa.run(X, Y, nsteps=na, batch_idx=order)              # a second launch continues from the first one's copies
-    torch.cuda.synchronize(); dist.barrier()
-    assert sa.aborted() == 0
-    for s in range(3 * nsteps, 3 * nsteps + 2 * na):
-        rows = slice(s * world * B, (s + 1) * world * B)
-        oracle.sgd_step(ref, x[rows].astype(np.float64), y[rows].astype(np.int64), lr)
-    mine = [p.detach().clone() for p in sa.home_params()]
-    for n, r, m in zip(names, ref, mine):
-        np.testing.assert_allclose(m.cpu().numpy(), r, rtol=1e-3, atol=6e-4, err_msg=f"sync all-reduce {n}")
-        np.testing.assert_allclose(store.read(n), r, rtol=1e-3, atol=6e-4, err_msg=f"sync all-reduce shard {n}")
-        other = m.clone()
-        dist.broadcast(other, src=0)
-        assert torch.equal(other, m), f"replica of {n} on rank {rank} differs from rank 0's"
-    assert sa.home("global/global_step").item() == 3 * nsteps + 2 * na == store.read("global/global_step").item()
-    assert fa.step[:na].cpu().tolist() == list(range(3 * nsteps + na, 3 * nsteps + 2 * na))
-    dist.barrier()
-    sa.close(); store.close()
+    step0 = 3 * nsteps
+    for mode in ("allreduce", "allreduce_ll"):
+        sa = SyncGroup(store, names, rank, world, mode=mode)
+        sa.refresh_replicas()
+        dist.barrier()
+        fa = FusedMlp2Stepper(spec, B, sa.home_params(), sa.home("global/global_step"), lr, dev,
+                              max_steps_per_launch=nsteps, remote=False, grad_buffers=sa.grad_views(shapes))
+        fa.sync_exchange = sa.exchange_struct(lr)
+        fa.cursor = torch.full((1,), step0, dtype=torch.int32, device=dev)
+        na = 1                                            # 4000 rows = 20 synchronous steps of 2 x 100: 15 are used up
+        fa.run(X, Y, nsteps=na, batch_idx=order)
+        fa.run(X, Y, nsteps=na, batch_idx=order)          # a second launch continues from the first one's copies
+        torch.cuda.synchronize(); dist.barrier()
+        assert sa.aborted() == 0
+        for s in range(step0, step0 + 2 * na):
+            rows = slice(s * world * B, (s + 1) * world * B)
+            oracle.sgd_step(ref, x[rows].astype(np.float64), y[rows].astype(np.int64), lr)
+        mine = [p.detach().clone() for p in sa.home_params()]
+        for n, r, m in zip(names, ref, mine):
+            np.testing.assert_allclose(m.cpu().numpy(), r, rtol=1e-3, atol=6e-4, err_msg=f"sync {mode} {n}")
+            np.testing.assert_allclose(store.read(n), r, rtol=1e-3, atol=6e-4, err_msg=f"sync {mode} shard {n}")
+            other = m.clone()
+            dist.broadcast(other, src=0)
+            assert torch.equal(other, m), f"{mode}: replica of {n} on rank {rank} differs from rank 0's"
+        step0 += 2 * na
+        assert sa.home("global/global_step").item() == step0 == store.read("global/global_step").item()
+        assert fa.step[:na].cpu().tolist() == [step0 - 1]
+        dist.barrier()
+        sa.close()
+    store.close()
 
     # ---------------- async: conservation of pushed deltas with exact arithmetic ---------------
     model, store = build_spmd_store(spec, rank, world, dev, seed=4)

@@ -150,3 +150,32 @@ def test_sync_rs_apply_single_rank():
                       [(param, 0, n)], -0.1, 1, torch.zeros(4, device="cuda", dtype=torch.int32), None, timeout_s=0.05)
     torch.cuda.synchronize()
     assert torch.equal(param, before)
+
+
+def test_contended_push_lossless_vs_unlocked():
+    """Two streams push into the same shard at the same time (what two workers sharing a ps do).  The default
+    push (red.add, performed by the L2 that owns the address) must conserve every update exactly - the values are
+    powers of two, so fp32 addition is exact in any order.  --unlocked_apply (TF1 use_locking=False: load, add,
+    store) may lose updates under contention and must never invent any; the fraction lost is printed."""
+    from distributedtensorflowexample_b200.ops import cuda_ops as ops
+    n, reps = 1 << 20, 200
+    s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+    g1 = torch.full((n,), 0.25, device="cuda"); g2 = torch.full((n,), 0.5, device="cuda")
+    expect = -reps * (0.25 + 0.5)
+    lost = {}
+    for atomic in (True, False):
+        shard = torch.zeros(n, device="cuda")
+        torch.cuda.synchronize()
+        for s, g in ((s1, g1), (s2, g2)):
+            with torch.cuda.stream(s):
+                for _ in range(reps):
+                    ops.push_sgd(shard, g, -1.0, atomic=atomic)
+        torch.cuda.synchronize()
+        got = shard.cpu().numpy()
+        if atomic:
+            assert np.all(got == expect), (got.min(), got.max(), expect)
+        else:
+            assert np.all(got <= 0) and np.all(got >= expect)           # nothing invented ...
+            assert np.all(np.abs(np.round(got * 4) - got * 4) < 1e-6)   # ... every value is a sum of whole updates
+            lost[atomic] = float(1.0 - got.sum() / (expect * n))
+    print(f"unlocked apply under contention lost {100 * lost[False]:.2f} % of the updates; red.add lost none")

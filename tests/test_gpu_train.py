@@ -373,8 +373,9 @@ def test_fused_step_with_in_kernel_sync_exchange_single_rank():
     sg.close(); store.close()
 
 
+@pytest.mark.parametrize("mode", ["allreduce", "allreduce_ll"])
 @pytest.mark.parametrize("dims,B", [((784, 100, 10), 100), ((50, 30, 7), 37)])
-def test_fused_step_allreduce_exchange_single_rank(dims, B):
+def test_fused_step_allreduce_exchange_single_rank(dims, B, mode):
     """The all-reduce form of the in-kernel exchange with world = 1: per-CTA flags, alternating gradient copies,
     W1 slice resident in shared memory across steps and launches, apply to the home copy, local step counter.
     Must equal plain SGD over two launches (the second starts from what the first wrote back)."""
@@ -388,7 +389,7 @@ def test_fused_step_allreduce_exchange_single_rank(dims, B):
     y = y.astype(np.int32)
     X = torch.tensor(x, device="cuda"); Y = torch.tensor(y, device="cuda")
     lr, nsteps = 0.05, 4
-    sg = SyncGroup(store, names, 0, 1, timeout_s=5.0, mode="allreduce")
+    sg = SyncGroup(store, names, 0, 1, timeout_s=5.0, mode=mode)
     sg.refresh_replicas()
     shapes = {n: tuple(store.tensor(n).shape) for n in names}
     st = FusedMlp2Stepper(spec, B, sg.home_params(), sg.home("global/global_step"), lr, "cuda:0",
