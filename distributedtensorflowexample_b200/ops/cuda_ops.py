@@ -46,6 +46,10 @@ _SIGS = {
                                 POINTER(c_size_t), c_float, c_uint, _P, _P, _P, ctypes.c_double, _P], c_int),
     "dtfe_sync_max_ranks": ([], c_int),
     "dtfe_gather_rows_f32": ([_P, c_long, _P, _P, _P, c_int, c_int, _P, _P, _P], c_int),
+    "dtfe_thin_fwd_bf16": ([_P, c_long, _P, c_long, _P, _P, c_long, c_int, c_int, c_int, _P], c_int),
+    "dtfe_thin_dx_bf16": ([_P, c_long, _P, c_long, _P, c_long, _P, c_long, c_int, c_int, c_int, _P], c_int),
+    "dtfe_thin_dw_scratch_words": ([c_int, c_int], c_size_t),
+    "dtfe_thin_dw_push_bf16": ([_P, c_long, _P, c_long, _P, c_long, c_float, c_int, c_int, c_int, _P, _P], c_int),
     "dtfe_mlp2_step_grid": ([c_int, c_int], c_int),
     "dtfe_mlp2_step_ctas": ([c_int, c_int, c_int, c_int], c_int),
     "dtfe_mlp2_step_workspace_words": ([c_int, c_int, c_int, c_int, c_int], c_size_t),
@@ -244,6 +248,43 @@ def bias_grad_push_bf16(dY, b, alpha: float, grad_out=None):
     check(lib().dtfe_bias_grad_push_bf16(dY.data_ptr(), dY.stride(0), M, N, _ptr(b),
                                          int(b is not None and b.dtype == torch.bfloat16), _ptr(grad_out), alpha,
                                          _stream()), "dtfe_bias_grad_push_bf16")
+
+
+# --------------------------------------------------------------------------------------
+# thin bf16 layer (output width <= 16): streaming kernels instead of 128-wide tensor-core tiles
+# --------------------------------------------------------------------------------------
+def thin_ok(act: torch.Tensor, W: torch.Tensor) -> bool:
+    return (isinstance(W, torch.Tensor) and W.dim() == 2 and W.shape[1] <= 16 and W.dtype == torch.bfloat16
+            and act.dtype == torch.bfloat16 and act.shape[1] % 8 == 0 and act.stride(0) % 8 == 0 and W.stride(0) % 8 == 0
+            and (W.shape[1] <= 8 or W.stride(0) >= 16) and act.data_ptr() % 16 == 0 and W.data_ptr() % 16 == 0)
+
+
+def thin_fwd(act, W, bias, out):
+    """out[M,C] (fp32) = act[M,K] @ W[K,C] + bias - reference worker.py:53 for an output layer of width <= 16."""
+    M, K = act.shape
+    check(lib().dtfe_thin_fwd_bf16(act.data_ptr(), act.stride(0), W.data_ptr(), W.stride(0), _ptr(bias), out.data_ptr(),
+                                   out.stride(0), M, K, W.shape[1], _stream()), "dtfe_thin_fwd_bf16")
+    return out
+
+
+def thin_dx(dZ, W, Hact, out):
+    """out[M,K] (bf16) = (dZ[M,C] @ W[K,C]^T) * Hact*(1-Hact)."""
+    M, K = Hact.shape
+    check(lib().dtfe_thin_dx_bf16(dZ.data_ptr(), dZ.stride(0), W.data_ptr(), W.stride(0), Hact.data_ptr(), Hact.stride(0),
+                                  out.data_ptr(), out.stride(0), M, K, W.shape[1], _stream()), "dtfe_thin_dx_bf16")
+    return out
+
+
+def thin_dw_scratch(M: int, K: int, device) -> torch.Tensor:
+    return torch.zeros(lib().dtfe_thin_dw_scratch_words(M, K), dtype=torch.float32, device=device)
+
+
+def thin_dw_push(act, dZ, Wshard, alpha: float, scratch):
+    """Wshard[K,C] += alpha * act[M,K]^T @ dZ[M,C] (one rounded red.add per element into the bf16 shard)."""
+    M, K = act.shape
+    check(lib().dtfe_thin_dw_push_bf16(act.data_ptr(), act.stride(0), dZ.data_ptr(), dZ.stride(0), Wshard.data_ptr(),
+                                       Wshard.stride(0), alpha, M, K, Wshard.shape[1], scratch.data_ptr(), _stream()),
+          "dtfe_thin_dw_push_bf16")
 
 
 def mean_loss_acc(rowloss, rowcorrect, M: int, out_loss=None, out_acc=None, out_count=None):

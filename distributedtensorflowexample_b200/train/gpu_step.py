@@ -290,6 +290,9 @@ class TcStepper:
         self.step = torch.zeros(1, device=dev, dtype=torch.int32)
         L = spec.num_layers
         self.launches_per_call = L + 2 + (L - 1) + 2 * L + 1
+        import os
+        self.thin = os.environ.get("DTFE_NO_THIN") != "1"      # streaming kernels for an output layer of width <= 16
+        self._thin_scratch = None
 
     def pull_partitioned(self) -> None:
         """Issue this step's pulls on side streams, one event per variable: the copy of layer l+1's weights over
@@ -362,7 +365,10 @@ class TcStepper:
             W, b = self._w(2 * l), self._w(2 * l + 1)
             last = l == L - 1
             out = logits if last else acts[l]
-            self.G.dense_fwd_tc(h, W, b, ops.ACT_NONE if last else ops.ACT_SIGMOID, out, tile_n=self.tile_n)
+            if last and self.thin and ops.thin_ok(h, W):
+                ops.thin_fwd(h, W, b, out)             # output layer of width <= 16: streaming kernel, not 128-wide tiles
+            else:
+                self.G.dense_fwd_tc(h, W, b, ops.ACT_NONE if last else ops.ACT_SIGMOID, out, tile_n=self.tile_n)
             h = out
         return logits
 
@@ -380,9 +386,18 @@ class TcStepper:
             W, b = self.params[2 * l], self.params[2 * l + 1]
             h_in = X if l == 0 else self.acts[l - 1]
             d_prev = None
+            thin = l == L - 1 and l > 0 and self.thin and ops.thin_ok(h_in, W)
             if l > 0:   # against the pre-update weights, so before this layer's push
-                d_prev = self.G.dense_bwd_dx_tc(d, self._w(2 * l), h_in, self.dacts[l - 1], tile_n=self.tile_n)
-            self.G.dense_bwd_dw_push_tc(h_in, d, W, alpha, tile_n=self.tile_n, tma_push=self.stage_all)
+                if thin:
+                    d_prev = ops.thin_dx(d, self._w(2 * l), h_in, self.dacts[l - 1])
+                else:
+                    d_prev = self.G.dense_bwd_dx_tc(d, self._w(2 * l), h_in, self.dacts[l - 1], tile_n=self.tile_n)
+            if thin:
+                if self._thin_scratch is None:
+                    self._thin_scratch = ops.thin_dw_scratch(h_in.shape[0], h_in.shape[1], h_in.device)
+                ops.thin_dw_push(h_in, d, W, alpha, self._thin_scratch)
+            else:
+                self.G.dense_bwd_dw_push_tc(h_in, d, W, alpha, tile_n=self.tile_n, tma_push=self.stage_all)
             ops.bias_grad_push_bf16(d, b, alpha)
             d = d_prev
         ops.global_step_add(self.global_step, 1, self.step)

@@ -178,6 +178,20 @@ int dtfe_mlp2_step_ctas(int B, int D, int H, int ks);  /* CTAs per launch on the
 size_t dtfe_mlp2_step_workspace_words(int B, int D, int H, int C, int ks);
 int dtfe_mlp2_step(const dtfe_mlp2_launch* launch, void* stream);
 
+/* ---- thin bf16 layer (output width C <= 16, e.g. 8192 -> 10 logits) ------------------------------------------
+ * Three streaming kernels for a layer whose products would waste >= 87 % of a 128-wide tensor-core tile:
+ * forward logits = act.W + b (reference worker.py:53), input gradient dX = (dZ.W^T) * H(1-H) (worker.py:72-73),
+ * and the weight gradient pushed into the shard, W += alpha * act^T.dZ (worker.py:75-79; partial sums of the row
+ * chunks meet in `scratch`, the last CTA per column block pushes once per element).  bf16 matrices with 16-byte
+ * aligned rows, K % 8 == 0; W is [K][ldw] with ldw >= 16 when C > 8. */
+int dtfe_thin_fwd_bf16(const void* act, long lda, const void* W, long ldw, const void* bias_or_null, float* out, long ldo,
+                       int M, int K, int C, void* stream);
+int dtfe_thin_dx_bf16(const void* dZ, long lddz, const void* W, long ldw, const void* Hact, long ldh, void* dX, long lddx,
+                      int M, int K, int C, void* stream);
+size_t dtfe_thin_dw_scratch_words(int M, int K);      /* 4-byte words, zeroed once */
+int dtfe_thin_dw_push_bf16(const void* act, long lda, const void* dZ, long lddz, void* Wshard, long ldw, float alpha, int M,
+                           int K, int C, float* scratch, void* stream);
+
 /* dtfe_mlp2_step on the tensor cores (same launch struct, workspace and results): X.W1 and X^T.dA run as
  * tcgen05.mma kind::tf32 with fp32 accumulators in TMEM on one cluster of 8 CTAs; CTA i owns a slice of the
  * features, pulls its slice of W1 from the shard with TMA (one step ahead, own update added in shared memory)

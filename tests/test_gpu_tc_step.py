@@ -50,3 +50,37 @@ def test_tc_step_matches_oracle(dims, B, partition):
         # bf16 storage rounds the updated weight (<= 2^-8 relative) and the GEMM inputs are bf16
         assert upd_err <= 2 ** -7 * np.abs(want).max() + 0.05 * np.abs(lr * g).max() + 1e-4, (n, upd_err)
     store.close()
+
+
+@pytest.mark.parametrize("M,K,C", [(300, 1024, 10), (64, 256, 7), (4096, 2048, 16), (33, 8, 1)])
+def test_thin_layer_kernels_match_fp32(M, K, C):
+    """The streaming kernels of an output layer of width <= 16 against plain fp32 torch on the same bf16 values."""
+    from distributedtensorflowexample_b200.ops import cuda_ops as ops
+    g = torch.Generator(device="cuda").manual_seed(M + K + C)
+    pitch = 16 if C > 8 else 8
+    act = torch.rand(M, K, device="cuda", generator=g).bfloat16()
+    Wp = torch.zeros(K, pitch, device="cuda", dtype=torch.bfloat16)
+    Wp[:, :C] = (torch.randn(K, C, device="cuda", generator=g) * 0.05).bfloat16()
+    W = Wp[:, :C]
+    bias = torch.randn(C, device="cuda", generator=g).bfloat16()
+    dZp = torch.zeros(M, pitch, device="cuda", dtype=torch.bfloat16)
+    dZp[:, :C] = (torch.randn(M, C, device="cuda", generator=g) / M).bfloat16()
+    dZ = dZp[:, :C]
+    assert ops.thin_ok(act, W)
+    out = torch.empty(M, pitch, device="cuda")[:, :C]
+    ops.thin_fwd(act, W, bias, out)
+    ref = act.float() @ W.float() + bias.float()
+    torch.testing.assert_close(out, ref, rtol=1e-4, atol=1e-3)
+    dX = torch.empty(M, K, device="cuda", dtype=torch.bfloat16)
+    ops.thin_dx(dZ, W, act, dX)
+    ref = (dZ.float() @ W.float().t()) * act.float() * (1 - act.float())
+    torch.testing.assert_close(dX.float(), ref, rtol=2e-2, atol=float(ref.abs().max()) * 2 ** -7)
+    scratch = ops.thin_dw_scratch(M, K, "cuda")
+    before = Wp.clone()
+    for rep in range(2):          # twice: the kernel must leave its counters ready for the next launch
+        ops.thin_dw_push(act, dZ, W, -0.5, scratch)
+    torch.cuda.synchronize()
+    upd = -0.5 * (act.float().t() @ dZ.float())
+    got = (Wp.float() - before.float())[:, :C]
+    assert (got - 2 * upd).abs().max() <= 2 ** -6 * before.float().abs().max() + 0.03 * upd.abs().max() + 1e-6
+    assert torch.equal(Wp[:, C:], before[:, C:])          # pad columns untouched (adding zero)
