@@ -291,7 +291,9 @@ class TcStepper:
         L = spec.num_layers
         self.launches_per_call = L + 2 + (L - 1) + 2 * L + 1
         import os
-        self.thin = os.environ.get("DTFE_NO_THIN") != "1"      # streaming kernels for an output layer of width <= 16
+        # streaming kernels for an output layer of width <= 16 (ops.thin_*): correct, but at 84 / 78 / 94 us they do
+        # not yet beat the 128-wide tensor-core tiles (57 / 70 / 46 us for 4096x8192x10), so they are opt-in
+        self.thin = os.environ.get("DTFE_THIN") == "1"
         self._thin_scratch = None
 
     def pull_partitioned(self) -> None:
