@@ -72,6 +72,8 @@ struct Mlp2Args {
   int ahead;                // pull one step ahead + own deltas (see the file header)
   int remote;               // some shard lives on a peer GPU: completion fence must be .sys
   long long* dbg;           // optional [nsteps][grid][16] globaltimer stamps (profiling)
+  int poison;               // debugging aid (DTFE_MLP2_POISON=1): scratch is overwritten with NaN as soon as its last
+                            // legitimate reader is done, so a read that races with the next producer shows up as NaN
   float *gW1, *gb1, *gW2, *gb2;  // sync mode: raw gradients are stored here instead of being pushed
   int* cursor;              // optional device-side step cursor: batches start at *cursor (graph replay)
   // In-kernel synchronous exchange (phase D): reduce-scatter of all ranks' gradient buffers + apply,
@@ -362,6 +364,16 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
     DBG_STAMP(1);
     grid_barrier(a.sync, bar_target, NC);
     DBG_STAMP(2);
+    if (a.poison && s > 0) {                 // phase C of the previous step (the only reader of these rows) is over
+      for (int r = g; r < B; r += (int)NC) {
+        for (int i = tid; i < H; i += kThreads) {
+          __stcg(a.Hbuf + (long)r * H + i, __int_as_float(0x7fc00000));
+          __stcg(a.dA + (long)r * H + i, __int_as_float(0x7fc00000));
+        }
+        if (tid < C) __stcg(a.dZ + (long)r * C + tid, __int_as_float(0x7fc00000));
+        if (tid == 0) __stcg(a.rowloss + r, __int_as_float(0x7fc00000));
+      }
+    }
     if (sx1) {
       // a CTA that gave up on its peers in the previous step said so before arriving here: stop, all CTAs alike
       unsigned v;
@@ -579,6 +591,10 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
     DBG_STAMP(3);
     grid_barrier(a.sync, bar_target, NC);
     DBG_STAMP(4);
+    if (a.poison && slice) {                 // every reader of this CTA's split-K partial is behind the barrier
+      float* P = a.part + (long)g * B * H;
+      for (int i = tid; i < B * H; i += kThreads) __stcg(P + i, __int_as_float(0x7fc00000));
+    }
 
     // ------------------------------ phase C ------------------------------------
     if (g == book && warp == 7) {
@@ -1072,6 +1088,8 @@ static int mlp2_fill(const Mlp2Launch& L, Mlp2Args& a) {
   static const bool ahead_off = getenv("DTFE_MLP2_NO_AHEAD") != nullptr;
   const bool aligned16 = (((uintptr_t)L.W1 | (uintptr_t)L.W2 | (uintptr_t)L.b1 | (uintptr_t)L.b2) % 16) == 0;
   a.ahead = (!ahead_off && a.train && !a.gW1 && aligned16) ? 1 : 0;
+  const char* poison = getenv("DTFE_MLP2_POISON");     // read per call: tests switch it on and off
+  a.poison = (poison && poison[0] == '1') ? 1 : 0;
   return 0;
 }
 

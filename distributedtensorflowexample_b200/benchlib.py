@@ -106,7 +106,9 @@ def measure_entrypoint(num_workers: int, num_gpus: int, training_steps: int, bat
                     "per-step summaries written) + --data synthetic --training_steps"}
     if speeds:
         gsps = _median(speeds)
-        out.update({"global_steps_per_sec": gsps, "value": gsps * batch, "unit": "examples/sec",
+        # asynchronous: one global step = one worker's batch; synchronous: one aggregated update of every worker's batch
+        per_step = batch * (num_workers if sync else 1)
+        out.update({"global_steps_per_sec": gsps, "value": gsps * per_step, "unit": "examples/sec",
                     "last_cost": costs[-1] if costs else None})
     else:
         tail = {n: ls[-5:] for n, ls in cl.lines.items()}

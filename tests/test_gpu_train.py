@@ -410,6 +410,44 @@ def test_fused_step_allreduce_exchange_single_rank(dims, B, mode):
     sg.close(); store.close()
 
 
+def test_scratch_poisoning_changes_nothing(monkeypatch):
+    """Race self-check of the fused step kernel (compute-sanitizer is closed on this pool): with DTFE_MLP2_POISON=1
+    every scratch region - split-K partials, H, dA, dZ, row losses - is overwritten with NaN the moment its last
+    legitimate reader is done.  A read that is not ordered after its producer (or before the next one) would pick
+    up a NaN; results must stay bit-identical to the unpoisoned run, asynchronous and synchronous."""
+    from distributedtensorflowexample_b200.parallel.sync import SyncGroup
+    from distributedtensorflowexample_b200.train.gpu_step import FusedMlp2Stepper
+    spec = reference_mlp_spec()
+    x, y = _data(3000)
+    X = torch.tensor(x, device="cuda"); Y = torch.tensor(y, device="cuda")
+    idx = torch.tensor(np.random.default_rng(2).integers(0, 3000, size=40 * 100).astype(np.int32), device="cuda")
+    for sync in (False, True):
+        outs = []
+        for poison in ("0", "1"):
+            monkeypatch.setenv("DTFE_MLP2_POISON", poison)
+            model, store, names = _store(spec, num_ps=2, seed=17)
+            if sync:
+                sg = SyncGroup(store, names, 0, 1, timeout_s=5.0, mode="allreduce_ll"); sg.refresh_replicas()
+                st = FusedMlp2Stepper(spec, 100, sg.home_params(), sg.home("global/global_step"), 0.05, "cuda:0",
+                                      max_steps_per_launch=20, remote=False,
+                                      grad_buffers=sg.grad_views({n: tuple(store.tensor(n).shape) for n in names}))
+                st.sync_exchange = sg.exchange_struct(0.05)
+            else:
+                st = FusedMlp2Stepper(spec, 100, [store.tensor(n) for n in names], store.tensor("global/global_step"),
+                                      0.05, "cuda:0", max_steps_per_launch=20)
+            losses = []
+            for k in range(2):
+                st.run(X, Y, nsteps=20, batch_idx=idx[k * 2000:(k + 1) * 2000])
+                losses += st.loss[:20].cpu().tolist()
+            torch.cuda.synchronize()
+            outs.append((losses, [store.read(n) for n in names]))
+            store.close()
+        assert np.isfinite(outs[1][0]).all()
+        assert outs[0][0] == outs[1][0]
+        for a, b in zip(outs[0][1], outs[1][1]):
+            assert np.array_equal(a, b)
+
+
 def test_tracer_device_spans_time_the_step_kernel():
     """utils.tracing on a GPU: a device span is a CUDA-event pair on the launching stream (plus an NVTX range
     for the host span); its duration must be the kernel's, not the host call's."""
