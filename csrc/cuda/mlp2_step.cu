@@ -160,7 +160,11 @@ __device__ __forceinline__ bool sx_wait(const unsigned* flag, unsigned epoch, co
   return true;
 }
 
-template <int KS>
+// FULL = false is the lean instantiation for plain asynchronous training and evaluation: no gradient buffers, no
+// synchronous exchange (phase D), no debugging aids.  Keeping that code out of the headline path is worth 0.9 us per
+// step (12.99 -> 12.11 us measured on one B200; an attempt to poll all ranks' pairs at once inside phase D had cost
+// the asynchronous path 2.4 us through register pressure alone, which is what prompted the split).
+template <int KS, bool FULL>
 __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
   static_assert(KS % 4 == 0 && KS <= 16, "KS must be 4, 8, 12 or 16");
   extern __shared__ __align__(16) float smem[];
@@ -268,8 +272,8 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
   };
   // Synchronous all-reduce mode: the parameters this kernel is given are this rank's own copies; the W1 slice
   // stays in shared memory for the whole launch and is updated in place in phase D.
-  const bool sx1 = a.has_sx && a.sx.mode >= 1;      // all-reduce forms: flags + peer loads (1) or low-latency pairs (2)
-  const bool sxll = a.has_sx && a.sx.mode == 2;
+  const bool sx1 = (FULL && a.has_sx) && a.sx.mode >= 1;      // all-reduce forms: flags + peer loads (1) or low-latency pairs (2)
+  const bool sxll = (FULL && a.has_sx) && a.sx.mode == 2;
   if (ahead || sx1) {
     dtfe::cta_copy_async(Ws, a.W1 + (long)k0 * H, nW1, tid, kThreads);
     dtfe::cp_async_commit();
@@ -280,7 +284,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
   const long sxOffW1 = sx1 ? (long)(a.gW1 - a.sx.grads[a.sx.rank]) : 0, sxOffB1 = sx1 ? (long)(a.gb1 - a.sx.grads[a.sx.rank]) : 0;
   const long sxOffW2 = sx1 ? (long)(a.gW2 - a.sx.grads[a.sx.rank]) : 0, sxOffB2 = sx1 ? (long)(a.gb2 - a.sx.grads[a.sx.rank]) : 0;
   int pending_step = 0;                                 // book CTA / thread 0: global step observed for the previous step
-  const unsigned sx_epoch0 = a.has_sx ? *reinterpret_cast<volatile unsigned*>(a.sx.epoch) : 0u;
+  const unsigned sx_epoch0 = (FULL && a.has_sx) ? *reinterpret_cast<volatile unsigned*>(a.sx.epoch) : 0u;
   const unsigned long long sx_t0 = gtime();
   __shared__ unsigned s_go;
   int steps_done = 0;
@@ -297,10 +301,10 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
     int ylab = 0;
     // all-reduce mode alternates between two copies of the gradient buffer (see phase D)
     const long goff = (sx1 && !sxll) ? (long)((sx_epoch0 + (unsigned)s + 1u) & 1u) * (long)a.sx.grad_stride : 0;
-    float* const gW1 = a.gW1 ? a.gW1 + goff : nullptr;
-    float* const gb1 = a.gb1 ? a.gb1 + goff : nullptr;
-    float* const gW2 = a.gW2 ? a.gW2 + goff : nullptr;
-    float* const gb2 = a.gb2 ? a.gb2 + goff : nullptr;
+    float* const gW1 = (FULL && a.gW1) ? a.gW1 + goff : nullptr;
+    float* const gb1 = (FULL && a.gb1) ? a.gb1 + goff : nullptr;
+    float* const gW2 = (FULL && a.gW2) ? a.gW2 + goff : nullptr;
+    float* const gb2 = (FULL && a.gb2) ? a.gb2 + goff : nullptr;
     LLSend llv;
     const LLSend* const ll = sxll ? &llv : nullptr;
     const float* const gbase = sxll ? a.sx.grads[a.sx.rank] : nullptr;
@@ -364,7 +368,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
     DBG_STAMP(1);
     grid_barrier(a.sync, bar_target, NC);
     DBG_STAMP(2);
-    if (a.poison && s > 0) {                 // phase C of the previous step (the only reader of these rows) is over
+    if ((FULL && a.poison) && s > 0) {                 // phase C of the previous step (the only reader of these rows) is over
       for (int r = g; r < B; r += (int)NC) {
         for (int i = tid; i < H; i += kThreads) {
           __stcg(a.Hbuf + (long)r * H + i, __int_as_float(0x7fc00000));
@@ -393,8 +397,8 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
     // reference's global_step and variable updates are separate, unordered ops as well); the exit handshake
     // puts a system fence before the launch's last increment.  The result (the global step the previous step
     // observed, what the reference fetches next to train_op) is consumed at the end of phase C.
-    if (g == book && tid == 0 && s > 0 && a.train && !a.has_sx)
-      pending_step = a.gW1 ? *reinterpret_cast<volatile int*>(a.global_step)
+    if (g == book && tid == 0 && s > 0 && a.train && !(FULL && a.has_sx))
+      pending_step = (FULL && a.gW1) ? *reinterpret_cast<volatile int*>(a.global_step)
                            : dtfe::atom_add_relaxed_sys_s32(a.global_step, 1);
     // Small parameters.  Direct mode (evaluation, synchronous mode, first step of a launch): read from the
     // shard after the barrier, so every CTA sees the pushes all CTAs made in the previous step's phase C.
@@ -591,7 +595,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
     DBG_STAMP(3);
     grid_barrier(a.sync, bar_target, NC);
     DBG_STAMP(4);
-    if (a.poison && slice) {                 // every reader of this CTA's split-K partial is behind the barrier
+    if ((FULL && a.poison) && slice) {                 // every reader of this CTA's split-K partial is behind the barrier
       float* P = a.part + (long)g * B * H;
       for (int i = tid; i < B * H; i += kThreads) __stcg(P + i, __int_as_float(0x7fc00000));
     }
@@ -762,10 +766,10 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
         }
         // Direct mode: the same thread reads back exactly the elements it just pushed (synchronous mode:
         // the parameters only change in phase D, the read-back happens there)
-        if (!ahead && !a.has_sx) fetch_w1();
+        if (!ahead && !(FULL && a.has_sx)) fetch_w1();
       }
       DBG_STAMP(5);
-      if (g == book && tid == 0 && s > 0 && !a.has_sx) a.step_out[s - 1] = pending_step;
+      if (g == book && tid == 0 && s > 0 && !(FULL && a.has_sx)) a.step_out[s - 1] = pending_step;
       // No per-step completion handshake: the next grid barrier (or the exit handshake below) orders all
       // of this step's pushes before the global_step increment that counts them.
       __syncthreads();                            // dAs / Xs are rewritten by the next step
@@ -906,7 +910,7 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
           asm volatile("st.release.gpu.global.u32 [%0], %1;" :: "l"(a.sync + 2), "r"(kSxAbort) : "memory");
         }
         __syncthreads();                          // the updated W1 slice is in Ws for every thread
-      } else if (a.has_sx) {
+      } else if ((FULL && a.has_sx)) {
         // ------------------------------ phase D (synchronous mode) -------------------------------
         // D1: every CTA's gradients are in this rank's exchange buffer
         grid_barrier(a.sync, bar_target, NC);
@@ -995,12 +999,12 @@ __global__ void __launch_bounds__(kThreads, 1) k_mlp2_step(Mlp2Args a) {
     unsigned prev = atomicAdd(a.sync + 1, 1u);
     if (prev == NC - 1) {
       a.sync[0] = 0; a.sync[1] = 0;
-      if (a.has_sx && a.sx.mode >= 1) a.sync[2] = 0;
-      if (a.has_sx) {
+      if ((FULL && a.has_sx) && a.sx.mode >= 1) a.sync[2] = 0;
+      if ((FULL && a.has_sx)) {
         *a.sx.epoch = sx_epoch0 + (unsigned)steps_done;
       } else if (a.train && a.nsteps > 0) {
         if (a.remote) __threadfence_system();
-        int old = a.gW1 ? *reinterpret_cast<volatile int*>(a.global_step) : dtfe::atom_add_sys_s32(a.global_step, 1);
+        int old = (FULL && a.gW1) ? *reinterpret_cast<volatile int*>(a.global_step) : dtfe::atom_add_sys_s32(a.global_step, 1);
         a.step_out[a.nsteps - 1] = old;
       }
       if (a.cursor) *a.cursor = (int)sbase + a.nsteps;   // every CTA read the cursor before arriving here
@@ -1101,9 +1105,10 @@ static int mlp2_max_ctas(int* out) {
   DTFE_CUDA_CHECK(cudaGetDevice(&dev));
   if (dev >= 64 || cached[dev] == 0) {
     size_t smem = smem_floats<KS>() * sizeof(float);
-    DTFE_CUDA_CHECK(cudaFuncSetAttribute(k_mlp2_step<KS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    DTFE_CUDA_CHECK(cudaFuncSetAttribute(k_mlp2_step<KS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    DTFE_CUDA_CHECK(cudaFuncSetAttribute(k_mlp2_step<KS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0, sms = 0;
-    DTFE_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_mlp2_step<KS>, kThreads, smem));
+    DTFE_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_mlp2_step<KS, true>, kThreads, smem));
     DTFE_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     int n = per_sm * sms;
     if (dev < 64) cached[dev] = n;
@@ -1135,7 +1140,9 @@ static int mlp2_launch(Mlp2Args& a, cudaStream_t stream) {
   int NC = 0;
   if (int rc = mlp2_grid_width<KS>(a.B, a.D, a.H, &NC)) return rc;   // also sets the kernel's smem attribute once
   void* args[] = {&a};
-  DTFE_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)k_mlp2_step<KS>, dim3(NC), dim3(kThreads), args, smem, stream));
+  const bool full = a.has_sx || a.poison || a.gW1 != nullptr;
+  DTFE_CUDA_CHECK(cudaLaunchCooperativeKernel(full ? (void*)k_mlp2_step<KS, true> : (void*)k_mlp2_step<KS, false>, dim3(NC),
+                                              dim3(kThreads), args, smem, stream));
   return 0;
 }
 

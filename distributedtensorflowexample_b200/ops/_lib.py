@@ -47,7 +47,9 @@ def cuda_lib(build_if_missing: bool = True) -> ctypes.CDLL:
         if _cuda is None:
             if build_if_missing and not _build.CUDA_LIB.exists() and os.environ.get("DTFE_NO_AUTOBUILD") != "1":
                 _build.build_cuda()
-            _cuda = _load(_build.CUDA_LIB)
+            # DTFE_CUDA_LIB: load another build of the library (A/B timing of kernel variants)
+            override = os.environ.get("DTFE_CUDA_LIB")
+            _cuda = _load(_build.CUDA_LIB if not override else type(_build.CUDA_LIB)(override))
             _cuda.dtfe_last_error.restype = ctypes.c_char_p
             _cuda.dtfe_mlp2_step_workspace_words.restype = ctypes.c_size_t
         return _cuda
