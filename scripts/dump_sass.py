@@ -15,7 +15,8 @@ OUT = os.path.join(ROOT, "profiles", "sass")
 
 # output name -> (substring of the demangled kernel name, what it is)
 KERNELS = {
-    "k_mlp2_step_8": ("k_mlp2_step<8>", "fused MNIST step, fp32 SIMT (async push = red.add.sys; sync all-reduce exchange = phase D)"),
+    "k_mlp2_step_8_async": ("k_mlp2_step<8, false>", "fused MNIST step, fp32 SIMT, lean instantiation: asynchronous training (pull = cp.async / ld.relaxed.sys from the shard, push = red.add.sys) and evaluation"),
+    "k_mlp2_step_8_sync": ("k_mlp2_step<8, true>", "the same step with the synchronous exchange as phase D (owners' reduce-scatter, per-CTA-flag all-reduce, {value, step} pair transport)"),
     "k_mlp2_step_tc_10": ("k_mlp2_step_tc<10>", "fused MNIST step on tcgen05 kind::tf32 (8-CTA cluster, W1 pulled by TMA, X by TMA gather4)"),
     "k_gemm_tc2_bf16_fwd_bias_act": ("k_gemm_tc2<0, 0, 1, 1>", "2-CTA GEMM, forward X.W (B MN-major = shard weights by TMA) + bias + sigmoid epilogue"),
     "k_gemm_tc2_bf16_dw_push": ("k_gemm_tc2<0, 1, 1, 3>", "2-CTA GEMM, dW = X^T.dY with the push (red.add.v4.bf16x2) as its epilogue"),
