@@ -56,6 +56,7 @@ def _worker(training_steps=10 ** 7, log_every=100, eval_every=10000, faults=None
     w.task_index = 0
     w.tracer = tracing.get_tracer()
     w._start_time, w._start_step = 100.0, 0
+    w.summary_writer = types.SimpleNamespace(added=[], add_summary=lambda summ, step: w.summary_writer.added.append((step, summ.values)))
     return w
 
 
@@ -91,3 +92,6 @@ def test_digest_evaluates_at_multiples_of_eval_every_including_zero(capsys):
     w._digest_launch(np.ones(100, np.float32), np.ones(100, np.float32), steps, 1.0, 2.0, lambda: 0.5, rec)
     out = capsys.readouterr().out.splitlines()
     assert out == ["test accuracy: 0.25"] + ["test accuracy: 0.5"] * 4          # steps 50, 100, 150, 200
+    # every evaluation is also logged (additive tag), keyed by the step that triggered it
+    assert [s for s, _ in w.summary_writer.added] == [0, 50, 100, 150, 200]
+    assert w.summary_writer.added[1][1] == [("local/test_accuracy", 0.5)]
