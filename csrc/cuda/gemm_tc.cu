@@ -53,7 +53,12 @@ template <int DT> struct Elem {
 };
 constexpr int kThreads = 192;
 
-enum { EPI_STORE = 0, EPI_BIAS_ACT = 1, EPI_ACTGRAD = 2, EPI_PUSH = 3, EPI_PUSH_TMA = 4 };
+enum { EPI_STORE = 0, EPI_BIAS_ACT = 1, EPI_ACTGRAD = 2, EPI_PUSH = 3, EPI_PUSH_TMA = 4, EPI_BIAS_ACT_TMA = 5, EPI_ACTGRAD_TMA = 6 };
+// the *_TMA forms (2-CTA kernel, bf16 output): the epilogue stages the bf16 tile in shared memory and hands it to the
+// TMA engine - a reduce-add for the push, a plain store for the forward / dX outputs - instead of four row-strided
+// 16-byte stores per thread and chunk.
+__host__ __device__ constexpr bool epi_tma(int e) { return e == EPI_PUSH_TMA || e == EPI_BIAS_ACT_TMA || e == EPI_ACTGRAD_TMA; }
+__host__ __device__ constexpr int epi_base(int e) { return e == EPI_PUSH_TMA ? EPI_PUSH : e == EPI_BIAS_ACT_TMA ? EPI_BIAS_ACT : e == EPI_ACTGRAD_TMA ? EPI_ACTGRAD : e; }
 enum { OUT_F32 = 0, OUT_BF16 = 1 };
 
 struct GemmTcArgs {
@@ -74,14 +79,9 @@ __device__ __forceinline__ float ld_param(const void* p, int dtype, int i) {
   return dtype == OUT_F32 ? __ldg((const float*)p + i) : __bfloat162float(((const __nv_bfloat16*)p)[i]);
 }
 
+// The element-wise part of an epilogue: v[0..31] = accumulators of row m, columns n0..n0+31, transformed in place.
 template <int EPI>
-__device__ __forceinline__ void epilogue_chunk(const GemmTcArgs& g, int m, int n0, const uint32_t* acc_bits) {
-  // one row m, 32 consecutive columns n0..n0+31
-  float v[32];
-#pragma unroll
-  for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(acc_bits[j]);
-  const int nvalid = min(32, g.N - n0);
-  if (nvalid <= 0) return;
+__device__ __forceinline__ void epilogue_transform(const GemmTcArgs& g, int m, int n0, int nvalid, float* v) {
   if (EPI == EPI_BIAS_ACT) {
     // The 32 bias values of this chunk are fetched up front with vector loads: one load per element inside the
     // guarded loop below made every element a serial load -> add -> exp -> rcp chain (ncu: the bias+sigmoid
@@ -149,6 +149,17 @@ __device__ __forceinline__ void epilogue_chunk(const GemmTcArgs& g, int m, int n
     }
     }
   }
+}
+
+template <int EPI>
+__device__ __forceinline__ void epilogue_chunk(const GemmTcArgs& g, int m, int n0, const uint32_t* acc_bits) {
+  // one row m, 32 consecutive columns n0..n0+31
+  float v[32];
+#pragma unroll
+  for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(acc_bits[j]);
+  const int nvalid = min(32, g.N - n0);
+  if (nvalid <= 0) return;
+  epilogue_transform<EPI>(g, m, n0, nvalid, v);
   if (EPI == EPI_PUSH) {
     if (g.G) {
       float* gp = g.G + (long)m * g.ldg + n0;
@@ -351,6 +362,10 @@ __device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* map, const 
   asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];"
                :: "l"(map), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1) : "memory");
 }
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, const void* smem_src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.tile.bulk_group [%0, {%2, %3}], [%1];"
+               :: "l"(map), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1) : "memory");
+}
 __device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
@@ -416,7 +431,7 @@ k_gemm_tc2(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ C
   // EPI_PUSH_TMA: the epilogue stages the scaled bf16 tile in shared memory (4 swizzled 128x64 boxes) and
   // pushes it with TMA reduce-adds - 16 KB per operation instead of 16 B per red instruction, which is what
   // makes a push into a PEER shard run at NVLink speed.  It trades two pipeline stages for the staging tile.
-  constexpr int kStages = EPI == EPI_PUSH_TMA ? 4 : kStages2;
+  constexpr int kStages = epi_tma(EPI) ? 4 : kStages2;
   using E = Elem<DT>;
   constexpr int BK = E::BKE;
   constexpr uint32_t A_BYTES = BM * 128;               // this CTA's 128 rows of A
@@ -527,10 +542,10 @@ k_gemm_tc2(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ C
       mbar_wait(&tmem_full_bar[as], aphase);
       tc_fence_after();
       const int m = m0 + q * 32 + lane;
-      if (EPI == EPI_PUSH_TMA) {
+      if (epi_tma(EPI)) {
         uint8_t* staging = smem + (size_t)kStages * STAGE_BYTES;
         const int row = q * 32 + lane;
-        // the previous tile's reduce-adds must have finished reading the staging tile
+        // the previous tile's bulk stores must have finished reading the staging tile
         if (warp == 2 && lane == 0) tma_store_wait_read();
         named_bar_sync(1, 128);
 #pragma unroll 1
@@ -538,16 +553,27 @@ k_gemm_tc2(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ C
           uint32_t r[32];
           tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN2 + c), r);
           tmem_ld_wait();
+          float v[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+          if (EPI == EPI_PUSH_TMA) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] *= g.alpha;
+          } else {
+            // rows / columns beyond the matrix are clipped by the tensor map; their values only have to be harmless
+            const int nvalid = min(32, g.N - (n0 + c));
+            if (m < g.M && nvalid > 0) epilogue_transform<epi_base(EPI)>(g, m, n0 + c, nvalid, v);
+          }
           // 32 columns = 4 chunks of 16 B inside the 128-byte row of box c/64, XOR-swizzled like the tensor map
           uint8_t* rowp = staging + (size_t)(c >> 6) * STAGING_BOX + (size_t)row * 128;
           const int chunk0 = (c & 32) ? 4 : 0;
 #pragma unroll
           for (int u = 0; u < 4; ++u) {
             uint4 pk;
-            pk.x = dtfe::pack_bf16x2(g.alpha * __uint_as_float(r[8 * u + 0]), g.alpha * __uint_as_float(r[8 * u + 1]));
-            pk.y = dtfe::pack_bf16x2(g.alpha * __uint_as_float(r[8 * u + 2]), g.alpha * __uint_as_float(r[8 * u + 3]));
-            pk.z = dtfe::pack_bf16x2(g.alpha * __uint_as_float(r[8 * u + 4]), g.alpha * __uint_as_float(r[8 * u + 5]));
-            pk.w = dtfe::pack_bf16x2(g.alpha * __uint_as_float(r[8 * u + 6]), g.alpha * __uint_as_float(r[8 * u + 7]));
+            pk.x = dtfe::pack_bf16x2(v[8 * u + 0], v[8 * u + 1]);
+            pk.y = dtfe::pack_bf16x2(v[8 * u + 2], v[8 * u + 3]);
+            pk.z = dtfe::pack_bf16x2(v[8 * u + 4], v[8 * u + 5]);
+            pk.w = dtfe::pack_bf16x2(v[8 * u + 6], v[8 * u + 7]);
             *reinterpret_cast<uint4*>(rowp + (((chunk0 + u) ^ (row & 7)) << 4)) = pk;
           }
         }
@@ -555,10 +581,13 @@ k_gemm_tc2(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ C
         named_bar_sync(1, 128);
         if (warp == 2 && lane == 0) {
           int part = 0, mloc = m0;
-          if (g.nparts) { part = m0 / g.rows_per_part; mloc = m0 - part * g.rows_per_part; }
+          if (EPI == EPI_PUSH_TMA && g.nparts) { part = m0 / g.rows_per_part; mloc = m0 - part * g.rows_per_part; }
 #pragma unroll
           for (int jb = 0; jb < BN2 / 64; ++jb)
-            if (n0 + jb * 64 < g.N) tma_reduce_add_2d(&dmaps.m[part], staging + (size_t)jb * STAGING_BOX, n0 + jb * 64, mloc);
+            if (n0 + jb * 64 < g.N) {
+              if (EPI == EPI_PUSH_TMA) tma_reduce_add_2d(&dmaps.m[part], staging + (size_t)jb * STAGING_BOX, n0 + jb * 64, mloc);
+              else tma_store_2d(&dmaps.m[0], staging + (size_t)jb * STAGING_BOX, n0 + jb * 64, mloc);
+            }
           tma_store_commit();
         }
       } else {
@@ -567,7 +596,7 @@ k_gemm_tc2(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ C
           uint32_t r[32];
           tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN2 + c), r);
           tmem_ld_wait();
-          if (m < g.M && n0 + c < g.N) epilogue_chunk<EPI == EPI_PUSH_TMA ? EPI_PUSH : EPI>(g, m, n0 + c, r);
+          if (m < g.M && n0 + c < g.N) epilogue_chunk<epi_base(EPI)>(g, m, n0 + c, r);
         }
       }
       tc_fence_before();
@@ -577,7 +606,7 @@ k_gemm_tc2(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ C
     }
   }
 
-  if (EPI == EPI_PUSH_TMA && warp == 2 && lane == 0) tma_store_wait_all();   // pushes complete before exit
+  if (epi_tma(EPI) && warp == 2 && lane == 0) tma_store_wait_all();   // bulk stores / pushes complete before exit
   tc_fence_before();
   __syncthreads();
   cluster_sync_all();            // nobody exits (or frees TMEM) while its peer may still signal it
@@ -609,7 +638,7 @@ int launch_cfg(const CUtensorMap& ta, const CUtensorMap& tb, const GemmTcArgs& g
 
 template <int DT, int A_MN, int B_MN, int EPI>
 int launch_cfg2(const CUtensorMap& ta, const CUtensorMap& tb, const DMaps& dm, const GemmTcArgs& g, cudaStream_t stream) {
-  constexpr size_t smem = EPI == EPI_PUSH_TMA
+  constexpr size_t smem = epi_tma(EPI)
       ? (size_t)4 * (BM * 128 + (BN2 / 2) * 128) + (size_t)(BN2 / 64) * BM * 128 + 1024
       : (size_t)kStages2 * (BM * 128 + (BN2 / 2) * 128) + 1024;
   auto kern = k_gemm_tc2<DT, A_MN, B_MN, EPI>;
@@ -649,6 +678,12 @@ int launch_epi2(int epi, int a_mn, int b_mn, const CUtensorMap& ta, const CUtens
     case EPI_PUSH: return launch_major2<DT, EPI_PUSH>(a_mn, b_mn, ta, tb, dm, g, s);
     case EPI_PUSH_TMA:
       if (DT == DT_BF16) return launch_major2<DT_BF16, EPI_PUSH_TMA>(a_mn, b_mn, ta, tb, dm, g, s);
+      break;
+    case EPI_BIAS_ACT_TMA:
+      if (DT == DT_BF16) return launch_major2<DT_BF16, EPI_BIAS_ACT_TMA>(a_mn, b_mn, ta, tb, dm, g, s);
+      break;
+    case EPI_ACTGRAD_TMA:
+      if (DT == DT_BF16) return launch_major2<DT_BF16, EPI_ACTGRAD_TMA>(a_mn, b_mn, ta, tb, dm, g, s);
       break;
   }
   dtfe_set_error("gemm_tc: unknown epilogue %d", epi);
@@ -734,7 +769,14 @@ int gemm_tc_impl(const dtfe_gemm_tc* p, void* stream) {
       }
       if (ok) epi = EPI_PUSH_TMA;
     }
-    return launch_epi2<DT>(epi, p->a_mn_major, p->b_mn_major, ta, tb, epi == EPI_PUSH_TMA ? local : dm, g, (cudaStream_t)stream);
+    // forward / dX outputs in bf16 can go through the TMA engine as well (DTFE_TMA_STORE=1).  Measured on 4096x8192x8192:
+    // 358 / 354 us against 326 / 315 us with per-thread stores - the staging tile costs two of the six pipeline stages
+    // and a CTA-wide handshake per tile, which outweighs the better store pattern when the target is local HBM.
+    if (DT == DT_BF16 && (epi == EPI_BIAS_ACT || epi == EPI_ACTGRAD) && p->out_bf16 && (p->ldd * 2) % 16 == 0 &&
+        ((uintptr_t)p->D % 16) == 0 && getenv("DTFE_TMA_STORE") != nullptr &&
+        make_tmap(&local.m[0], p->D, (uint64_t)p->N, (uint64_t)p->M, (uint64_t)p->ldd, 64, BM) == 0)
+      epi = epi == EPI_BIAS_ACT ? EPI_BIAS_ACT_TMA : EPI_ACTGRAD_TMA;
+    return launch_epi2<DT>(epi, p->a_mn_major, p->b_mn_major, ta, tb, epi_tma(epi) ? local : dm, g, (cudaStream_t)stream);
   }
   if (DT == DT_BF16 && bn == 256)
     return launch_epi<DT_BF16, 256>(p->epilogue, p->a_mn_major, p->b_mn_major, ta, tb, g, (cudaStream_t)stream);

@@ -291,8 +291,9 @@ class TcStepper:
         L = spec.num_layers
         self.launches_per_call = L + 2 + (L - 1) + 2 * L + 1
         import os
-        # streaming kernels for an output layer of width <= 16 (ops.thin_*): correct, but at 84 / 78 / 94 us they do
-        # not yet beat the 128-wide tensor-core tiles (57 / 70 / 46 us for 4096x8192x10), so they are opt-in
+        # streaming kernels for an output layer of width <= 16 (ops.thin_*): correct, but at 52 / 74 / 102 us (forward,
+        # dX, dW+push; scripts/bench_thin.py) only the forward one beats the 128-wide tensor-core tiles (57 / 70 / 45 us
+        # for 4096x8192x10), so they are opt-in
         self.thin = os.environ.get("DTFE_THIN") == "1"
         self._thin_scratch = None
 

@@ -273,14 +273,14 @@ class Worker:
                 self._summary_thread.drain()
             self.summary_writer.flush()
             os._exit(17)
-        if step % f.log_every == 0 and step != 0:
+        if f.log_every > 0 and step % f.log_every == 0 and step != 0:
             now = time.time() if now is None else now
             elapsed = now - self._start_time
             print("step: {}\t| cost: {}\t| speed: {}step/sec".format(
                 step, cost, float((step - self._start_step) / max(elapsed, 1e-9))), flush=True)
             self._start_time = now
             self._start_step = step
-        if step % f.eval_every == 0:
+        if f.eval_every > 0 and step % f.eval_every == 0:
             with self.tracer.span("eval", "host", step=step):
                 test_acc = eval_fn()
                 print("test accuracy: {}".format(test_acc), flush=True)
@@ -367,7 +367,12 @@ class Worker:
                     hold = False
         finally:
             # launches already queued run to completion on the GPU (they cannot be recalled); their steps were
-            # applied and counted, but like a reference worker that was told to stop, nobody logs them
+            # applied and counted, but like a reference worker that was told to stop, nobody logs them.  Wait for
+            # them: the shards they push into must stay mapped until they are done.
+            try:
+                torch.cuda.synchronize(dev)
+            except Exception:
+                pass
             writer.close()
         return step
 
@@ -380,7 +385,11 @@ class Worker:
         m = int(over[0]) + 1 if len(over) else n          # the step that ends training is the last one handled
         with self.tracer.span("summary", "host", steps=m):
             writer.submit(steps[:m], loss[:m], acc[:m])
-        hot = (steps[:m] % f.log_every == 0) | (steps[:m] % f.eval_every == 0)
+        hot = np.zeros(m, dtype=bool)
+        if f.log_every > 0:
+            hot |= steps[:m] % f.log_every == 0
+        if f.eval_every > 0:
+            hot |= steps[:m] % f.eval_every == 0
         hot[m - 1] = True
         if "kill_worker" in self.faults and self.faults["kill_worker"][0] == self.task_index:
             hot |= steps[:m] >= self.faults["kill_worker"][1]

@@ -68,6 +68,34 @@ def test_dense_layer_ops_tc(B_, din, dout):
     assert (Wb.float() - want).abs().max().item() < 2e-2 * want.abs().max().item() + 1e-3
 
 
+@pytest.mark.parametrize("B_,din,dout", [(4096, 1024, 2048), (4000, 1032, 2056)])
+def test_forward_and_dx_epilogues_through_tma_store(B_, din, dout, monkeypatch):
+    """DTFE_TMA_STORE=1: the 2-CTA kernel stages the bf16 output tile in shared memory and stores it with TMA
+    (rows and columns beyond the matrix are clipped by the tensor map); same numbers as the per-thread stores."""
+    from distributedtensorflowexample_b200.ops import gemm_tc as G
+    x = torch.rand(B_, din, device="cuda").bfloat16()
+    W = _mk((din, dout), 3, 0.05)
+    b = _mk((1, dout), 4)[0]
+    dY = _mk((B_, dout), 5, 0.1)
+    Hprev = torch.rand(B_, din, device="cuda").bfloat16()
+    outs = {}
+    for mode in ("0", "1"):
+        if mode == "1":
+            monkeypatch.setenv("DTFE_TMA_STORE", "1")
+        else:
+            monkeypatch.delenv("DTFE_TMA_STORE", raising=False)
+        out = torch.full((B_ + 8, dout), 7.0, device="cuda", dtype=torch.bfloat16)      # guard rows behind the matrix
+        G.dense_fwd_tc(x, W, b, 1, out[:B_], tile_n=512)
+        dX = torch.full((B_ + 8, din), 7.0, device="cuda", dtype=torch.bfloat16)
+        G.dense_bwd_dx_tc(dY, W, Hprev, dX[:B_], tile_n=512)
+        torch.cuda.synchronize()
+        assert (out[B_:] == 7.0).all() and (dX[B_:] == 7.0).all()                       # nothing written out of bounds
+        outs[mode] = (out[:B_].float(), dX[:B_].float())
+    ref = torch.sigmoid(x.float() @ W.float() + b.float())
+    assert (outs["1"][0] - ref).abs().max().item() < 1e-2
+    assert torch.equal(outs["0"][0], outs["1"][0]) and torch.equal(outs["0"][1], outs["1"][1])
+
+
 @pytest.mark.parametrize("parts", [0, 2, 4])
 @pytest.mark.parametrize("M,N,K", [(1024, 512, 256), (2048, 1536, 1024), (1000, 520, 300)])
 def test_push_epilogue_through_tma_reduce(M, N, K, parts):
