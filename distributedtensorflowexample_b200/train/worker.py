@@ -64,8 +64,9 @@ def plan_launch_steps(next_step_lb: int, training_steps: int, eval_every: int, n
                       nothing_in_flight: bool) -> int:
     """How many steps the next kernel launch of a worker should fuse (0: enqueue nothing, wait for results).
 
-    ``next_step_lb`` is a lower bound on the global step the next step of this worker will observe (last observed
-    step + 1 + this worker's steps in flight; other workers can only add to it).  The reference checks its
+    ``next_step_lb`` is the estimate of the global step the first step of the launch will observe: last observed
+    step + 1 + ``num_workers`` x this worker's steps in flight (exact for a lone worker; with peers, every step of
+    ours that is still queued stands for about ``num_workers`` global steps).  The reference checks its
     cadence rules after every single step (worker.py:143-159); a multi-step launch checks them when it returns,
     so its size is chosen such that, counting on this worker's own steps alone,
       * the step that observes ``training_steps`` (the last one the reference would run) is the last of a launch,
@@ -341,7 +342,9 @@ class Worker:
         try:
             while not stop and not sv.should_stop():
                 while len(pending) < PIPELINE_DEPTH and not hold:
-                    lb = next_lb + in_flight
+                    # where the global step will be when this launch starts: every step of ours still in flight
+                    # stands for about W global steps (the other workers run at our pace)
+                    lb = next_lb + W * in_flight
                     n = plan_launch_steps(lb, f.training_steps, f.eval_every, W, cap, not pending)
                     if n == 0:
                         break

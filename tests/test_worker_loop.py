@@ -95,3 +95,41 @@ def test_digest_evaluates_at_multiples_of_eval_every_including_zero(capsys):
     # every evaluation is also logged (additive tag), keyed by the step that triggered it
     assert [s for s, _ in w.summary_writer.added] == [0, 50, 100, 150, 200]
     assert w.summary_writer.added[1][1] == [("local/test_accuracy", 0.5)]
+
+
+def _race(T, Wk, cap, E, seed, depth=W.PIPELINE_DEPTH):
+    """Wk workers with the loop's planning rule and two launches in flight each, steps interleaved at random."""
+    import random
+    rnd = random.Random(seed)
+    g = 0
+    ws = [dict(pending=[], next_lb=0, inflight=0, stop=False, hold=False) for _ in range(Wk)]
+    while not all(w["stop"] for w in ws):
+        w = rnd.choice([w for w in ws if not w["stop"]])
+        while len(w["pending"]) < depth and not w["hold"]:
+            lb = w["next_lb"] + Wk * w["inflight"]
+            n = W.plan_launch_steps(lb, T, E, Wk, cap, not w["pending"])
+            if n == 0:
+                break
+            w["hold"] = E > 0 and lb + n - 1 >= -(-lb // E) * E
+            w["pending"].append([n, []]); w["inflight"] += n
+        l = w["pending"][0]
+        l[1].append(g); g += 1
+        if len(l[1]) == l[0]:
+            w["pending"].pop(0); w["inflight"] -= l[0]
+            hit = [s for s in l[1] if s >= T]
+            w["stop"] = bool(hit)
+            w["next_lb"] = max(w["next_lb"], (hit[0] if hit else l[1][-1]) + 1)
+            if not w["pending"]:
+                w["hold"] = False
+    return g
+
+
+def test_racing_workers_overshoot_training_steps_by_little():
+    """The reference overshoots training_steps by at most num_workers - 1 updates (every worker notices at its next
+    step).  Multi-step launches notice a launch late; the planning rule keeps that to a few dozen updates per worker
+    instead of the thousands a fixed launch size would run past the bound."""
+    for Wk in (2, 4, 8, 16):
+        for T in (250, 5000, 60000):
+            over = max(_race(T, Wk, 256, 10000, seed) - T for seed in range(3))
+            assert 0 < over <= 24 * Wk, (Wk, T, over)
+    assert _race(5000, 1, 256, 10000, 0) == 5001          # a lone worker: exactly the reference's count
